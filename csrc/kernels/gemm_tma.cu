@@ -1,0 +1,262 @@
+// Persistent, warp-specialised, TMA-fed tcgen05 GEMM for layer-sized matrices (the Dense
+// layers of the larger configs in BASELINE.json: ResNet-50's classifier, BERT-base's QKV /
+// FFN projections; same op as tf.keras.layers.Dense in /root/reference/tf_dist_example.py:46).
+//
+//   D[M,N] = act(A[M,K] * B[N,K]^T + bias[N])      A, B bf16 row-major (K contiguous)
+//
+// Shape of the kernel (one CTA per SM, 192 threads):
+//   warp 0      TMA producer: cp.async.bulk.tensor.2d tiles (128B swizzle) into a STAGES-deep ring
+//   warp 1      MMA issuer: one elected lane issues tcgen05.mma (128 x BN x 16) from smem descriptors,
+//               accumulating in TMEM; tcgen05.commit releases ring slots / publishes accumulators
+//   warps 2-5   epilogue: tcgen05.ld the accumulator (each warp its own 32-lane quarter), bias +
+//               activation, 128-bit global stores. Two TMEM accumulator stages let the epilogue
+//               of tile i overlap the MMAs of tile i+1.
+#include <cuda.h>
+#include "common.cuh"
+#include "../../include/tfdl_kernels.h"
+
+namespace tfdl {
+
+constexpr int BM = 128;
+constexpr int BK = 64;  // 64 bf16 = 128 bytes = one swizzle row
+
+struct TmaGemmParams {
+  float* Df;               // fp32 out (optional)
+  __nv_bfloat16* Dh;       // bf16 out (optional)
+  const float* bias;       // optional
+  int M, N, K, ldd;
+  int act;                 // 0 none, 1 relu, 2 gelu(tanh)
+  int m_tiles, n_tiles;
+};
+
+__device__ __forceinline__ float apply_act(float x, int act) {
+  if (act == 1) return fmaxf(x, 0.f);
+  if (act == 2) {
+    const float k0 = 0.7978845608028654f, k1 = 0.044715f;
+    float u = k0 * (x + k1 * x * x * x);
+    return 0.5f * x * (1.f + tanhf(u));
+  }
+  return x;
+}
+
+template <int BN, int STAGES>
+__global__ void __launch_bounds__(192, 1)
+tma_gemm_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ CUtensorMap tmB,
+                TmaGemmParams p) {
+  extern __shared__ __align__(1024) uint8_t smem_raw[];
+  // 1024-byte alignment is required by the 128B swizzle atom (8 rows x 128 B).
+  uint8_t* smem = reinterpret_cast<uint8_t*>((reinterpret_cast<uintptr_t>(smem_raw) + 1023) & ~uintptr_t(1023));
+  constexpr uint32_t A_BYTES = BM * BK * 2;
+  constexpr uint32_t B_BYTES = BN * BK * 2;
+  constexpr uint32_t STAGE_BYTES = A_BYTES + B_BYTES;
+  __shared__ uint64_t full_bar[STAGES], empty_bar[STAGES], acc_full[2], acc_empty[2];
+  __shared__ uint32_t tmem_slot;
+
+  const int warp = threadIdx.x >> 5;
+  const int num_tiles = p.m_tiles * p.n_tiles;
+  const int k_blocks = (p.K + BK - 1) / BK;
+  constexpr uint32_t TMEM_COLS = tmem_cols_for(2 * BN);
+
+  if (warp == 0) {
+    if (elect_one()) {
+      tma_prefetch_desc(&tmA);
+      tma_prefetch_desc(&tmB);
+    }
+    tmem_alloc(&tmem_slot, TMEM_COLS);
+  }
+  if (threadIdx.x == 32) {
+    for (int i = 0; i < STAGES; ++i) {
+      mbar_init(&full_bar[i], 1);
+      mbar_init(&empty_bar[i], 1);
+    }
+    for (int i = 0; i < 2; ++i) {
+      mbar_init(&acc_full[i], 1);
+      mbar_init(&acc_empty[i], 4);  // one arrive per epilogue warp
+    }
+    fence_mbar_init();
+  }
+  tc_fence_before_sync();
+  __syncthreads();
+  tc_fence_after_sync();
+  const uint32_t tmem_base = tmem_slot;
+  const uint32_t smem_base = smem_u32(smem);
+
+  if (warp == 0) {
+    // ------------------------------ TMA producer ------------------------------
+    if (elect_one()) {
+      uint32_t stage = 0, phase = 0;
+      for (int t = blockIdx.x; t < num_tiles; t += gridDim.x) {
+        const int mt = t % p.m_tiles, nt = t / p.m_tiles;
+        for (int kb = 0; kb < k_blocks; ++kb) {
+          mbar_wait(&empty_bar[stage], phase ^ 1);
+          mbar_expect_tx(&full_bar[stage], STAGE_BYTES);
+          const uint32_t sa = smem_base + stage * STAGE_BYTES;
+          tma_load_2d(sa, &tmA, kb * BK, mt * BM, &full_bar[stage]);
+          tma_load_2d(sa + A_BYTES, &tmB, kb * BK, nt * BN, &full_bar[stage]);
+          if (++stage == STAGES) { stage = 0; phase ^= 1; }
+        }
+      }
+    }
+  } else if (warp == 1) {
+    // ------------------------------ MMA issuer --------------------------------
+    if (elect_one()) {
+      constexpr uint32_t idesc = umma_idesc_bf16(BM, BN, false, false);
+      uint32_t stage = 0, phase = 0, as = 0, aphase = 0;
+      for (int t = blockIdx.x; t < num_tiles; t += gridDim.x) {
+        mbar_wait(&acc_empty[as], aphase ^ 1);
+        tc_fence_after_sync();
+        const uint32_t d_tmem = tmem_base + as * BN;
+        for (int kb = 0; kb < k_blocks; ++kb) {
+          mbar_wait(&full_bar[stage], phase);
+          tc_fence_after_sync();
+          const uint32_t sa = smem_base + stage * STAGE_BYTES;
+          const uint32_t sb = sa + A_BYTES;
+#pragma unroll
+          for (int k = 0; k < BK / 16; ++k) {
+            // K-major, 128B swizzle: 8-row atoms 1024 B apart; a K step of 16 bf16 = +32 B
+            uint64_t ad = umma_smem_desc(sa + k * 32, 16, 1024, SWZ_128B);
+            uint64_t bd = umma_smem_desc(sb + k * 32, 16, 1024, SWZ_128B);
+            umma_bf16(d_tmem, ad, bd, idesc, (kb | k) != 0);
+          }
+          umma_commit(&empty_bar[stage]);
+          if (++stage == STAGES) { stage = 0; phase ^= 1; }
+        }
+        umma_commit(&acc_full[as]);
+        if (++as == 2) { as = 0; aphase ^= 1; }
+      }
+    }
+  } else {
+    // ------------------------------ epilogue ----------------------------------
+    const int q = warp & 3;  // TMEM lane quarter this warp may read
+    uint32_t as = 0, aphase = 0;
+    for (int t = blockIdx.x; t < num_tiles; t += gridDim.x) {
+      const int mt = t % p.m_tiles, nt = t / p.m_tiles;
+      mbar_wait(&acc_full[as], aphase);
+      tc_fence_after_sync();
+      const int row = mt * BM + q * 32 + (int)lane_id();
+      const uint32_t t_row = tmem_base + as * BN + ((uint32_t)(q * 32) << 16);
+#pragma unroll 1
+      for (int c = 0; c < BN; c += 32) {
+        uint32_t v[32];
+        tmem_ld32(t_row + c, v);
+        tmem_ld_wait();
+        const int col0 = nt * BN + c;
+        if (row < p.M && col0 < p.N) {
+          float x[32];
+#pragma unroll
+          for (int i = 0; i < 32; ++i) {
+            float b = (p.bias && col0 + i < p.N) ? __ldg(p.bias + col0 + i) : 0.f;
+            x[i] = apply_act(__uint_as_float(v[i]) + b, p.act);
+          }
+          const bool full = (col0 + 32 <= p.N);
+          if (p.Dh) {
+            __nv_bfloat16* dst = p.Dh + (size_t)row * p.ldd + col0;
+            if (full && ((reinterpret_cast<uintptr_t>(dst) & 15) == 0)) {
+#pragma unroll
+              for (int i = 0; i < 32; i += 8) {
+                uint4 o = make_uint4(pack_bf16x2(x[i], x[i + 1]), pack_bf16x2(x[i + 2], x[i + 3]),
+                                     pack_bf16x2(x[i + 4], x[i + 5]), pack_bf16x2(x[i + 6], x[i + 7]));
+                *reinterpret_cast<uint4*>(dst + i) = o;
+              }
+            } else {
+              for (int i = 0; i < 32 && col0 + i < p.N; ++i) dst[i] = __float2bfloat16(x[i]);
+            }
+          }
+          if (p.Df) {
+            float* dst = p.Df + (size_t)row * p.ldd + col0;
+            if (full && ((reinterpret_cast<uintptr_t>(dst) & 15) == 0)) {
+#pragma unroll
+              for (int i = 0; i < 32; i += 4)
+                *reinterpret_cast<float4*>(dst + i) = make_float4(x[i], x[i + 1], x[i + 2], x[i + 3]);
+            } else {
+              for (int i = 0; i < 32 && col0 + i < p.N; ++i) dst[i] = x[i];
+            }
+          }
+        }
+      }
+      tc_fence_before_sync();
+      __syncwarp();
+      if (lane_id() == 0) mbar_arrive(&acc_empty[as]);
+      if (++as == 2) { as = 0; aphase ^= 1; }
+    }
+  }
+  tc_fence_before_sync();
+  __syncthreads();
+  if (warp == 0) tmem_dealloc(tmem_base, TMEM_COLS);
+}
+
+// ---------------------------------------------------------------------------------------
+// host side
+// ---------------------------------------------------------------------------------------
+typedef CUresult (*EncodeTiledFn)(CUtensorMap*, CUtensorMapDataType, cuuint32_t, void*, const cuuint64_t*,
+                                  const cuuint64_t*, const cuuint32_t*, const cuuint32_t*,
+                                  CUtensorMapInterleave, CUtensorMapSwizzle, CUtensorMapL2promotion,
+                                  CUtensorMapFloatOOBfill);
+static EncodeTiledFn get_encode_fn() {
+  static EncodeTiledFn fn = nullptr;
+  if (!fn) {
+    void* sym = nullptr;
+    cudaDriverEntryPointQueryResult qres;
+    if (cudaGetDriverEntryPoint("cuTensorMapEncodeTiled", &sym, cudaEnableDefault, &qres) != cudaSuccess ||
+        qres != cudaDriverEntryPointSuccess)
+      return nullptr;
+    fn = reinterpret_cast<EncodeTiledFn>(sym);
+  }
+  return fn;
+}
+
+// Row-major bf16 matrix [rows][cols] (pitch ld elements) -> tensor map with a (box_rows x 64)
+// box and 128-byte swizzle.
+int make_tmap_bf16_2d(CUtensorMap* out, const void* base, uint64_t rows, uint64_t cols, uint64_t ld,
+                      uint32_t box_rows, uint32_t box_cols) {
+  EncodeTiledFn fn = get_encode_fn();
+  TFDL_REQUIRE(fn, "cuTensorMapEncodeTiled not available from the driver");
+  cuuint64_t dims[2] = {cols, rows};
+  cuuint64_t strides[1] = {ld * 2};
+  cuuint32_t box[2] = {box_cols, box_rows};
+  cuuint32_t estr[2] = {1, 1};
+  CUresult r = fn(out, CU_TENSOR_MAP_DATA_TYPE_BFLOAT16, 2, const_cast<void*>(base), dims, strides, box, estr,
+                  CU_TENSOR_MAP_INTERLEAVE_NONE, CU_TENSOR_MAP_SWIZZLE_128B, CU_TENSOR_MAP_L2_PROMOTION_L2_256B,
+                  CU_TENSOR_MAP_FLOAT_OOB_FILL_NONE);
+  TFDL_REQUIRE(r == CUDA_SUCCESS, "cuTensorMapEncodeTiled failed with CUresult %d", (int)r);
+  return 0;
+}
+
+template <int BN, int STAGES>
+static int launch_tma_gemm(const void* A, const void* B, TmaGemmParams p, int lda, int ldb, cudaStream_t s) {
+  CUtensorMap tmA, tmB;
+  int rc = make_tmap_bf16_2d(&tmA, A, p.M, p.K, lda, BM, BK);
+  if (rc) return rc;
+  rc = make_tmap_bf16_2d(&tmB, B, p.N, p.K, ldb, BN, BK);
+  if (rc) return rc;
+  p.m_tiles = (p.M + BM - 1) / BM;
+  p.n_tiles = (p.N + BN - 1) / BN;
+  constexpr size_t smem = (size_t)STAGES * (BM * BK * 2 + BN * BK * 2) + 1024;
+  auto kern = tma_gemm_kernel<BN, STAGES>;
+  TFDL_CUDA_OK(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
+  int dev = 0, sms = 148;
+  TFDL_CUDA_OK(cudaGetDevice(&dev));
+  TFDL_CUDA_OK(cudaDeviceGetAttribute(&sms, cudaDevAttrMultiProcessorCount, dev));
+  int grid = p.m_tiles * p.n_tiles < sms ? p.m_tiles * p.n_tiles : sms;
+  kern<<<grid, 192, smem, s>>>(tmA, tmB, p);
+  TFDL_CUDA_OK(cudaGetLastError());
+  return 0;
+}
+
+}  // namespace tfdl
+
+extern "C" int tfdl_gemm_bf16_tma(const void* A, const void* B, float* Df, void* Dh, const float* bias, int M,
+                                  int N, int K, int lda, int ldb, int ldd, int act, void* stream) {
+  using namespace tfdl;
+  TFDL_REQUIRE(M > 0 && N > 0 && K > 0, "gemm_tma: empty problem");
+  TFDL_REQUIRE(K % 8 == 0 && lda % 8 == 0 && ldb % 8 == 0, "gemm_tma: K, lda, ldb must be multiples of 8");
+  TFDL_REQUIRE(((uintptr_t)A & 15) == 0 && ((uintptr_t)B & 15) == 0, "gemm_tma: A/B must be 16-byte aligned");
+  TmaGemmParams p{};
+  p.Df = Df; p.Dh = (__nv_bfloat16*)Dh; p.bias = bias; p.M = M; p.N = N; p.K = K; p.ldd = ldd; p.act = act;
+  cudaStream_t s = (cudaStream_t)stream;
+  // Tile choice: 128x256 when there are enough tiles to fill the chip, else 128x128 / 128x64
+  long tiles256 = (long)((M + 127) / 128) * ((N + 255) / 256);
+  if (N >= 256 && tiles256 >= 120) return launch_tma_gemm<256, 4>(A, B, p, lda, ldb, s);
+  if (N > 64) return launch_tma_gemm<128, 6>(A, B, p, lda, ldb, s);
+  return launch_tma_gemm<64, 8>(A, B, p, lda, ldb, s);
+}
