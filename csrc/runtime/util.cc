@@ -1,0 +1,168 @@
+// Error string, crc32c (software slicing-by-8 with an SSE4.2 fast path), data-pipeline helpers.
+//
+// Data helpers stand in for tf.data's C++ kernels behind the reference's
+// `.shuffle(BUFFER_SIZE)` / `.batch(GLOBAL_BATCH_SIZE)` (/root/reference/tf_dist_example.py:31,33):
+// the shuffle buffer runs on element *indices* and batches are assembled by one gather straight
+// into a (pinned) staging buffer, optionally fusing the uint8 -> float32 /255 scale of
+// tf_dist_example.py:22-25.
+#include <algorithm>
+#include <thread>
+#include "rt_common.h"
+#include "../../include/tfdl_runtime.h"
+
+#if defined(__x86_64__)
+#include <nmmintrin.h>
+#include <cpuid.h>
+#endif
+
+namespace tfdl_rt {
+
+static thread_local char g_err[1024] = "";
+void set_error(const char* fmt, ...) {
+  va_list ap;
+  va_start(ap, fmt);
+  vsnprintf(g_err, sizeof(g_err), fmt, ap);
+  va_end(ap);
+}
+const char* last_error() { return g_err; }
+
+// ---------------------------------------------------------------------------------------------
+// crc32c (Castagnoli, reflected polynomial 0x82F63B78)
+// ---------------------------------------------------------------------------------------------
+static uint32_t g_tab[8][256];
+static bool g_tab_init = [] {
+  for (uint32_t i = 0; i < 256; ++i) {
+    uint32_t c = i;
+    for (int k = 0; k < 8; ++k) c = (c >> 1) ^ (0x82F63B78u & (0u - (c & 1)));
+    g_tab[0][i] = c;
+  }
+  for (uint32_t i = 0; i < 256; ++i)
+    for (int t = 1; t < 8; ++t) g_tab[t][i] = (g_tab[t - 1][i] >> 8) ^ g_tab[0][g_tab[t - 1][i] & 0xFF];
+  return true;
+}();
+
+#if defined(__x86_64__)
+static bool has_sse42() {
+  unsigned a, b, c, d;
+  if (!__get_cpuid(1, &a, &b, &c, &d)) return false;
+  return (c & bit_SSE4_2) != 0;
+}
+__attribute__((target("sse4.2"))) static uint32_t crc_hw(uint32_t crc, const uint8_t* p, size_t n) {
+  uint64_t c = crc;
+  while (n >= 8) {
+    uint64_t v;
+    memcpy(&v, p, 8);
+    c = _mm_crc32_u64(c, v);
+    p += 8;
+    n -= 8;
+  }
+  while (n--) c = _mm_crc32_u8((uint32_t)c, *p++);
+  return (uint32_t)c;
+}
+#endif
+
+uint32_t crc32c_extend(uint32_t crc, const void* data, size_t n) {
+  (void)g_tab_init;
+  const uint8_t* p = static_cast<const uint8_t*>(data);
+  uint32_t c = crc ^ 0xFFFFFFFFu;
+#if defined(__x86_64__)
+  static const bool hw = has_sse42();
+  if (hw) return crc_hw(c, p, n) ^ 0xFFFFFFFFu;
+#endif
+  while (n >= 8) {
+    uint32_t lo, hi;
+    memcpy(&lo, p, 4);
+    memcpy(&hi, p + 4, 4);
+    lo ^= c;
+    c = g_tab[7][lo & 0xFF] ^ g_tab[6][(lo >> 8) & 0xFF] ^ g_tab[5][(lo >> 16) & 0xFF] ^ g_tab[4][lo >> 24] ^
+        g_tab[3][hi & 0xFF] ^ g_tab[2][(hi >> 8) & 0xFF] ^ g_tab[1][(hi >> 16) & 0xFF] ^ g_tab[0][hi >> 24];
+    p += 8;
+    n -= 8;
+  }
+  while (n--) c = g_tab[0][(c ^ *p++) & 0xFF] ^ (c >> 8);
+  return c ^ 0xFFFFFFFFu;
+}
+
+}  // namespace tfdl_rt
+
+using namespace tfdl_rt;
+
+extern "C" const char* tfdl_rt_last_error(void) { return last_error(); }
+extern "C" int tfdl_rt_abi_version(void) { return 1; }
+extern "C" uint32_t tfdl_rt_crc32c(uint32_t crc, const void* data, uint64_t n) { return crc32c_extend(crc, data, n); }
+extern "C" uint32_t tfdl_rt_crc32c_mask(uint32_t crc) { return crc32c_mask(crc); }
+
+// tf.data shuffle-buffer semantics on an index stream: hold `buffer` indices, emit a uniformly
+// random slot, refill it from the stream, drain the buffer in random order at the end.
+extern "C" int tfdl_rt_shuffle_indices(const int64_t* src, int64_t n, int64_t buffer, uint64_t seed, int64_t* out) {
+  if (n < 0 || buffer < 1) {
+    set_error("shuffle_indices: bad arguments n=%lld buffer=%lld", (long long)n, (long long)buffer);
+    return -1;
+  }
+  Rng rng(seed);
+  if (buffer >= n) {
+    std::copy(src, src + n, out);
+    for (int64_t i = n - 1; i > 0; --i) std::swap(out[i], out[rng.below(i + 1)]);
+    return 0;
+  }
+  std::vector<int64_t> buf(src, src + buffer);
+  int64_t o = 0;
+  for (int64_t t = buffer; t < n; ++t) {
+    uint64_t j = rng.below(buffer);
+    out[o++] = buf[j];
+    buf[j] = src[t];
+  }
+  for (int64_t i = buffer - 1; i > 0; --i) std::swap(buf[i], buf[rng.below(i + 1)]);
+  std::copy(buf.begin(), buf.end(), out + o);
+  return 0;
+}
+
+template <class F>
+static void parallel_rows(int64_t n, int threads, F fn) {
+  if (threads <= 1 || n < 256) {
+    fn(0, n);
+    return;
+  }
+  std::vector<std::thread> ts;
+  int64_t per = (n + threads - 1) / threads;
+  for (int t = 0; t < threads; ++t) {
+    int64_t lo = t * per, hi = std::min(n, lo + per);
+    if (lo >= hi) break;
+    ts.emplace_back([=] { fn(lo, hi); });
+  }
+  for (auto& t : ts) t.join();
+}
+
+// dst[i, :] = src[idx[i], :]  (row_bytes each)
+extern "C" int tfdl_rt_gather_rows(const void* src, int64_t num_rows, int64_t row_bytes, const int64_t* idx,
+                                   int64_t n, void* dst, int threads) {
+  for (int64_t i = 0; i < n; ++i)
+    if (idx[i] < 0 || idx[i] >= num_rows) {
+      set_error("gather_rows: index %lld out of range [0,%lld)", (long long)idx[i], (long long)num_rows);
+      return -1;
+    }
+  const char* s = static_cast<const char*>(src);
+  char* d = static_cast<char*>(dst);
+  parallel_rows(n, threads, [=](int64_t lo, int64_t hi) {
+    for (int64_t i = lo; i < hi; ++i) memcpy(d + i * row_bytes, s + idx[i] * row_bytes, row_bytes);
+  });
+  return 0;
+}
+
+// dst[i, :] = float(src_u8[idx[i], :]) * scale   (the scale() map of the reference fused into batching)
+extern "C" int tfdl_rt_gather_rows_u8_to_f32(const uint8_t* src, int64_t num_rows, int64_t row_elems,
+                                             const int64_t* idx, int64_t n, float scale, float* dst, int threads) {
+  for (int64_t i = 0; i < n; ++i)
+    if (idx[i] < 0 || idx[i] >= num_rows) {
+      set_error("gather_rows_u8_to_f32: index %lld out of range", (long long)idx[i]);
+      return -1;
+    }
+  parallel_rows(n, threads, [=](int64_t lo, int64_t hi) {
+    for (int64_t i = lo; i < hi; ++i) {
+      const uint8_t* s = src + idx[i] * row_elems;
+      float* d = dst + i * row_elems;
+      for (int64_t j = 0; j < row_elems; ++j) d[j] = (float)s[j] * scale;
+    }
+  });
+  return 0;
+}

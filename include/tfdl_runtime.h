@@ -1,0 +1,69 @@
+/* C ABI of libtfdl_runtime.so - host-side runtime (no CUDA dependency).
+ *
+ * Return convention: 0 = ok; negative = failure, tfdl_rt_last_error() has the message
+ * (-2: a peer failed / connection lost, -3: timeout). Handles are opaque pointers.
+ * "ref:" notes name the line of /root/reference each piece stands in for.
+ */
+#ifndef TFDL_RUNTIME_H_
+#define TFDL_RUNTIME_H_
+#include <stdint.h>
+#ifdef __cplusplus
+extern "C" {
+#endif
+
+const char* tfdl_rt_last_error(void);
+int tfdl_rt_abi_version(void);
+
+/* ---- crc32c (checkpoint + event-file checksums) ------------------------------------------ */
+uint32_t tfdl_rt_crc32c(uint32_t crc, const void* data, uint64_t n);
+uint32_t tfdl_rt_crc32c_mask(uint32_t crc);
+
+/* ---- input pipeline helpers (ref: tf_dist_example.py:22-33 map/shuffle/batch) ------------ */
+int tfdl_rt_shuffle_indices(const int64_t* src, int64_t n, int64_t buffer, uint64_t seed, int64_t* out);
+int tfdl_rt_gather_rows(const void* src, int64_t num_rows, int64_t row_bytes, const int64_t* idx, int64_t n,
+                        void* dst, int threads);
+int tfdl_rt_gather_rows_u8_to_f32(const uint8_t* src, int64_t num_rows, int64_t row_elems, const int64_t* idx,
+                                  int64_t n, float scale, float* dst, int threads);
+
+/* ---- TCP control plane + RING collective (ref: README.md:21-23,65-68) -------------------- */
+/* Binds the port of addrs[rank], connects ring/control/heartbeat channels, returns once every
+ * peer has joined (or NULL after timeout_ms). addrs = training tasks in rank order. */
+void* tfdl_rt_group_create(int rank, int world, const char* const* addrs, int timeout_ms, int hb_interval_ms,
+                           int hb_timeout_ms);
+void tfdl_rt_group_destroy(void* group);
+int tfdl_rt_group_rank(void* group);
+int tfdl_rt_group_world(void* group);
+int tfdl_rt_group_failed_rank(void* group); /* -1 while everyone is alive */
+void tfdl_rt_group_set_timeout(void* group, int ms);
+uint64_t tfdl_rt_group_bytes_sent(void* group);
+int tfdl_rt_barrier(void* group);
+int tfdl_rt_allgather(void* group, const void* in, uint64_t nbytes, void* out /* world*nbytes */);
+int tfdl_rt_broadcast0(void* group, void* buf, uint64_t nbytes);
+int tfdl_rt_ring_allreduce_f32(void* group, float* buf, int64_t n);
+int tfdl_rt_ring_allreduce_f64(void* group, double* buf, int64_t n);
+
+/* ---- TensorBundle checkpoints (ref: README.md:51 "chief saves checkpoints") --------------- */
+void* tfdl_rt_bundle_writer_create(const char* prefix);
+int tfdl_rt_bundle_writer_add(void* w, const char* key, int tf_dtype, int ndim, const int64_t* dims,
+                              const void* data, uint64_t nbytes);
+int tfdl_rt_bundle_writer_add_string(void* w, const char* key, const void* data, uint64_t nbytes);
+int tfdl_rt_bundle_writer_finish(void* w); /* writes <prefix>.index and .data-00000-of-00001 atomically; frees w */
+void tfdl_rt_bundle_writer_abort(void* w);
+void* tfdl_rt_bundle_reader_open(const char* prefix);
+void tfdl_rt_bundle_reader_close(void* r);
+int tfdl_rt_bundle_reader_num_entries(void* r);
+int tfdl_rt_bundle_reader_entry(void* r, int i, char* key, int key_cap, int* tf_dtype, int* ndim, int64_t* dims8,
+                                uint64_t* nbytes);
+int tfdl_rt_bundle_reader_read(void* r, int i, void* dst, uint64_t cap, uint64_t* written);
+
+/* ---- TensorBoard event files (ref: README.md:51 "chief ... TensorBoard") ------------------ */
+void* tfdl_rt_events_open(const char* logdir, const char* suffix);
+int tfdl_rt_events_scalar(void* w, const char* tag, double value, int64_t step);
+int tfdl_rt_events_flush(void* w);
+const char* tfdl_rt_events_path(void* w);
+void tfdl_rt_events_close(void* w);
+
+#ifdef __cplusplus
+}
+#endif
+#endif /* TFDL_RUNTIME_H_ */

@@ -1,0 +1,530 @@
+"""Model / Sequential with compile() and fit() (ref: /root/reference/tf_dist_example.py:39-59).
+
+Call path of `fit` (mirrors SURVEY 3.3, re-designed):
+    fit -> strategy.experimental_distribute_dataset(x)      global batch -> per-replica batches
+        -> for epoch / for step: engine.train_step(PerReplica batch)
+              forward + loss + backward on every local replica (gradients land in the flat arena)
+              cross_device_ops.allreduce_grads(...)         ONE collective over the whole arena
+              optimizer update on the arena                 (fused into the collective on B200)
+              metric accumulators updated on device         (no host sync)
+        -> logs are read (device->host, plus a scalar all-reduce across workers) at epoch end only
+
+Two engines implement `train_step`: the portable TorchEngine below (CPU, stand-in baseline, anything
+without a native kernel) and keras/native_engine.NativeCnnEngine (sm_100a kernels + CUDA graph).
+"""
+from __future__ import annotations
+
+import os
+import sys
+import time
+from typing import Any, Dict, Iterator, List, Optional, Sequence, Tuple, Union
+
+import numpy as np
+import torch
+
+from ..data import Dataset
+from ..parallel import strategy as _strat
+from ..parallel.strategy import DistributedDataset, Strategy, get_strategy
+from ..parallel.values import MirroredVariable, ParamArena, PerReplica
+from . import callbacks as _cb
+from . import losses as _losses
+from . import metrics as _metrics
+from . import optimizers as _optimizers
+from .layers import CallContext, InputLayer, Layer
+
+_policy = {"compute_dtype": torch.float32}
+
+
+class mixed_precision:  # tf.keras.mixed_precision look-alike
+    @staticmethod
+    def set_global_policy(name: str) -> None:
+        _policy["compute_dtype"] = {"float32": torch.float32, "mixed_bfloat16": torch.bfloat16,
+                                    "mixed_float16": torch.float16}[name]
+
+    @staticmethod
+    def global_policy() -> str:
+        return {torch.float32: "float32", torch.bfloat16: "mixed_bfloat16", torch.float16: "mixed_float16"}[
+            _policy["compute_dtype"]]
+
+
+class History(_cb.Callback):
+    def __init__(self) -> None:
+        super().__init__()
+        self.history: Dict[str, List[float]] = {}
+        self.epoch: List[int] = []
+
+    def on_epoch_end(self, epoch: int, logs: Optional[Dict[str, float]] = None) -> None:
+        self.epoch.append(epoch)
+        for k, v in (logs or {}).items():
+            self.history.setdefault(k, []).append(v)
+
+
+def _as_dataset(x: Any, y: Any, batch_size: Optional[int], shuffle: bool = False) -> Dataset:
+    if isinstance(x, Dataset):
+        if y is not None:
+            raise ValueError("when x is a Dataset, y must not be given (the dataset yields (x, y))")
+        return x
+    xs = np.asarray(x)
+    tensors = (xs, np.asarray(y)) if y is not None else (xs,)
+    ds = Dataset.from_tensor_slices(tensors)
+    if shuffle:
+        ds = ds.shuffle(len(xs))
+    return ds.batch(batch_size or 32)
+
+
+class Model:
+    """Base model: a stack (or custom graph) of layers with Keras-style training methods."""
+
+    def __init__(self, name: Optional[str] = None) -> None:
+        self.name = name or "model"
+        self.strategy: Strategy = get_strategy()  # captured at construction: build under strategy.scope()
+        self.built = False
+        self.optimizer: Optional[_optimizers.Optimizer] = None
+        self.loss: Optional[_losses.Loss] = None
+        self.compiled_metrics: List[_metrics.Metric] = []
+        self.loss_tracker = _metrics.Mean("loss")
+        self.stop_training = False
+        self.compute_dtype = _policy["compute_dtype"]
+        self._arenas: List[ParamArena] = []
+        self._engine: Any = None
+        self._engine_pref = os.environ.get("TFDL_ENGINE", "auto")
+        self.history: Optional[History] = None
+        self._train_iter: Optional[Iterator[PerReplica]] = None
+        self._steps_done = 0
+        self._input_shape: Optional[Tuple[int, ...]] = None
+
+    # ---- to be provided by subclasses -------------------------------------------------------
+    def _layers(self) -> List[Layer]:
+        raise NotImplementedError
+
+    def _forward(self, x: torch.Tensor, ctx: CallContext) -> torch.Tensor:
+        raise NotImplementedError
+
+    def build(self, input_shape: Sequence[int]) -> None:
+        raise NotImplementedError
+
+    # ---- variables --------------------------------------------------------------------------
+    @property
+    def layers(self) -> List[Layer]:
+        return [l for l in self._layers() if not isinstance(l, InputLayer)]
+
+    @property
+    def weights(self) -> List[MirroredVariable]:
+        return [w for l in self._layers() for w in l.weights]
+
+    variables = weights
+
+    @property
+    def trainable_weights(self) -> List[MirroredVariable]:
+        return [w for w in self.weights if w.trainable]
+
+    trainable_variables = trainable_weights
+
+    def count_params(self) -> int:
+        return sum(int(np.prod(w.shape)) for w in self.weights)
+
+    def get_weights(self) -> List[np.ndarray]:
+        return [w.numpy() for w in self.weights]
+
+    def set_weights(self, ws: Sequence[np.ndarray]) -> None:
+        vs = self.weights
+        if len(ws) != len(vs):
+            raise ValueError(f"expected {len(vs)} weight arrays, got {len(ws)}")
+        for v, a in zip(vs, ws):
+            v.assign(a)
+        self._weights_changed()
+
+    def _weights_changed(self) -> None:
+        if self._engine is not None and hasattr(self._engine, "weights_changed"):
+            self._engine.weights_changed()
+
+    def summary(self, print_fn=print) -> None:
+        print_fn(f'Model: "{self.name}"')
+        print_fn(f"{'Layer (type)':<34}{'Output Shape':<26}{'Param #':>10}")
+        print_fn("=" * 70)
+        for l in self.layers:
+            shp = (None,) + tuple(l.output_shape) if l.output_shape is not None else "?"
+            print_fn(f"{l.name + ' (' + type(l).__name__ + ')':<34}{str(shp):<26}{l.count_params():>10}")
+        print_fn("=" * 70)
+        print_fn(f"Total params: {self.count_params():,}")
+
+    # ---- finalisation: arenas, mirrored copies, chief broadcast ------------------------------
+    def _finalize(self) -> None:
+        """Allocate one flat (params, grads) arena per local replica, bind every variable to its
+        slice, and make all replicas of all workers start from the chief's values (K15)."""
+        if self._arenas:
+            return
+        if not self.built:
+            raise RuntimeError("the model has no input shape yet: pass input_shape= to the first layer, call "
+                               "model.build(input_shape), or call fit() which builds from the data")
+        s = self.strategy
+        specs = [w.spec for w in self.weights]
+        ops = s.cross_device_ops
+        alloc = getattr(ops, "alloc_arena", None)
+        self._arenas = [ParamArena(specs, d, allocator=alloc) for d in s.local_devices]
+        for w in self.weights:
+            w.bind(self._arenas)
+        mask = torch.zeros(self._arenas[0].numel)
+        for sp in specs:
+            if sp.trainable:
+                mask[sp.offset:sp.offset + sp.numel] = 1
+        self._all_trainable = bool(all(sp.trainable for sp in specs))
+        self._masks = [mask.to(a.device) for a in self._arenas]
+        ops.broadcast_params([a.params for a in self._arenas])
+
+    @property
+    def arenas(self) -> List[ParamArena]:
+        self._finalize()
+        return self._arenas
+
+    # ---- compile ----------------------------------------------------------------------------
+    def compile(self, optimizer: Any = "sgd", loss: Any = None, metrics: Optional[Sequence[Any]] = None,
+                **_: Any) -> None:
+        """tf.keras.Model.compile (tf_dist_example.py:49-52). Creates optimizer slots and metric
+        accumulators; call it inside strategy.scope() like the reference does."""
+        scope = get_strategy()
+        if _strat.has_strategy() and scope is not self.strategy:
+            raise RuntimeError("compile() is running under a different strategy scope than the one the model "
+                               "was created in")
+        self.optimizer = _optimizers.get(optimizer)
+        self.loss = _losses.get(loss) if loss is not None else None
+        self.compiled_metrics = [_metrics.get(m, self.loss) for m in (metrics or [])]
+        devs = self.strategy.local_devices
+        self.loss_tracker.bind(devs)
+        for m in self.compiled_metrics:
+            m.bind(devs)
+        self._engine = None
+        if self.built:
+            self._finalize()
+            self.optimizer.bind([a.params for a in self._arenas])
+
+    @property
+    def metrics_names(self) -> List[str]:
+        return ["loss"] + [m.name for m in self.compiled_metrics]
+
+    # ---- engine -----------------------------------------------------------------------------
+    def _make_engine(self) -> Any:
+        if self._engine is not None:
+            return self._engine
+        self._finalize()
+        assert self.optimizer is not None, "call compile() before fit()/evaluate()"
+        if not self.optimizer._slots and self.optimizer.slot_names():
+            self.optimizer.bind([a.params for a in self._arenas])
+        elif not self.optimizer.slot_names():
+            self.optimizer._slots = {}
+        pref = self._engine_pref
+        on_cuda = all(d.type == "cuda" for d in self.strategy.local_devices)
+        engine = None
+        if pref in ("auto", "native") and on_cuda:
+            from . import native_engine
+
+            engine = native_engine.try_build(self)  # raises if the .so is missing on a GPU box
+            if engine is None and pref == "native":
+                raise RuntimeError("TFDL_ENGINE=native but this model/strategy has no native step program")
+        elif pref == "native":
+            raise RuntimeError("TFDL_ENGINE=native needs CUDA replicas")
+        self._engine = engine or TorchEngine(self)
+        return self._engine
+
+    @property
+    def engine_name(self) -> str:
+        return type(self._make_engine()).__name__
+
+    # ---- logs -------------------------------------------------------------------------------
+    def _read_logs(self, prefix: str = "") -> Dict[str, float]:
+        eng = self._engine
+        if eng is not None and hasattr(eng, "flush_metrics"):
+            eng.flush_metrics()
+        trackers = [self.loss_tracker] + self.compiled_metrics
+        local = np.concatenate([t.local_state() for t in trackers])
+        tot = self.strategy.cross_device_ops.allreduce_scalars(local)
+        out = {}
+        for i, t in enumerate(trackers):
+            total, count = tot[2 * i], tot[2 * i + 1]
+            out[prefix + t.name] = float(total / count) if count else 0.0
+        return out
+
+    def reset_metrics(self) -> None:
+        if self._engine is not None and hasattr(self._engine, "flush_metrics"):
+            self._engine.flush_metrics()
+        for t in [self.loss_tracker] + self.compiled_metrics:
+            t.reset_state()
+
+    # ---- fit --------------------------------------------------------------------------------
+    def fit(self, x: Any = None, y: Any = None, batch_size: Optional[int] = None, epochs: int = 1,
+            verbose: Union[int, str] = 1, callbacks: Optional[Sequence[_cb.Callback]] = None,
+            validation_data: Any = None, shuffle: bool = True, initial_epoch: int = 0,
+            steps_per_epoch: Optional[int] = None, validation_steps: Optional[int] = None, **_: Any) -> History:
+        """tf.keras.Model.fit (tf_dist_example.py:59: fit(x=dataset, epochs=10, steps_per_epoch=20)).
+
+        With `steps_per_epoch` the dataset iterator is carried across epochs (the reference has no
+        .repeat(): 200 steps x 64 samples stay below one pass of the data); without it every epoch
+        is one full pass."""
+        if self.optimizer is None or self.loss is None:
+            raise RuntimeError("compile(optimizer=..., loss=...) must be called before fit()")
+        ds = _as_dataset(x, y, batch_size, shuffle=shuffle and not isinstance(x, Dataset))
+        dist = ds if isinstance(x, DistributedDataset) else self.strategy.experimental_distribute_dataset(ds)
+        if not self.built:
+            first = next(iter(dist))
+            xb = first[0][0] if isinstance(first[0], (tuple, list)) else first[0]
+            self.build(tuple(np.asarray(xb).shape[1:]))
+        engine = self._make_engine()
+        history = History()
+        cbs = _cb.CallbackList([history] + list(callbacks or []), model=self, verbose=verbose, epochs=epochs,
+                               steps=steps_per_epoch)
+        self.stop_training = False
+        logs: Dict[str, float] = {}
+        cbs.on_train_begin()
+        initial_epoch = cbs.initial_epoch(initial_epoch)
+        it: Optional[Iterator[PerReplica]] = None
+        for epoch in range(initial_epoch, epochs):
+            self.reset_metrics()
+            cbs.on_epoch_begin(epoch)
+            t0 = time.time()
+            if it is None or steps_per_epoch is None:
+                it = iter(dist)
+            step = 0
+            while steps_per_epoch is None or step < steps_per_epoch:
+                try:
+                    batch = next(it)
+                except StopIteration:
+                    if steps_per_epoch is not None:
+                        if verbose:
+                            print(f"WARNING: input ran out of data after {step} of {steps_per_epoch} steps "
+                                  f"in epoch {epoch + 1}; use .repeat() on the dataset", file=sys.stderr)
+                        self.stop_training = True
+                    break
+                cbs.on_train_batch_begin(step)
+                engine.train_step(batch)
+                self._steps_done += 1
+                cbs.on_train_batch_end(step, None)
+                step += 1
+                if self.stop_training:
+                    break
+            logs = self._read_logs()
+            if validation_data is not None:
+                val = self.evaluate(validation_data, steps=validation_steps, verbose=0, return_dict=True,
+                                    _prefix="val_")
+                logs.update(val)
+            logs["_epoch_time"] = time.time() - t0
+            logs["_steps"] = step
+            cbs.on_epoch_end(epoch, logs)
+            if self.stop_training:
+                break
+        cbs.on_train_end(logs)
+        for k in ("_epoch_time", "_steps"):
+            history.history.pop(k, None)
+        self.history = history
+        return history
+
+    def train_on_batch(self, x: Any, y: Any = None, return_dict: bool = False) -> Any:
+        """One step on one GLOBAL batch given as arrays; the batch is split over local replicas."""
+        engine = self._prepare_for_arrays(x)
+        self.reset_metrics()
+        engine.train_step(self._split_arrays(x, y))
+        self._steps_done += 1
+        logs = self._read_logs()
+        return logs if return_dict else [logs[n] for n in self.metrics_names]
+
+    def _prepare_for_arrays(self, x: Any) -> Any:
+        if not self.built:
+            self.build(tuple(np.asarray(x).shape[1:]))
+        return self._make_engine()
+
+    def _split_arrays(self, x: Any, y: Any) -> PerReplica:
+        n = self.strategy.num_local_replicas
+        xs = np.array_split(np.asarray(x), n)
+        if y is None:
+            return PerReplica([(a,) for a in xs])
+        ys = np.array_split(np.asarray(y), n)
+        return PerReplica(list(zip(xs, ys)))
+
+    # ---- evaluate / predict --------------------------------------------------------------------
+    def evaluate(self, x: Any = None, y: Any = None, batch_size: Optional[int] = None, verbose: Union[int, str] = 0,
+                 steps: Optional[int] = None, return_dict: bool = False, _prefix: str = "", **_: Any) -> Any:
+        ds = _as_dataset(x, y, batch_size)
+        dist = ds if isinstance(x, DistributedDataset) else self.strategy.experimental_distribute_dataset(ds)
+        if not self.built:
+            first = next(iter(dist))
+            self.build(tuple(np.asarray(first[0][0]).shape[1:]))
+        engine = self._make_engine()
+        saved = [(t, [v.clone() for v in t._total], [v.clone() for v in t._count])
+                 for t in [self.loss_tracker] + self.compiled_metrics] if _prefix else []
+        self.reset_metrics()
+        for i, batch in enumerate(dist):
+            if steps is not None and i >= steps:
+                break
+            engine.test_step(batch)
+        logs = self._read_logs(_prefix)
+        for t, tot, cnt in saved:  # restore the training accumulators
+            for dst, src in zip(t._total, tot):
+                dst.copy_(src)
+            for dst, src in zip(t._count, cnt):
+                dst.copy_(src)
+        if verbose:
+            print(" - ".join(f"{k}: {v:.4f}" for k, v in logs.items()))
+        return logs if return_dict else [logs[_prefix + n] for n in self.metrics_names]
+
+    def predict(self, x: Any, batch_size: Optional[int] = None, steps: Optional[int] = None, **_: Any) -> np.ndarray:
+        ds = _as_dataset(x, None, batch_size)
+        if not self.built:
+            first = next(iter(ds))
+            xb = first[0] if isinstance(first, (tuple, list)) else first
+            self.build(tuple(np.asarray(xb).shape[1:]))
+        engine = self._make_engine()
+        outs = []
+        for i, b in enumerate(ds):
+            if steps is not None and i >= steps:
+                break
+            xb = b[0] if isinstance(b, (tuple, list)) else b
+            outs.append(engine.predict_step(np.asarray(xb)))
+        return np.concatenate(outs) if outs else np.zeros((0,))
+
+    def __call__(self, x: Any, training: bool = False) -> torch.Tensor:
+        """Eager forward on replica 0 (torch ops)."""
+        if not self.built:
+            self.build(tuple(np.asarray(x).shape[1:]))
+        self._finalize()
+        dev = self.strategy.local_devices[0]
+        xt = torch.as_tensor(np.asarray(x)).to(dev)
+        ctx = CallContext(0, training, lambda v: v.value(0), self.compute_dtype)
+        with torch.no_grad():
+            return self._forward(xt, ctx)
+
+    # ---- weights IO -----------------------------------------------------------------------------
+    def save_weights(self, filepath: str, overwrite: bool = True, save_format: Optional[str] = None) -> None:
+        """Keras TF-format weights (TensorBundle with object-graph keys) or `.npz`. Under a
+        multi-worker strategy every worker must call this; only the chief writes (README.md:51)."""
+        from ..checkpoint import save_model_weights
+
+        save_model_weights(self, filepath, save_format)
+
+    def load_weights(self, filepath: str) -> None:
+        from ..checkpoint import load_model_weights
+
+        load_model_weights(self, filepath)
+        self._weights_changed()
+
+
+class Sequential(Model):
+    """tf.keras.Sequential (tf_dist_example.py:40-48)."""
+
+    def __init__(self, layers: Optional[Sequence[Layer]] = None, name: Optional[str] = None) -> None:
+        super().__init__(name or "sequential")
+        self._stack: List[Layer] = []
+        for l in layers or []:
+            self.add(l)
+
+    def add(self, layer: Layer) -> None:
+        if self._arenas:
+            raise RuntimeError("cannot add layers after the model's variables have been created")
+        self._stack.append(layer)
+        if self.built:
+            assert self._stack[-2].output_shape is not None
+            layer._maybe_build(self._stack[-2].output_shape)
+        elif self._stack[0].input_shape_arg is not None:
+            self.build(self._stack[0].input_shape_arg)
+
+    def _layers(self) -> List[Layer]:
+        return self._stack
+
+    def build(self, input_shape: Sequence[int]) -> None:
+        shape = tuple(int(s) for s in input_shape)
+        self._input_shape = shape
+        for l in self._stack:
+            shape = l._maybe_build(shape)
+        self.built = True
+
+    @property
+    def input_shape(self) -> Optional[Tuple[Optional[int], ...]]:
+        return (None,) + self._input_shape if self._input_shape else None
+
+    @property
+    def output_shape(self) -> Optional[Tuple[Optional[int], ...]]:
+        return (None,) + tuple(self._stack[-1].output_shape) if self.built else None
+
+    def _forward(self, x: torch.Tensor, ctx: CallContext) -> torch.Tensor:
+        for l in self._stack:
+            x = l.call(x, ctx)
+        return x
+
+
+class TorchEngine:
+    """Portable training engine on torch ops + autograd. Gradients are accumulated straight into the
+    flat gradient arena (each parameter leaf's .grad is a view of it), the strategy's cross-device
+    op reduces the arena in place, and the optimizer updates the parameter arena in one pass."""
+
+    def __init__(self, model: Model) -> None:
+        self.model = model
+        self.strategy = model.strategy
+        self.devices = self.strategy.local_devices
+        self.leaves: List[Dict[int, torch.Tensor]] = []
+        for r, arena in enumerate(model.arenas):
+            d: Dict[int, torch.Tensor] = {}
+            for w in model.weights:
+                leaf = w.value(r).detach()
+                if w.trainable:
+                    leaf.requires_grad_(True)
+                    leaf.grad = w.grad(r)
+                d[id(w)] = leaf
+            self.leaves.append(d)
+
+    def _ctx(self, r: int, training: bool) -> CallContext:
+        leaves = self.leaves[r]
+        return CallContext(r, training, lambda v: leaves[id(v)], self.model.compute_dtype)
+
+    def _to_device(self, a: Any, dev: torch.device) -> torch.Tensor:
+        t = torch.from_numpy(np.ascontiguousarray(a)) if not isinstance(a, torch.Tensor) else a
+        if dev.type == "cuda":
+            return t.pin_memory().to(dev, non_blocking=True) if not t.is_cuda else t
+        return t
+
+    def _split(self, batch: Any) -> Tuple[Any, Any]:
+        if isinstance(batch, (tuple, list)):
+            return batch[0], (batch[1] if len(batch) > 1 else None)
+        return batch, None
+
+    def train_step(self, batches: PerReplica) -> None:
+        m, s = self.model, self.strategy
+        assert m.loss is not None and m.optimizer is not None
+        nrep = s.num_replicas_in_sync
+        for r, dev in enumerate(self.devices):
+            arena = m.arenas[r]
+            arena.grads.zero_()
+            x, y = self._split(batches[r])
+            n = int(np.asarray(x).shape[0]) if not isinstance(x, torch.Tensor) else x.shape[0]
+            if n == 0:
+                continue
+            xt, yt = self._to_device(x, dev), self._to_device(y, dev)
+            pred = m._forward(xt, self._ctx(r, True))
+            per = m.loss.per_example(yt, pred)
+            (per.mean() / nrep).backward()
+            m.loss_tracker.add(r, per.detach().sum(), float(per.numel()))
+            with torch.no_grad():
+                for met in m.compiled_metrics:
+                    met.update_state(yt, pred.detach(), r)
+        s.cross_device_ops.allreduce_grads([a.grads for a in m.arenas])
+        with torch.no_grad():
+            for r, arena in enumerate(m.arenas):
+                m.optimizer.apply_flat(arena.params, arena.grads, r, None if m._all_trainable else m._masks[r])
+        m.optimizer.step_done()
+
+    def test_step(self, batches: PerReplica) -> None:
+        m = self.model
+        assert m.loss is not None
+        with torch.no_grad():
+            for r, dev in enumerate(self.devices):
+                x, y = self._split(batches[r])
+                if np.asarray(x).shape[0] == 0:
+                    continue
+                xt, yt = self._to_device(x, dev), self._to_device(y, dev)
+                pred = m._forward(xt, self._ctx(r, False))
+                per = m.loss.per_example(yt, pred)
+                m.loss_tracker.add(r, per.sum(), float(per.numel()))
+                for met in m.compiled_metrics:
+                    met.update_state(yt, pred, r)
+
+    def predict_step(self, x: np.ndarray) -> np.ndarray:
+        with torch.no_grad():
+            xt = self._to_device(x, self.devices[0])
+            return self.model._forward(xt, self._ctx(0, False)).float().cpu().numpy()

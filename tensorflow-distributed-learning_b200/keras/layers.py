@@ -1,0 +1,426 @@
+"""Keras-style layers (ref: /root/reference/tf_dist_example.py:40-48).
+
+Shapes follow Keras: activations are NHWC, Conv2D kernels report HWIO, Dense kernels (in, out),
+Flatten orders features (h, w, c). *Storage* differs (see parallel/values.py): conv kernels are held
+OHWI and dense kernels [out, in] so that the forward GEMM operands are K-major for tcgen05 and so
+that torch's channels_last conv can use them without a copy; `get_weights()` / checkpoints convert
+back to the Keras layout.
+
+`call()` here is the portable torch implementation (CPU tests, stand-in baseline, layers that have no
+native kernel yet). On a B200 the supported stacks are executed by the native step program instead
+(keras/native_engine.py), which never calls these functions.
+"""
+from __future__ import annotations
+
+import math
+from typing import Any, Callable, Dict, List, Optional, Sequence, Tuple, Union
+
+import numpy as np
+import torch
+import torch.nn.functional as F
+
+from ..parallel.values import MirroredVariable, VarSpec
+
+_uids: Dict[str, int] = {}
+
+
+def _unique_name(prefix: str) -> str:
+    n = _uids.get(prefix, 0)
+    _uids[prefix] = n + 1
+    return prefix if n == 0 else f"{prefix}_{n}"
+
+
+def clear_session() -> None:
+    """keras.backend.clear_session(): restart the auto-naming counters."""
+    _uids.clear()
+
+
+def _pair(v: Union[int, Sequence[int]]) -> Tuple[int, int]:
+    return (int(v), int(v)) if isinstance(v, int) else (int(v[0]), int(v[1]))
+
+
+# ---- initialisers -------------------------------------------------------------------------------
+
+_init_rng = np.random.default_rng()
+
+
+def set_init_seed(seed: Optional[int]) -> None:
+    global _init_rng
+    _init_rng = np.random.default_rng(seed)
+
+
+def glorot_uniform(shape: Tuple[int, ...]) -> np.ndarray:
+    """Keras default kernel initialiser. fans for a conv kernel HWIO: in = h*w*i, out = h*w*o."""
+    if len(shape) == 2:
+        fan_in, fan_out = shape
+    else:
+        rf = int(np.prod(shape[:-2]))
+        fan_in, fan_out = shape[-2] * rf, shape[-1] * rf
+    lim = math.sqrt(6.0 / (fan_in + fan_out))
+    return _init_rng.uniform(-lim, lim, size=shape).astype(np.float32)
+
+
+def he_normal(shape: Tuple[int, ...]) -> np.ndarray:
+    rf = int(np.prod(shape[:-2])) if len(shape) > 2 else 1
+    fan_in = shape[-2] * rf if len(shape) >= 2 else shape[0]
+    return (_init_rng.standard_normal(size=shape) * math.sqrt(2.0 / fan_in)).astype(np.float32)
+
+
+def truncated_normal(stddev: float = 0.02) -> Callable[[Tuple[int, ...]], np.ndarray]:
+    def init(shape: Tuple[int, ...]) -> np.ndarray:
+        a = _init_rng.standard_normal(size=shape)
+        bad = np.abs(a) > 2
+        while bad.any():
+            a[bad] = _init_rng.standard_normal(size=int(bad.sum()))
+            bad = np.abs(a) > 2
+        return (a * stddev).astype(np.float32)
+
+    return init
+
+
+def zeros(shape: Tuple[int, ...]) -> np.ndarray:
+    return np.zeros(shape, np.float32)
+
+
+def ones(shape: Tuple[int, ...]) -> np.ndarray:
+    return np.ones(shape, np.float32)
+
+
+_INITS = {"glorot_uniform": glorot_uniform, "he_normal": he_normal, "zeros": zeros, "ones": ones}
+
+
+def get_initializer(x: Union[str, Callable]) -> Callable[[Tuple[int, ...]], np.ndarray]:
+    return _INITS[x] if isinstance(x, str) else x
+
+
+# ---- activations --------------------------------------------------------------------------------
+
+def _gelu_tanh(x: torch.Tensor) -> torch.Tensor:
+    return F.gelu(x, approximate="tanh")
+
+
+_ACTS: Dict[Optional[str], Optional[Callable[[torch.Tensor], torch.Tensor]]] = {
+    None: None, "linear": None, "relu": torch.relu, "gelu": _gelu_tanh, "tanh": torch.tanh,
+    "sigmoid": torch.sigmoid, "softmax": lambda x: torch.softmax(x, dim=-1),
+}
+
+
+class CallContext:
+    """Per-call state handed to layers: which replica, training or not, and how to fetch the
+    autograd leaf that aliases a variable in that replica's arena."""
+
+    def __init__(self, replica: int, training: bool, param: Callable[[MirroredVariable], torch.Tensor],
+                 compute_dtype: torch.dtype = torch.float32) -> None:
+        self.replica, self.training, self.param, self.compute_dtype = replica, training, param, compute_dtype
+
+
+class Layer:
+    """Base layer: lazily built from the input shape (excluding the batch dimension)."""
+
+    def __init__(self, name: Optional[str] = None, input_shape: Optional[Sequence[int]] = None,
+                 trainable: bool = True, **kw: Any) -> None:
+        cls = type(self).__name__
+        snake = "".join("_" + c.lower() if c.isupper() and i and not cls[i - 1].isdigit() and not cls[i - 1].isupper()
+                        else c.lower() for i, c in enumerate(cls))
+        self.name = name or _unique_name(snake)
+        self.trainable = trainable
+        self.built = False
+        self.input_shape_arg = tuple(input_shape) if input_shape is not None else None
+        self.input_shape: Optional[Tuple[int, ...]] = None
+        self.output_shape: Optional[Tuple[int, ...]] = None
+        self._weights: List[MirroredVariable] = []
+
+    # -- weights ------------------------------------------------------------------------------
+    def add_weight(self, name: str, shape: Sequence[int], initializer: Union[str, Callable] = "glorot_uniform",
+                   trainable: bool = True, to_storage: Optional[Tuple[int, ...]] = None) -> MirroredVariable:
+        shape = tuple(int(s) for s in shape)
+        st_shape = shape if to_storage is None else tuple(shape[p] for p in to_storage)
+        spec = VarSpec(f"{self.name}/{name}:0", shape, st_shape, to_storage, trainable=trainable and self.trainable)
+        v = MirroredVariable(spec, get_initializer(initializer)(shape))
+        self._weights.append(v)
+        return v
+
+    @property
+    def weights(self) -> List[MirroredVariable]:
+        return list(self._weights)
+
+    @property
+    def trainable_weights(self) -> List[MirroredVariable]:
+        return [w for w in self._weights if w.trainable]
+
+    def count_params(self) -> int:
+        return sum(int(np.prod(w.shape)) for w in self._weights)
+
+    def get_weights(self) -> List[np.ndarray]:
+        return [w.numpy() for w in self._weights]
+
+    def set_weights(self, ws: Sequence[np.ndarray]) -> None:
+        if len(ws) != len(self._weights):
+            raise ValueError(f"{self.name}: expected {len(self._weights)} arrays, got {len(ws)}")
+        for w, a in zip(self._weights, ws):
+            w.assign(a)
+
+    # -- build / call -------------------------------------------------------------------------
+    def build(self, input_shape: Tuple[int, ...]) -> None:
+        pass
+
+    def compute_output_shape(self, input_shape: Tuple[int, ...]) -> Tuple[int, ...]:
+        return input_shape
+
+    def _maybe_build(self, input_shape: Tuple[int, ...]) -> Tuple[int, ...]:
+        input_shape = tuple(int(s) for s in input_shape)
+        if not self.built:
+            self.input_shape = input_shape
+            self.build(input_shape)
+            self.output_shape = self.compute_output_shape(input_shape)
+            self.built = True
+        elif self.input_shape != input_shape:
+            raise ValueError(f"{self.name} was built for input shape {self.input_shape}, got {input_shape}")
+        assert self.output_shape is not None
+        return self.output_shape
+
+    def call(self, x: torch.Tensor, ctx: CallContext) -> torch.Tensor:
+        return x
+
+    def get_config(self) -> Dict[str, Any]:
+        return {"name": self.name}
+
+    def __repr__(self) -> str:
+        return f"<{type(self).__name__} {self.name}>"
+
+
+class InputLayer(Layer):
+    def __init__(self, input_shape: Sequence[int], **kw: Any) -> None:
+        super().__init__(input_shape=input_shape, **kw)
+
+
+class Conv2D(Layer):
+    """tf.keras.layers.Conv2D (tf_dist_example.py:41,43): NHWC, kernel HWIO, stride 1 / 'valid' by default."""
+
+    def __init__(self, filters: int, kernel_size: Union[int, Sequence[int]], strides: Union[int, Sequence[int]] = 1,
+                 padding: str = "valid", activation: Optional[str] = None, use_bias: bool = True,
+                 kernel_initializer: Union[str, Callable] = "glorot_uniform",
+                 bias_initializer: Union[str, Callable] = "zeros", **kw: Any) -> None:
+        super().__init__(**kw)
+        self.filters, self.kernel_size, self.strides = int(filters), _pair(kernel_size), _pair(strides)
+        self.padding = padding.lower()
+        if self.padding not in ("valid", "same"):
+            raise ValueError("padding must be 'valid' or 'same'")
+        if activation not in _ACTS:
+            raise ValueError(f"unknown activation {activation!r}")
+        self.activation, self.use_bias = activation, use_bias
+        self._kinit, self._binit = kernel_initializer, bias_initializer
+        self.kernel: Optional[MirroredVariable] = None
+        self.bias: Optional[MirroredVariable] = None
+
+    def build(self, input_shape: Tuple[int, ...]) -> None:
+        if len(input_shape) != 3:
+            raise ValueError(f"{self.name}: Conv2D expects (H, W, C) inputs, got {input_shape}")
+        kh, kw = self.kernel_size
+        # Keras HWIO -> storage OHWI
+        self.kernel = self.add_weight("kernel", (kh, kw, input_shape[2], self.filters), self._kinit,
+                                      to_storage=(3, 0, 1, 2))
+        if self.use_bias:
+            self.bias = self.add_weight("bias", (self.filters,), self._binit)
+
+    def _pads(self, size: int, k: int, s: int) -> Tuple[int, int]:
+        if self.padding == "valid":
+            return 0, 0
+        out = -(-size // s)
+        tot = max((out - 1) * s + k - size, 0)
+        return tot // 2, tot - tot // 2
+
+    def compute_output_shape(self, input_shape: Tuple[int, ...]) -> Tuple[int, ...]:
+        h, w, _ = input_shape
+        (kh, kw), (sh, sw) = self.kernel_size, self.strides
+        if self.padding == "valid":
+            return ((h - kh) // sh + 1, (w - kw) // sw + 1, self.filters)
+        return (-(-h // sh), -(-w // sw), self.filters)
+
+    def call(self, x: torch.Tensor, ctx: CallContext) -> torch.Tensor:
+        assert self.kernel is not None
+        w = ctx.param(self.kernel).permute(0, 3, 1, 2)  # OHWI storage viewed as OIHW (channels_last strides)
+        b = ctx.param(self.bias) if self.bias is not None else None
+        xin = x.permute(0, 3, 1, 2)
+        if self.padding == "same":
+            pt, pb = self._pads(x.shape[1], self.kernel_size[0], self.strides[0])
+            pl, pr = self._pads(x.shape[2], self.kernel_size[1], self.strides[1])
+            if pt or pb or pl or pr:
+                xin = F.pad(xin, (pl, pr, pt, pb))
+        if ctx.compute_dtype != torch.float32:
+            xin, w = xin.to(ctx.compute_dtype), w.to(ctx.compute_dtype)
+            b = b.to(ctx.compute_dtype) if b is not None else None
+        y = F.conv2d(xin, w, b, stride=self.strides).permute(0, 2, 3, 1)
+        act = _ACTS[self.activation]
+        return act(y) if act else y
+
+
+class MaxPooling2D(Layer):
+    """tf.keras.layers.MaxPooling2D (tf_dist_example.py:42,44): 2x2, stride 2, 'valid' by default."""
+
+    def __init__(self, pool_size: Union[int, Sequence[int]] = 2, strides: Union[None, int, Sequence[int]] = None,
+                 padding: str = "valid", **kw: Any) -> None:
+        super().__init__(**kw)
+        self.pool_size = _pair(pool_size)
+        self.strides = _pair(strides) if strides is not None else self.pool_size
+        self.padding = padding.lower()
+
+    def compute_output_shape(self, input_shape: Tuple[int, ...]) -> Tuple[int, ...]:
+        h, w, c = input_shape
+        if self.padding == "same":
+            return (-(-h // self.strides[0]), -(-w // self.strides[1]), c)
+        return ((h - self.pool_size[0]) // self.strides[0] + 1, (w - self.pool_size[1]) // self.strides[1] + 1, c)
+
+    def call(self, x: torch.Tensor, ctx: CallContext) -> torch.Tensor:
+        xin = x.permute(0, 3, 1, 2)
+        if self.padding == "same":
+            oh, ow, _ = self.compute_output_shape(tuple(x.shape[1:]))
+            ph = max((oh - 1) * self.strides[0] + self.pool_size[0] - x.shape[1], 0)
+            pw = max((ow - 1) * self.strides[1] + self.pool_size[1] - x.shape[2], 0)
+            xin = F.pad(xin, (pw // 2, pw - pw // 2, ph // 2, ph - ph // 2), value=float("-inf"))
+        return F.max_pool2d(xin, self.pool_size, self.strides).permute(0, 2, 3, 1)
+
+
+class AveragePooling2D(MaxPooling2D):
+    def call(self, x: torch.Tensor, ctx: CallContext) -> torch.Tensor:
+        return F.avg_pool2d(x.permute(0, 3, 1, 2), self.pool_size, self.strides).permute(0, 2, 3, 1)
+
+
+class GlobalAveragePooling2D(Layer):
+    def compute_output_shape(self, input_shape: Tuple[int, ...]) -> Tuple[int, ...]:
+        return (input_shape[2],)
+
+    def call(self, x: torch.Tensor, ctx: CallContext) -> torch.Tensor:
+        return x.mean(dim=(1, 2))
+
+
+class Flatten(Layer):
+    """tf.keras.layers.Flatten (tf_dist_example.py:45): NHWC order (h, w, c)."""
+
+    def compute_output_shape(self, input_shape: Tuple[int, ...]) -> Tuple[int, ...]:
+        return (int(np.prod(input_shape)),)
+
+    def call(self, x: torch.Tensor, ctx: CallContext) -> torch.Tensor:
+        return x.reshape(x.shape[0], -1)
+
+
+class Dense(Layer):
+    """tf.keras.layers.Dense (tf_dist_example.py:46-47): kernel (in, out) in Keras layout."""
+
+    def __init__(self, units: int, activation: Optional[str] = None, use_bias: bool = True,
+                 kernel_initializer: Union[str, Callable] = "glorot_uniform",
+                 bias_initializer: Union[str, Callable] = "zeros", **kw: Any) -> None:
+        super().__init__(**kw)
+        if activation not in _ACTS:
+            raise ValueError(f"unknown activation {activation!r}")
+        self.units, self.activation, self.use_bias = int(units), activation, use_bias
+        self._kinit, self._binit = kernel_initializer, bias_initializer
+        self.kernel: Optional[MirroredVariable] = None
+        self.bias: Optional[MirroredVariable] = None
+
+    def build(self, input_shape: Tuple[int, ...]) -> None:
+        self.kernel = self.add_weight("kernel", (input_shape[-1], self.units), self._kinit, to_storage=(1, 0))
+        if self.use_bias:
+            self.bias = self.add_weight("bias", (self.units,), self._binit)
+
+    def compute_output_shape(self, input_shape: Tuple[int, ...]) -> Tuple[int, ...]:
+        return tuple(input_shape[:-1]) + (self.units,)
+
+    def call(self, x: torch.Tensor, ctx: CallContext) -> torch.Tensor:
+        assert self.kernel is not None
+        w = ctx.param(self.kernel)
+        b = ctx.param(self.bias) if self.bias is not None else None
+        if ctx.compute_dtype != torch.float32:
+            x, w = x.to(ctx.compute_dtype), w.to(ctx.compute_dtype)
+            b = b.to(ctx.compute_dtype) if b is not None else None
+        y = F.linear(x, w, b)
+        act = _ACTS[self.activation]
+        return act(y) if act else y
+
+
+class Activation(Layer):
+    def __init__(self, activation: str, **kw: Any) -> None:
+        super().__init__(**kw)
+        if activation not in _ACTS:
+            raise ValueError(f"unknown activation {activation!r}")
+        self.activation = activation
+
+    def call(self, x: torch.Tensor, ctx: CallContext) -> torch.Tensor:
+        act = _ACTS[self.activation]
+        return act(x) if act else x
+
+
+class ReLU(Activation):
+    def __init__(self, **kw: Any) -> None:
+        super().__init__("relu", **kw)
+
+
+class Dropout(Layer):
+    def __init__(self, rate: float, **kw: Any) -> None:
+        super().__init__(**kw)
+        self.rate = float(rate)
+
+    def call(self, x: torch.Tensor, ctx: CallContext) -> torch.Tensor:
+        return F.dropout(x, self.rate, training=ctx.training)
+
+
+class BatchNormalization(Layer):
+    """Per-replica batch statistics (Keras default under MirroredStrategy: not synchronised).
+    gamma/beta are mirrored trainable variables; moving statistics are non-trainable."""
+
+    def __init__(self, momentum: float = 0.99, epsilon: float = 1e-3, **kw: Any) -> None:
+        super().__init__(**kw)
+        self.momentum, self.epsilon = momentum, epsilon
+
+    def build(self, input_shape: Tuple[int, ...]) -> None:
+        c = input_shape[-1]
+        self.gamma = self.add_weight("gamma", (c,), "ones")
+        self.beta = self.add_weight("beta", (c,), "zeros")
+        self.moving_mean = self.add_weight("moving_mean", (c,), "zeros", trainable=False)
+        self.moving_variance = self.add_weight("moving_variance", (c,), "ones", trainable=False)
+
+    def call(self, x: torch.Tensor, ctx: CallContext) -> torch.Tensor:
+        g, b = ctx.param(self.gamma), ctx.param(self.beta)
+        mm, mv = ctx.param(self.moving_mean), ctx.param(self.moving_variance)
+        dims = tuple(range(x.dim() - 1))
+        xf = x.float()
+        if ctx.training:
+            mean, var = xf.mean(dims), xf.var(dims, unbiased=False)
+            with torch.no_grad():
+                mm.mul_(self.momentum).add_(mean.detach(), alpha=1 - self.momentum)
+                mv.mul_(self.momentum).add_(var.detach(), alpha=1 - self.momentum)
+        else:
+            mean, var = mm, mv
+        y = (xf - mean) * torch.rsqrt(var + self.epsilon) * g + b
+        return y.to(x.dtype)
+
+
+class LayerNormalization(Layer):
+    def __init__(self, epsilon: float = 1e-12, **kw: Any) -> None:
+        super().__init__(**kw)
+        self.epsilon = epsilon
+
+    def build(self, input_shape: Tuple[int, ...]) -> None:
+        self.gamma = self.add_weight("gamma", (input_shape[-1],), "ones")
+        self.beta = self.add_weight("beta", (input_shape[-1],), "zeros")
+
+    def call(self, x: torch.Tensor, ctx: CallContext) -> torch.Tensor:
+        return F.layer_norm(x.float(), (x.shape[-1],), ctx.param(self.gamma), ctx.param(self.beta),
+                            self.epsilon).to(x.dtype)
+
+
+class Embedding(Layer):
+    def __init__(self, input_dim: int, output_dim: int, embeddings_initializer: Union[str, Callable] = None,
+                 **kw: Any) -> None:
+        super().__init__(**kw)
+        self.input_dim, self.output_dim = int(input_dim), int(output_dim)
+        self._init = embeddings_initializer or truncated_normal(0.02)
+
+    def build(self, input_shape: Tuple[int, ...]) -> None:
+        self.embeddings = self.add_weight("embeddings", (self.input_dim, self.output_dim), self._init)
+
+    def compute_output_shape(self, input_shape: Tuple[int, ...]) -> Tuple[int, ...]:
+        return tuple(input_shape) + (self.output_dim,)
+
+    def call(self, x: torch.Tensor, ctx: CallContext) -> torch.Tensor:
+        return F.embedding(x.long(), ctx.param(self.embeddings))

@@ -1,0 +1,132 @@
+"""Host runtime (libtfdl_runtime.so): crc32c, shuffle buffer, TCP group, ring all-reduce, failure detection."""
+import os
+import time
+
+import numpy as np
+import pytest
+
+from _mp import run_workers
+
+native = pytest.importorskip("tfdl.runtime.native")
+if not native.available():  # pragma: no cover
+    pytest.skip("runtime library not built", allow_module_level=True)
+
+
+def test_crc32c_known_vectors():
+    assert native.crc32c(b"123456789") == 0xE3069283
+    assert native.crc32c(b"") == 0
+    assert native.crc32c(bytes(32)) == 0x8A9136AA
+    # extend == one shot
+    assert native.crc32c(b"6789", native.crc32c(b"12345")) == 0xE3069283
+    from tensorboard.compat.tensorflow_stub.pywrap_tensorflow import masked_crc32c as tb_masked
+
+    for blob in (b"hello", os.urandom(1000)):
+        assert native.masked_crc32c(blob) == tb_masked(blob)
+
+
+def test_shuffle_indices_is_permutation_with_buffer_locality():
+    src = np.arange(5000, dtype=np.int64)
+    out = native.shuffle_indices(src, 100, seed=7)
+    assert sorted(out.tolist()) == src.tolist()
+    # element emitted at position t can only come from the first t + buffer stream elements
+    assert np.all(out[:4900] < np.arange(4900) + 100 + 1)
+    assert not np.array_equal(out, src)
+    assert np.array_equal(out, native.shuffle_indices(src, 100, seed=7))
+    assert not np.array_equal(out, native.shuffle_indices(src, 100, seed=8))
+    full = native.shuffle_indices(src, 10000, seed=1)
+    assert sorted(full.tolist()) == src.tolist()
+
+
+def test_gather_rows_and_fused_scale():
+    rng = np.random.default_rng(0)
+    x = rng.integers(0, 255, size=(1000, 28, 28, 1), dtype=np.uint8)
+    idx = rng.integers(0, 1000, size=300)
+    np.testing.assert_array_equal(native.gather_rows(x, idx), x[idx])
+    out = np.empty((300, 28, 28, 1), np.float32)
+    native.gather_rows_u8_to_f32(x, idx, 1 / 255.0, out.ctypes.data)
+    np.testing.assert_allclose(out, x[idx].astype(np.float32) / 255, rtol=1e-6)
+    with pytest.raises(Exception):
+        native.gather_rows(x, np.array([1000]))
+
+
+def _w_collectives(rank, addrs, n):
+    from tfdl.runtime import native as nat
+
+    g = nat.Group(rank, addrs, timeout_s=30)
+    g.barrier()
+    got = g.allgather_bytes(bytes([rank]) * 4)
+    objs = g.allgather_object({"rank": rank, "pad": "x" * rank})
+    a = np.arange(n, dtype=np.float32) * (rank + 1)
+    g.allreduce_(a)
+    d = np.full(3, rank + 0.5, dtype=np.float64)
+    g.allreduce_(d)
+    b = np.full(1000, float(rank), dtype=np.float32)
+    g.broadcast_array(b)
+    g.barrier()
+    g.close()
+    return got, [o["rank"] for o in objs], a, d, b
+
+
+@pytest.mark.parametrize("world,n", [(2, 225034), (3, 1001), (4, 7)])
+def test_group_collectives(world, n):
+    res = run_workers(_w_collectives, world, args=(n,))
+    assert all(v[0] == "ok" for v in res.values()), res
+    tot = sum(r + 1 for r in range(world))
+    for r in range(world):
+        got, ranks, a, d, b = res[r][1]
+        assert got == [bytes([k]) * 4 for k in range(world)]
+        assert ranks == list(range(world))
+        np.testing.assert_allclose(a, np.arange(n, dtype=np.float32) * tot, rtol=1e-6)
+        np.testing.assert_allclose(d, sum(k + 0.5 for k in range(world)))
+        assert np.all(b == 0.0)
+    # bitwise identical on every rank
+    for r in range(1, world):
+        assert np.array_equal(res[0][1][2], res[r][1][2])
+
+
+def _w_mismatch(rank, addrs):
+    from tfdl.runtime import native as nat
+
+    use = addrs if rank == 0 else addrs + ["127.0.0.1:1"]
+    try:
+        nat.Group(rank, use, timeout_s=3)
+    except nat.CollectiveError as e:
+        return str(e)
+    return "no error"
+
+
+def test_rendezvous_timeout_and_cluster_mismatch():
+    t0 = time.time()
+    with pytest.raises(native.CollectiveError, match="could not reach rank"):
+        native.Group(0, ["127.0.0.1:1", "127.0.0.1:9"], timeout_s=0.5)
+    assert time.time() - t0 < 10
+    res = run_workers(_w_mismatch, 2)
+    assert any("identical on every node" in v[1] or "could not reach" in v[1] or "timed out" in v[1]
+               for v in res.values()), res
+
+
+def _w_kill(rank, addrs):
+    from tfdl.runtime import native as nat
+
+    g = nat.Group(rank, addrs, timeout_s=20, hb_interval_s=0.05, hb_timeout_s=1.0)
+    g.barrier()
+    if rank == 1:
+        os._exit(17)  # die mid-run without saying goodbye
+    a = np.ones(1 << 20, dtype=np.float32)
+    t0 = time.time()
+    try:
+        for _ in range(50):
+            g.allreduce_(a)
+    except nat.CollectiveError as e:
+        return str(e), time.time() - t0, g.failed_rank
+    return "no error", time.time() - t0, g.failed_rank
+
+
+def test_killed_worker_is_reported_not_hung():
+    res = run_workers(_w_kill, 3, timeout=60, expect_fail=(1,))
+    for r in (0, 2):
+        status, (msg, dt, failed) = res[r]
+        assert status == "ok"
+        assert "rank" in msg and msg != "no error", msg
+        assert dt < 15
+        assert failed in (1,), (r, failed, msg)
