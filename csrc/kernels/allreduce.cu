@@ -1,0 +1,330 @@
+// Fused gradient all-reduce + optimizer update over NVLink peer memory.
+//
+// This replaces the reference's per-step gradient aggregation - `CollectiveAllReduce` /
+// `NcclAllReduce` followed by one `ResourceApplyGradientDescent` per variable
+// (/root/reference/README.md:17,21,23,67; tf_dist_example.py:51,59) - with ONE kernel per step that
+//   * waits until every peer's backward pass has finished (flag barrier over NVLink),
+//   * sums the peers' gradient arenas by loading them directly from peer memory,
+//   * applies the 1/N scale and the SGD / momentum / Nesterov update to the fp32 master weights,
+//   * refreshes the bf16 shadow copy of the weights that the tcgen05 kernels consume,
+//   * clears the gradient buffer of the *other* parity for the next step,
+// so no NCCL call, no pack/unpack copy and no separate optimizer launch is on the step path.
+//
+// Three data paths, chosen per message size by ops/allreduce.py (the reference's `AUTO`):
+//   one-shot   every rank reads all W arenas and updates its own full copy        (latency-optimal)
+//   two-shot   rank r reduces slice r, updates it, and stores the new weights
+//              into every rank's arena (reduce-scatter + all-gather by peer stores) (bandwidth-optimal)
+//   multimem   as two-shot, but the slice is reduced inside the NVSwitch with
+//              multimem.ld_reduce and broadcast with multimem.st                    (NVLS)
+//
+// Synchronisation protocol (all variants):
+//   * `epoch` is a device-local step counter. Step e (1-based) uses gradient buffer parity
+//     (e-1)&1; backward kernels read the same counter to pick the buffer they write.
+//   * start barrier: block b of rank r writes e into slot [b][r] of every peer's flag pad
+//     (st.release.sys) and spins until its own pad holds >= e in slots [b][*] (ld.acquire.sys).
+//     A peer's flag can only arrive after that peer's stream reached this kernel, i.e. after its
+//     backward for step e is complete and its step e-1 reads are over. That is why gradient
+//     buffers are double-buffered by parity instead of guarded by a second barrier: the buffer a
+//     fast rank starts overwriting in step e+1 is never the one a slow rank still reads in step e.
+//   * end barrier (two-shot / multimem only): same exchange on a second pad after the peer stores,
+//     so the kernel does not retire before every peer's slice has landed in this rank's arena.
+//   * every spin is bounded (trap after TFDL_SPIN_LIMIT polls) and polls a host-visible abort word.
+// All ranks compute bit-identical weights: one-shot sums in rank order on every rank; in the
+// sliced variants only the slice owner computes.
+#include "common.cuh"
+#include "../../include/tfdl_kernels.h"
+
+namespace tfdl {
+
+__device__ __forceinline__ bool spin_until_ge(const uint32_t* flag, uint32_t want, const uint32_t* abort_word) {
+  uint32_t spins = 0;
+  while (ld_acquire_sys(flag) < want) {
+    if ((++spins & 0x3FF) == 0) {
+      if (abort_word && ld_relaxed_sys(abort_word) != 0) return false;
+      if (spins > TFDL_SPIN_LIMIT) __trap();
+    }
+  }
+  return true;
+}
+
+// Cross-rank barrier for block `b`: returns false if aborted.
+__device__ __forceinline__ bool block_barrier(const TfdlFusedArParams& p, uint32_t pad_off, uint32_t value) {
+  const int W = p.world;
+  const uint32_t slot_base = pad_off + blockIdx.x * W;
+  __shared__ int ok;
+  if (threadIdx.x == 0) ok = 1;
+  __syncthreads();  // all prior global writes of this block are ordered before the release below
+  if ((int)threadIdx.x < W && (int)threadIdx.x != p.rank) {
+    __threadfence_system();
+    st_release_sys(p.flags[threadIdx.x] + slot_base + p.rank, value);
+    if (!spin_until_ge(p.flags[p.rank] + slot_base + threadIdx.x, value, p.abort_word)) ok = 0;
+  }
+  __syncthreads();
+  return ok != 0;
+}
+
+__device__ __forceinline__ float4 sgd_update(float4 w, float4 g, float4* v, const TfdlHyper& h) {
+  if (h.momentum == 0.f) {
+    w.x -= h.lr * g.x; w.y -= h.lr * g.y; w.z -= h.lr * g.z; w.w -= h.lr * g.w;
+    return w;
+  }
+  float4 m = *v;
+  m.x = h.momentum * m.x - h.lr * g.x; m.y = h.momentum * m.y - h.lr * g.y;
+  m.z = h.momentum * m.z - h.lr * g.z; m.w = h.momentum * m.w - h.lr * g.w;
+  *v = m;
+  if (h.nesterov != 0.f) {
+    w.x += h.momentum * m.x - h.lr * g.x; w.y += h.momentum * m.y - h.lr * g.y;
+    w.z += h.momentum * m.z - h.lr * g.z; w.w += h.momentum * m.w - h.lr * g.w;
+  } else {
+    w.x += m.x; w.y += m.y; w.z += m.z; w.w += m.w;
+  }
+  return w;
+}
+
+__device__ __forceinline__ uint2 to_bf16x4(float4 w) {
+  return make_uint2(pack_bf16x2(w.x, w.y), pack_bf16x2(w.z, w.w));
+}
+
+__device__ __forceinline__ void finish_step(const TfdlFusedArParams& p, uint32_t e) {
+  // last block to leave publishes the new epoch for the next step's kernels
+  __syncthreads();
+  if (threadIdx.x == 0) {
+    __threadfence();
+    uint32_t t = atomicAdd(p.done, 1u);
+    if (t == gridDim.x - 1) {
+      *p.done = 0;
+      __threadfence();
+      *p.epoch = e;
+    }
+  }
+}
+
+// -------------------------------------------------------------------------------------------
+// one-shot
+// -------------------------------------------------------------------------------------------
+__global__ void __launch_bounds__(512) fused_ar_oneshot_kernel(TfdlFusedArParams p) {
+  const uint32_t e = *p.epoch + 1;
+  const int par = p.parity >= 0 ? p.parity : (int)((e - 1) & 1);
+  const TfdlHyper h = *p.hyper;
+  if (p.world > 1 && !block_barrier(p, 0, e)) return;
+  const int64_t n4 = p.n >> 2;
+  const int W = p.world;
+  float4* w4 = reinterpret_cast<float4*>(p.params[p.rank]);
+  float4* v4 = reinterpret_cast<float4*>(p.mom);
+  uint2* s2 = reinterpret_cast<uint2*>(p.shadow[p.rank]);
+  float4* z4 = reinterpret_cast<float4*>(p.grads[par ^ 1][p.rank]);
+  for (int64_t i = (int64_t)blockIdx.x * blockDim.x + threadIdx.x; i < n4; i += (int64_t)gridDim.x * blockDim.x) {
+    float4 g = make_float4(0.f, 0.f, 0.f, 0.f);
+#pragma unroll 1
+    for (int r = 0; r < W; ++r) {
+      const float4* src = reinterpret_cast<const float4*>(p.grads[par][r]) + i;
+      float4 x = (r == p.rank) ? *src : ld_peer_f4(src);
+      g.x += x.x; g.y += x.y; g.z += x.z; g.w += x.w;
+    }
+    g.x *= h.scale; g.y *= h.scale; g.z *= h.scale; g.w *= h.scale;
+    float4 w = sgd_update(w4[i], g, v4 ? v4 + i : nullptr, h);
+    w4[i] = w;
+    if (s2) s2[i] = to_bf16x4(w);
+    if (z4) z4[i] = make_float4(0.f, 0.f, 0.f, 0.f);
+  }
+  finish_step(p, e);
+}
+
+// -------------------------------------------------------------------------------------------
+// two-shot (MC = false) and multimem / NVLS (MC = true)
+// -------------------------------------------------------------------------------------------
+template <bool MC>
+__global__ void __launch_bounds__(512) fused_ar_sliced_kernel(TfdlFusedArParams p) {
+  const uint32_t e = *p.epoch + 1;
+  const int par = p.parity >= 0 ? p.parity : (int)((e - 1) & 1);
+  const TfdlHyper h = *p.hyper;
+  const int W = p.world;
+  if (!block_barrier(p, 0, e)) return;
+  const int64_t n4 = p.n >> 2;
+  const int64_t per = (n4 + W - 1) / W;
+  const int64_t lo = per * p.rank, hi = min(n4, lo + per);
+  float4* v4 = reinterpret_cast<float4*>(p.mom);
+  const float4* w_own = reinterpret_cast<const float4*>(p.params[p.rank]);
+  for (int64_t i = lo + (int64_t)blockIdx.x * blockDim.x + threadIdx.x; i < hi; i += (int64_t)gridDim.x * blockDim.x) {
+    float4 g;
+    if (MC) {
+      const float4* src = reinterpret_cast<const float4*>(p.mc_grads[par]) + i;
+      asm volatile("multimem.ld_reduce.relaxed.sys.global.add.v4.f32 {%0, %1, %2, %3}, [%4];"
+                   : "=f"(g.x), "=f"(g.y), "=f"(g.z), "=f"(g.w)
+                   : "l"(src)
+                   : "memory");
+    } else {
+      g = make_float4(0.f, 0.f, 0.f, 0.f);
+#pragma unroll 1
+      for (int r = 0; r < W; ++r) {
+        const float4* src = reinterpret_cast<const float4*>(p.grads[par][r]) + i;
+        float4 x = (r == p.rank) ? *src : ld_peer_f4(src);
+        g.x += x.x; g.y += x.y; g.z += x.z; g.w += x.w;
+      }
+    }
+    g.x *= h.scale; g.y *= h.scale; g.z *= h.scale; g.w *= h.scale;
+    float4 w = sgd_update(w_own[i], g, v4 ? v4 + i : nullptr, h);
+    uint2 s = to_bf16x4(w);
+    if (MC) {
+      float4* dst = reinterpret_cast<float4*>(p.mc_params) + i;
+      asm volatile("multimem.st.relaxed.sys.global.v4.f32 [%0], {%1, %2, %3, %4};" ::"l"(dst), "f"(w.x), "f"(w.y),
+                   "f"(w.z), "f"(w.w)
+                   : "memory");
+      if (p.mc_shadow) {
+        uint2* sd = reinterpret_cast<uint2*>(p.mc_shadow) + i;
+        asm volatile("multimem.st.relaxed.sys.global.v2.f32 [%0], {%1, %2};" ::"l"(sd), "f"(__uint_as_float(s.x)),
+                     "f"(__uint_as_float(s.y))
+                     : "memory");
+      }
+    } else {
+#pragma unroll 1
+      for (int r = 0; r < W; ++r) {
+        float4* dst = reinterpret_cast<float4*>(p.params[r]) + i;
+        if (r == p.rank) *dst = w; else st_peer_f4(dst, w);
+        if (p.shadow[r]) {
+          uint2* sd = reinterpret_cast<uint2*>(p.shadow[r]) + i;
+          if (r == p.rank) *sd = s;
+          else asm volatile("st.relaxed.sys.global.v2.u32 [%0], {%1, %2};" ::"l"(sd), "r"(s.x), "r"(s.y) : "memory");
+        }
+      }
+    }
+  }
+  // clear the other-parity gradient buffer (whole local arena)
+  float4* z4 = reinterpret_cast<float4*>(p.grads[par ^ 1][p.rank]);
+  if (z4)
+    for (int64_t i = (int64_t)blockIdx.x * blockDim.x + threadIdx.x; i < n4; i += (int64_t)gridDim.x * blockDim.x)
+      z4[i] = make_float4(0.f, 0.f, 0.f, 0.f);
+  // end barrier: every peer's slice has been written into my arena before this kernel retires
+  if (!block_barrier(p, p.pad_stride, e)) return;
+  finish_step(p, e);
+}
+
+// Plain in-place all-reduce (sum) of a symmetric fp32 buffer - used by the bandwidth sweep and by
+// callers that want the reduced gradients themselves (metrics, optimizers without a fused form).
+// Two-shot over peer memory; `epoch`/flags as above but without parity (the caller separates calls).
+template <bool MC>
+__global__ void __launch_bounds__(512) allreduce_sum_kernel(TfdlFusedArParams p) {
+  const uint32_t e = *p.epoch + 1;
+  const int W = p.world;
+  if (!block_barrier(p, 0, e)) return;
+  const int64_t n4 = p.n >> 2;
+  const int64_t per = (n4 + W - 1) / W;
+  const int64_t lo = per * p.rank, hi = min(n4, lo + per);
+  for (int64_t i = lo + (int64_t)blockIdx.x * blockDim.x + threadIdx.x; i < hi; i += (int64_t)gridDim.x * blockDim.x) {
+    float4 g;
+    if (MC) {
+      const float4* src = reinterpret_cast<const float4*>(p.mc_grads[0]) + i;
+      asm volatile("multimem.ld_reduce.relaxed.sys.global.add.v4.f32 {%0, %1, %2, %3}, [%4];"
+                   : "=f"(g.x), "=f"(g.y), "=f"(g.z), "=f"(g.w) : "l"(src) : "memory");
+      float4* dst = reinterpret_cast<float4*>(p.mc_grads[0]) + i;
+      asm volatile("multimem.st.relaxed.sys.global.v4.f32 [%0], {%1, %2, %3, %4};" ::"l"(dst), "f"(g.x), "f"(g.y),
+                   "f"(g.z), "f"(g.w) : "memory");
+    } else {
+      g = make_float4(0.f, 0.f, 0.f, 0.f);
+#pragma unroll 1
+      for (int r = 0; r < W; ++r) {
+        const float4* src = reinterpret_cast<const float4*>(p.grads[0][r]) + i;
+        float4 x = (r == p.rank) ? *src : ld_peer_f4(src);
+        g.x += x.x; g.y += x.y; g.z += x.z; g.w += x.w;
+      }
+      // slice `rank` of every arena is read by this rank alone, so it can be overwritten right away
+#pragma unroll 1
+      for (int r = 0; r < W; ++r) {
+        float4* dst = reinterpret_cast<float4*>(p.grads[0][r]) + i;
+        if (r == p.rank) *dst = g; else st_peer_f4(dst, g);
+      }
+    }
+  }
+  if (!block_barrier(p, p.pad_stride, e)) return;
+  finish_step(p, e);
+}
+
+// fp32 -> bf16 shadow refresh (after set_weights / checkpoint load) and buffer clear
+__global__ void cast_shadow_kernel(const float* __restrict__ src, __nv_bfloat16* __restrict__ dst, int64_t n) {
+  int64_t i = ((int64_t)blockIdx.x * blockDim.x + threadIdx.x) * 4;
+  if (i + 3 < n) {
+    float4 w = *reinterpret_cast<const float4*>(src + i);
+    *reinterpret_cast<uint2*>(dst + i) = to_bf16x4(w);
+  } else {
+    for (; i < n; ++i) dst[i] = __float2bfloat16(src[i]);
+  }
+}
+
+}  // namespace tfdl
+
+using namespace tfdl;
+
+static int pick_grid(const TfdlFusedArParams* p, int64_t work4, int threads) {
+  int64_t blocks = (work4 + threads - 1) / threads;
+  int cap = p->max_blocks > 0 ? p->max_blocks : 148;
+  if (blocks > cap) blocks = cap;
+  if (blocks < 1) blocks = 1;
+  return (int)blocks;
+}
+
+extern "C" int tfdl_fused_allreduce_sgd(const TfdlFusedArParams* p, int algo, void* stream) {
+  TFDL_REQUIRE(p && p->world >= 1 && p->world <= TFDL_MAX_RANKS, "fused_allreduce_sgd: world %d out of range",
+               p ? p->world : -1);
+  TFDL_REQUIRE(p->n > 0 && p->n % 4 == 0, "fused_allreduce_sgd: n=%lld must be a positive multiple of 4",
+               (long long)p->n);
+  TFDL_REQUIRE(p->epoch && p->done && p->hyper, "fused_allreduce_sgd: epoch/done/hyper pointers are required");
+  TFDL_REQUIRE(p->world == 1 || p->flags[p->rank], "fused_allreduce_sgd: flag pads missing");
+  cudaStream_t s = (cudaStream_t)stream;
+  const int threads = 256;
+  const int64_t n4 = p->n / 4;
+  if (algo == TFDL_AR_ONESHOT || p->world == 1) {
+    int grid = pick_grid(p, n4, threads);
+    fused_ar_oneshot_kernel<<<grid, threads, 0, s>>>(*p);
+  } else if (algo == TFDL_AR_TWOSHOT) {
+    int grid = pick_grid(p, (n4 + p->world - 1) / p->world, threads);
+    fused_ar_sliced_kernel<false><<<grid, threads, 0, s>>>(*p);
+  } else if (algo == TFDL_AR_MULTIMEM) {
+    TFDL_REQUIRE(p->mc_params && p->mc_grads[0] && p->mc_grads[1], "fused_allreduce_sgd: multicast pointers missing");
+    int grid = pick_grid(p, (n4 + p->world - 1) / p->world, threads);
+    fused_ar_sliced_kernel<true><<<grid, threads, 0, s>>>(*p);
+  } else {
+    TFDL_REQUIRE(false, "fused_allreduce_sgd: unknown algorithm %d", algo);
+  }
+  TFDL_CUDA_OK(cudaGetLastError());
+  return 0;
+}
+
+extern "C" int tfdl_allreduce_sum(const TfdlFusedArParams* p, int algo, void* stream) {
+  TFDL_REQUIRE(p && p->world >= 2 && p->world <= TFDL_MAX_RANKS, "allreduce_sum: world %d out of range",
+               p ? p->world : -1);
+  TFDL_REQUIRE(p->n > 0 && p->n % 4 == 0, "allreduce_sum: n must be a positive multiple of 4");
+  cudaStream_t s = (cudaStream_t)stream;
+  const int threads = 512;
+  int grid = pick_grid(p, (p->n / 4 + p->world - 1) / p->world, threads);
+  if (algo == TFDL_AR_MULTIMEM) {
+    TFDL_REQUIRE(p->mc_grads[0], "allreduce_sum: multicast pointer missing");
+    allreduce_sum_kernel<true><<<grid, threads, 0, s>>>(*p);
+  } else {
+    allreduce_sum_kernel<false><<<grid, threads, 0, s>>>(*p);
+  }
+  TFDL_CUDA_OK(cudaGetLastError());
+  return 0;
+}
+
+extern "C" int tfdl_cast_f32_to_bf16(const float* src, void* dst, int64_t n, void* stream) {
+  if (n <= 0) return 0;
+  int threads = 256;
+  int64_t blocks = ((n + 3) / 4 + threads - 1) / threads;
+  cast_shadow_kernel<<<(unsigned)blocks, threads, 0, (cudaStream_t)stream>>>(src, (__nv_bfloat16*)dst, n);
+  TFDL_CUDA_OK(cudaGetLastError());
+  return 0;
+}
+
+extern "C" int tfdl_enable_peer_access(int device, int peer) {
+  int cur = 0;
+  TFDL_CUDA_OK(cudaGetDevice(&cur));
+  TFDL_CUDA_OK(cudaSetDevice(device));
+  int can = 0;
+  TFDL_CUDA_OK(cudaDeviceCanAccessPeer(&can, device, peer));
+  TFDL_REQUIRE(can, "device %d cannot access peer %d", device, peer);
+  cudaError_t e = cudaDeviceEnablePeerAccess(peer, 0);
+  if (e == cudaErrorPeerAccessAlreadyEnabled) { cudaGetLastError(); e = cudaSuccess; }
+  cudaSetDevice(cur);
+  TFDL_CUDA_OK(e);
+  return 0;
+}

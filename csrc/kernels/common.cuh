@@ -268,6 +268,39 @@ __device__ __forceinline__ uint32_t core_off_mnmajor(uint32_t k, uint32_t g, uin
   return g * (kchunks * 128u) + (k >> 3) * 128u + (k & 7u) * 16u;
 }
 
+// Stage `rows` x `kcols` of a K-major operand (row pitch ld elements) starting at (r0,k0).
+__device__ __forceinline__ void stage_kmajor(uint32_t smem_base, const __nv_bfloat16* X, int ld, int r0,
+                                             int rows_valid_end, int k0, int tile_rows, int kcols) {
+  const int kchunks = kcols >> 3;
+  const int total = tile_rows * kchunks;
+  for (int i = threadIdx.x; i < total; i += blockDim.x) {
+    // consecutive threads -> consecutive rows inside one core matrix (conflict-free 128B stores)
+    int r_in = i & 7;
+    int rest = i >> 3;
+    int j = rest % kchunks;
+    int rg = rest / kchunks;
+    int r = rg * 8 + r_in;
+    bool ok = (r0 + r) < rows_valid_end;
+    const __nv_bfloat16* src = ok ? X + (size_t)(r0 + r) * ld + k0 + j * 8 : X;
+    cp_async16(smem_base + core_off_kmajor(r, j, kchunks), src, ok);
+  }
+}
+// Stage an MN-major operand: global is [K][cols] (pitch ld); tile covers cols [c0, c0+tile_cols).
+__device__ __forceinline__ void stage_mnmajor(uint32_t smem_base, const __nv_bfloat16* X, int ld, int c0,
+                                              int cols_valid_end, int k0, int tile_cols, int kcols) {
+  const int kchunks = kcols >> 3;
+  const int groups = tile_cols >> 3;
+  const int total = groups * kcols;
+  for (int i = threadIdx.x; i < total; i += blockDim.x) {
+    // consecutive threads -> consecutive MN chunks of one k row (coalesced 16B global reads)
+    int g = i % groups;
+    int k = i / groups;
+    bool ok = (c0 + g * 8) < cols_valid_end;
+    const __nv_bfloat16* src = ok ? X + (size_t)(k0 + k) * ld + c0 + g * 8 : X;
+    cp_async16(smem_base + core_off_mnmajor(k, g, kchunks), src, ok);
+  }
+}
+
 // ----------------------------------------------------------------------------------------
 // system-scope flag traffic for the NVLink collectives
 // ----------------------------------------------------------------------------------------

@@ -30,40 +30,8 @@ struct GatherGemmParams {
   int k_split;            // gridDim.z; each z handles a contiguous range of k-blocks
   int relu;
   int atomic_out;         // accumulate into D with red.add (split-K)
+  int trans_out;          // write D transposed: element (row, col) goes to D[col*ldd + row]
 };
-
-// Stage `rows` x `kcols` of a K-major operand (row pitch ld elements) starting at (r0,k0).
-__device__ __forceinline__ void stage_kmajor(uint32_t smem_base, const __nv_bfloat16* X, int ld, int r0,
-                                             int rows_valid_end, int k0, int tile_rows, int kcols) {
-  const int kchunks = kcols >> 3;
-  const int total = tile_rows * kchunks;
-  for (int i = threadIdx.x; i < total; i += blockDim.x) {
-    // consecutive threads -> consecutive rows inside one core matrix (conflict-free 128B stores)
-    int r_in = i & 7;
-    int rest = i >> 3;
-    int j = rest % kchunks;
-    int rg = rest / kchunks;
-    int r = rg * 8 + r_in;
-    bool ok = (r0 + r) < rows_valid_end;
-    const __nv_bfloat16* src = ok ? X + (size_t)(r0 + r) * ld + k0 + j * 8 : X;
-    cp_async16(smem_base + core_off_kmajor(r, j, kchunks), src, ok);
-  }
-}
-// Stage an MN-major operand: global is [K][cols] (pitch ld); tile covers cols [c0, c0+tile_cols).
-__device__ __forceinline__ void stage_mnmajor(uint32_t smem_base, const __nv_bfloat16* X, int ld, int c0,
-                                              int cols_valid_end, int k0, int tile_cols, int kcols) {
-  const int kchunks = kcols >> 3;
-  const int groups = tile_cols >> 3;
-  const int total = groups * kcols;
-  for (int i = threadIdx.x; i < total; i += blockDim.x) {
-    // consecutive threads -> consecutive MN chunks of one k row (coalesced 16B global reads)
-    int g = i % groups;
-    int k = i / groups;
-    bool ok = (c0 + g * 8) < cols_valid_end;
-    const __nv_bfloat16* src = ok ? X + (size_t)(k0 + k) * ld + c0 + g * 8 : X;
-    cp_async16(smem_base + core_off_mnmajor(k, g, kchunks), src, ok);
-  }
-}
 
 __global__ void __launch_bounds__(128, 1) gather_gemm_kernel(GatherGemmParams p) {
   extern __shared__ __align__(1024) uint8_t smem[];
@@ -146,13 +114,14 @@ __global__ void __launch_bounds__(128, 1) gather_gemm_kernel(GatherGemmParams p)
           const int col = n0 + c + i;
           if (col >= p.N) break;
           float x = __uint_as_float(v[i]);
+          const size_t o = p.trans_out ? (size_t)col * p.ldd + row : (size_t)row * p.ldd + col;
           if (p.atomic_out) {
-            atomicAdd(p.D + (size_t)row * p.ldd + col, x);
+            atomicAdd(p.D + o, x);
           } else {
-            if (p.bias) x += p.bias[col];
+            if (p.bias) x += p.bias[p.trans_out ? row : col];
             if (p.relu) x = fmaxf(x, 0.f);
-            if (p.D) p.D[(size_t)row * p.ldd + col] = x;
-            if (p.Dh) p.Dh[(size_t)row * p.ldd + col] = __float2bfloat16(x);
+            if (p.D) p.D[o] = x;
+            if (p.Dh) p.Dh[o] = __float2bfloat16(x);
           }
         }
       }
@@ -165,9 +134,20 @@ __global__ void __launch_bounds__(128, 1) gather_gemm_kernel(GatherGemmParams p)
 
 }  // namespace tfdl
 
+extern "C" int tfdl_gemm_bf16_gather_ex(const void* A, const void* B, float* D, void* Dh, const float* bias, int M,
+                                        int N, int K, int lda, int ldb, int ldd, int a_mn, int b_mn, int relu,
+                                        int k_split, int n_tile, int k_block, int trans_out, void* stream);
+
 extern "C" int tfdl_gemm_bf16_gather(const void* A, const void* B, float* D, void* Dh, const float* bias, int M,
                                      int N, int K, int lda, int ldb, int ldd, int a_mn, int b_mn, int relu,
                                      int k_split, void* stream) {
+  return tfdl_gemm_bf16_gather_ex(A, B, D, Dh, bias, M, N, K, lda, ldb, ldd, a_mn, b_mn, relu, k_split, 0, 0, 0,
+                                  stream);
+}
+
+extern "C" int tfdl_gemm_bf16_gather_ex(const void* A, const void* B, float* D, void* Dh, const float* bias, int M,
+                                        int N, int K, int lda, int ldb, int ldd, int a_mn, int b_mn, int relu,
+                                        int k_split, int n_tile, int k_block, int trans_out, void* stream) {
   using namespace tfdl;
   TFDL_REQUIRE(M > 0 && N > 0 && K > 0, "gemm_gather: empty problem");
   TFDL_REQUIRE(K % 16 == 0, "gemm_gather: K=%d must be a multiple of 16", K);
@@ -180,24 +160,25 @@ extern "C" int tfdl_gemm_bf16_gather(const void* A, const void* B, float* D, voi
   p.bias = bias; p.M = M; p.N = N; p.K = K; p.lda = lda; p.ldb = ldb; p.ldd = ldd;
   p.a_mn = a_mn; p.b_mn = b_mn; p.relu = relu;
   int n_pad = (N + 15) / 16 * 16;
-  p.n_tile = n_pad <= 256 ? n_pad : 128;
+  p.n_tile = n_tile > 0 ? n_tile : (n_pad <= 256 ? n_pad : 128);
+  TFDL_REQUIRE(p.n_tile % 16 == 0 && p.n_tile <= 256, "gemm_gather: n_tile=%d must be a multiple of 16, <= 256",
+               p.n_tile);
   // K block: as large as fits in ~192 KB with both operands resident
   int kb = (192 * 1024) / (2 * (128 + p.n_tile));
   kb = kb / 16 * 16;
+  if (k_block > 0) kb = k_block;
   if (kb > K) kb = K;
   if (kb > 512) kb = 512;
+  TFDL_REQUIRE(kb % 16 == 0 && (size_t)(128 + p.n_tile) * kb * 2 <= 200 * 1024, "gemm_gather: bad k_block %d", kb);
   p.k_block = kb;
   p.k_split = k_split < 1 ? 1 : k_split;
   p.atomic_out = p.k_split > 1;
+  p.trans_out = trans_out;
   TFDL_REQUIRE(!p.atomic_out || (D && !Dh && !bias && !relu),
                "gemm_gather: split-K accumulates into fp32 D only (caller zeroes D, applies bias later)");
   size_t smem = (size_t)(128 + p.n_tile) * p.k_block * 2;
-  static size_t configured = 0;
-  if (smem > configured) {
-    TFDL_CUDA_OK(cudaFuncSetAttribute(gather_gemm_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize,
-                                      (int)(200 * 1024)));
-    configured = 200 * 1024;
-  }
+  TFDL_CUDA_OK(cudaFuncSetAttribute(gather_gemm_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize,
+                                    (int)(200 * 1024)));
   dim3 grid((M + 127) / 128, (N + p.n_tile - 1) / p.n_tile, p.k_split);
   gather_gemm_kernel<<<grid, 128, smem, (cudaStream_t)stream>>>(p);
   TFDL_CUDA_OK(cudaGetLastError());

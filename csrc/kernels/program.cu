@@ -1,0 +1,230 @@
+// Native step executor for the reference CNN (what model.fit(...) at
+// /root/reference/tf_dist_example.py:59 drives on a B200).
+//
+// TensorFlow's fit() dispatches a traced graph step by step from Python/C++ with an input iterator,
+// an all-reduce and eight optimizer launches. Here one training step is a CUDA graph
+// (9 compute kernels on two captured branches + the fused all-reduce/SGD kernel), there are two such
+// graphs (gradient-buffer parity 0/1, see allreduce.cu), and tfdl_cnn_program_run() drives any number
+// of steps from C++: per step one async H2D copy of the packed batch from pinned host memory on a
+// copy stream, one graph launch, one async 8-byte D2H copy of (loss, accuracy). The host never
+// waits for the device inside the loop.
+#include <vector>
+#include "common.cuh"
+#include "../../include/tfdl_kernels.h"
+
+using namespace tfdl;
+
+#define TFDL_RC(expr)        \
+  do {                       \
+    int _rc = (expr);        \
+    if (_rc != 0) return _rc; \
+  } while (0)
+
+extern "C" int tfdl_cnn_step_launch(const TfdlCnnStep* s, void* stream, void* side, void* ev_fork, void* ev_join) {
+  const TfdlCnnDims* d = &s->dims;
+  cudaStream_t st = (cudaStream_t)stream, sd = (cudaStream_t)side;
+  cudaEvent_t ef = (cudaEvent_t)ev_fork, ej = (cudaEvent_t)ev_join;
+  const float* P = s->params;
+  const __nv_bfloat16* H = (const __nv_bfloat16*)s->shadow;
+  float* G = s->grads;
+  const bool forked = sd != nullptr && sd != st && ef != nullptr && ej != nullptr;
+  // ---- forward ----
+  TFDL_RC(tfdl_cnn_conv1_fwd(s->x, P + s->off_w1c, P + s->off_b1c, s->a1, s->idx1, d, st));
+  TFDL_RC(tfdl_cnn_conv2_fwd(s->a1, H + s->off_w2c, P + s->off_b2c, s->a2, s->idx2, d, st));
+  // dense1: acc[s][u] += sum_k W1[u][k] a2[s][k]   (swap-AB: M = units, N = samples, split-K, transposed RED)
+  TFDL_RC(tfdl_gemm_bf16_gather_ex(H + s->off_w1d, s->a2, s->acc, nullptr, nullptr, d->D1, d->B, d->F, d->F, d->F,
+                                   d->D1, 0, 0, 0, s->dense1_ksplit > 0 ? s->dense1_ksplit : 1, 0, 64, 1, st));
+  TFDL_RC(tfdl_cnn_head(s->acc, P + s->off_b1d, P + s->off_w2d, P + s->off_b2d, s->labels, s->dh, G + s->off_w2d,
+                        G + s->off_b2d, G + s->off_b1d, s->metrics, s->step_out, d, st));
+  // ---- backward ----
+  if (forked) {
+    TFDL_CUDA_OK(cudaEventRecord(ef, st));
+    TFDL_CUDA_OK(cudaStreamWaitEvent(sd, ef, 0));
+  }
+  cudaStream_t off = forked ? sd : st;
+  // dW1[u][f] = sum_s dh[s][u] a2[s][f]: both operands MN-major (off the critical path)
+  TFDL_RC(tfdl_gemm_bf16_gather_ex(s->dh, s->a2, G + s->off_w1d, nullptr, nullptr, d->D1, d->F, d->B, d->D1, d->F,
+                                   d->F, 1, 1, 0, 1, 64, 0, 0, off));
+  TFDL_RC(tfdl_cnn_dense1_dgrad(s->dh, H + s->off_w1d, s->a2, s->idx2, s->dy2, d, st));
+  if (forked) {
+    // conv2 wgrad needs dy2 (main branch) but nothing downstream needs it before the all-reduce
+    TFDL_CUDA_OK(cudaEventRecord(ef, st));
+    TFDL_CUDA_OK(cudaStreamWaitEvent(sd, ef, 0));
+  }
+  TFDL_RC(tfdl_cnn_conv2_wgrad(s->a1, s->dy2, G + s->off_w2c, G + s->off_b2c, d, off));
+  TFDL_RC(tfdl_cnn_conv2_dgrad(s->dy2, H + s->off_w2c, s->a1, s->g1, d, st));
+  TFDL_RC(tfdl_cnn_conv1_wgrad(s->x, s->g1, s->idx1, G + s->off_w1c, G + s->off_b1c, d, st));
+  if (forked) {
+    TFDL_CUDA_OK(cudaEventRecord(ej, sd));
+    TFDL_CUDA_OK(cudaStreamWaitEvent(st, ej, 0));
+  }
+  return 0;
+}
+
+struct TfdlCnnProgram {
+  TfdlCnnStep steps[2];
+  TfdlFusedArParams ar[2];
+  int algo = 0;
+  int use_graph = 1;
+  cudaGraphExec_t exec[2] = {nullptr, nullptr};
+  cudaStream_t side = nullptr, copy = nullptr, out = nullptr;
+  cudaEvent_t ev_fork = nullptr, ev_join = nullptr;
+  cudaEvent_t ev_in[2] = {nullptr, nullptr}, ev_used[2] = {nullptr, nullptr}, ev_step[2] = {nullptr, nullptr},
+              ev_out[2] = {nullptr, nullptr};
+  int64_t steps_done = 0;
+  int device = 0;
+};
+
+static int enqueue_step(TfdlCnnProgram* p, int par, cudaStream_t st) {
+  TFDL_RC(tfdl_cnn_step_launch(&p->steps[par], st, p->side, p->ev_fork, p->ev_join));
+  TFDL_RC(tfdl_fused_allreduce_sgd(&p->ar[par], p->algo, st));
+  return 0;
+}
+
+static int ensure_graph(TfdlCnnProgram* p, int par, cudaStream_t st) {
+  if (p->exec[par]) return 0;
+  // cudaFuncSetAttribute calls inside the launch helpers are not stream operations, so they are legal
+  // during capture; run the step once eagerly first anyway? No: that would advance training. Capture only.
+  cudaGraph_t graph = nullptr;
+  TFDL_CUDA_OK(cudaStreamBeginCapture(st, cudaStreamCaptureModeRelaxed));
+  int rc = enqueue_step(p, par, st);
+  cudaError_t ce = cudaStreamEndCapture(st, &graph);
+  if (rc != 0) {
+    if (graph) cudaGraphDestroy(graph);
+    return rc;
+  }
+  TFDL_CUDA_OK(ce);
+  TFDL_CUDA_OK(cudaGraphInstantiate(&p->exec[par], graph, 0));
+  TFDL_CUDA_OK(cudaGraphDestroy(graph));
+  return 0;
+}
+
+extern "C" int tfdl_cnn_program_create(const TfdlCnnStep steps[2], const TfdlFusedArParams ar[2], int algo,
+                                       int use_graph, TfdlCnnProgram** out) {
+  TFDL_REQUIRE(steps && ar && out, "cnn_program_create: null argument");
+  auto* p = new TfdlCnnProgram();
+  for (int i = 0; i < 2; ++i) {
+    p->steps[i] = steps[i];
+    p->ar[i] = ar[i];
+    p->ar[i].parity = i;
+  }
+  p->algo = algo;
+  p->use_graph = use_graph;
+  TFDL_CUDA_OK(cudaGetDevice(&p->device));
+  TFDL_CUDA_OK(cudaStreamCreateWithFlags(&p->side, cudaStreamNonBlocking));
+  TFDL_CUDA_OK(cudaStreamCreateWithFlags(&p->copy, cudaStreamNonBlocking));
+  TFDL_CUDA_OK(cudaStreamCreateWithFlags(&p->out, cudaStreamNonBlocking));
+  TFDL_CUDA_OK(cudaEventCreateWithFlags(&p->ev_fork, cudaEventDisableTiming));
+  TFDL_CUDA_OK(cudaEventCreateWithFlags(&p->ev_join, cudaEventDisableTiming));
+  for (int i = 0; i < 2; ++i) {
+    TFDL_CUDA_OK(cudaEventCreateWithFlags(&p->ev_in[i], cudaEventDisableTiming));
+    TFDL_CUDA_OK(cudaEventCreateWithFlags(&p->ev_used[i], cudaEventDisableTiming));
+    TFDL_CUDA_OK(cudaEventCreateWithFlags(&p->ev_step[i], cudaEventDisableTiming));
+    TFDL_CUDA_OK(cudaEventCreateWithFlags(&p->ev_out[i], cudaEventDisableTiming));
+  }
+  *out = p;
+  return 0;
+}
+
+extern "C" int tfdl_cnn_program_destroy(TfdlCnnProgram* p) {
+  if (!p) return 0;
+  for (int i = 0; i < 2; ++i) {
+    if (p->exec[i]) cudaGraphExecDestroy(p->exec[i]);
+    if (p->ev_in[i]) cudaEventDestroy(p->ev_in[i]);
+    if (p->ev_used[i]) cudaEventDestroy(p->ev_used[i]);
+    if (p->ev_step[i]) cudaEventDestroy(p->ev_step[i]);
+    if (p->ev_out[i]) cudaEventDestroy(p->ev_out[i]);
+  }
+  if (p->ev_fork) cudaEventDestroy(p->ev_fork);
+  if (p->ev_join) cudaEventDestroy(p->ev_join);
+  if (p->side) cudaStreamDestroy(p->side);
+  if (p->copy) cudaStreamDestroy(p->copy);
+  if (p->out) cudaStreamDestroy(p->out);
+  delete p;
+  return 0;
+}
+
+static int launch_one(TfdlCnnProgram* p, cudaStream_t st) {
+  const int par = (int)(p->steps_done & 1);
+  if (p->use_graph) {
+    TFDL_RC(ensure_graph(p, par, st));
+    TFDL_CUDA_OK(cudaGraphLaunch(p->exec[par], st));
+  } else {
+    TFDL_RC(enqueue_step(p, par, st));
+  }
+  p->steps_done++;
+  return 0;
+}
+
+extern "C" int tfdl_cnn_program_step(TfdlCnnProgram* p, void* stream) { return launch_one(p, (cudaStream_t)stream); }
+
+extern "C" int tfdl_cnn_program_run(TfdlCnnProgram* p, const void* host_batches, int64_t n_records, int64_t n_steps,
+                                    float* host_out, void* stream) {
+  TFDL_REQUIRE(p && host_batches && n_records > 0 && n_steps >= 0, "cnn_program_run: bad arguments");
+  cudaStream_t st = (cudaStream_t)stream;
+  const TfdlCnnDims& d = p->steps[0].dims;
+  const size_t x_bytes = (size_t)d.B * d.H0 * d.W0 * sizeof(float), y_bytes = (size_t)d.B * sizeof(int);
+  const size_t rec = x_bytes + y_bytes;
+  // both parities must be captured before the pipelined loop (capture is not allowed to interleave with
+  // the event waits below)
+  if (p->use_graph) {
+    TFDL_RC(ensure_graph(p, 0, st));
+    TFDL_RC(ensure_graph(p, 1, st));
+  }
+  // the copy stream must not overwrite an input buffer that work already queued on `st` still reads
+  TFDL_CUDA_OK(cudaEventRecord(p->ev_used[0], st));
+  TFDL_CUDA_OK(cudaEventRecord(p->ev_used[1], st));
+  TFDL_CUDA_OK(cudaEventRecord(p->ev_out[0], p->out));
+  TFDL_CUDA_OK(cudaEventRecord(p->ev_out[1], p->out));
+  for (int64_t i = 0; i < n_steps; ++i) {
+    const int par = (int)(p->steps_done & 1);
+    const char* src = static_cast<const char*>(host_batches) + (size_t)(i % n_records) * rec;
+    const TfdlCnnStep& s = p->steps[par];
+    // H2D of this step's batch (into the input buffers of this parity) once the step two back has consumed them
+    TFDL_CUDA_OK(cudaStreamWaitEvent(p->copy, p->ev_used[par], 0));
+    TFDL_CUDA_OK(cudaMemcpyAsync(const_cast<float*>(s.x), src, x_bytes, cudaMemcpyHostToDevice, p->copy));
+    TFDL_CUDA_OK(cudaMemcpyAsync(const_cast<int*>(s.labels), src + x_bytes, y_bytes, cudaMemcpyHostToDevice, p->copy));
+    TFDL_CUDA_OK(cudaEventRecord(p->ev_in[par], p->copy));
+    TFDL_CUDA_OK(cudaStreamWaitEvent(st, p->ev_in[par], 0));
+    TFDL_CUDA_OK(cudaStreamWaitEvent(st, p->ev_out[par], 0));  // step_out[par] of two steps back has been read
+    TFDL_RC(launch_one(p, st));
+    TFDL_CUDA_OK(cudaEventRecord(p->ev_used[par], st));
+    if (host_out) {
+      TFDL_CUDA_OK(cudaStreamWaitEvent(p->out, p->ev_used[par], 0));
+      TFDL_CUDA_OK(cudaMemcpyAsync(host_out + 2 * i, s.step_out, 2 * sizeof(float), cudaMemcpyDeviceToHost, p->out));
+      TFDL_CUDA_OK(cudaEventRecord(p->ev_out[par], p->out));
+    }
+  }
+  // make `st` the single stream the caller has to synchronise
+  TFDL_CUDA_OK(cudaEventRecord(p->ev_out[0], p->out));
+  TFDL_CUDA_OK(cudaStreamWaitEvent(st, p->ev_out[0], 0));
+  return 0;
+}
+
+// Same loop with the batches already resident on the device (a pool larger than L2 keeps the inputs
+// coming from HBM): per step two D2D copies into this parity's input buffers and one graph launch,
+// all on `stream`. This is the kernel-only measurement path of bench.py.
+extern "C" int tfdl_cnn_program_run_device(TfdlCnnProgram* p, const void* dev_batches, int64_t n_records,
+                                           int64_t n_steps, void* stream) {
+  TFDL_REQUIRE(p && dev_batches && n_records > 0 && n_steps >= 0, "cnn_program_run_device: bad arguments");
+  cudaStream_t st = (cudaStream_t)stream;
+  const TfdlCnnDims& d = p->steps[0].dims;
+  const size_t x_bytes = (size_t)d.B * d.H0 * d.W0 * sizeof(float), y_bytes = (size_t)d.B * sizeof(int);
+  const size_t rec = x_bytes + y_bytes;
+  if (p->use_graph) {
+    TFDL_RC(ensure_graph(p, 0, st));
+    TFDL_RC(ensure_graph(p, 1, st));
+  }
+  for (int64_t i = 0; i < n_steps; ++i) {
+    const int par = (int)(p->steps_done & 1);
+    const char* src = static_cast<const char*>(dev_batches) + (size_t)(i % n_records) * rec;
+    const TfdlCnnStep& s = p->steps[par];
+    TFDL_CUDA_OK(cudaMemcpyAsync(const_cast<float*>(s.x), src, x_bytes, cudaMemcpyDeviceToDevice, st));
+    TFDL_CUDA_OK(cudaMemcpyAsync(const_cast<int*>(s.labels), src + x_bytes, y_bytes, cudaMemcpyDeviceToDevice, st));
+    TFDL_RC(launch_one(p, st));
+  }
+  return 0;
+}
+
+extern "C" int64_t tfdl_cnn_program_steps_done(const TfdlCnnProgram* p) { return p ? p->steps_done : 0; }
+extern "C" int64_t tfdl_cnn_program_launches_per_step(const TfdlCnnProgram*) { return 10; }

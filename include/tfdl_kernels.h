@@ -32,11 +32,133 @@ int tfdl_gemm_bf16_gather(const void* A, const void* B, float* D, void* Dh, cons
                           int K, int lda, int ldb, int ldd, int a_mn, int b_mn, int relu, int k_split,
                           void* stream);
 
+/* Same with explicit tiling: n_tile (multiple of 16, 0 = auto), k_block (0 = auto), and trans_out = 1 to
+ * write element (row, col) to D[col*ldd + row] (coalesced split-K atomics when rows are the fast index). */
+int tfdl_gemm_bf16_gather_ex(const void* A, const void* B, float* D, void* Dh, const float* bias, int M, int N,
+                             int K, int lda, int ldb, int ldd, int a_mn, int b_mn, int relu, int k_split,
+                             int n_tile, int k_block, int trans_out, void* stream);
+
 /* D[M,N] = act(A[M,K] * B[N,K]^T + bias): persistent warp-specialised TMA + tcgen05 kernel
  * (128B-swizzled tiles, 4-8 stage mbarrier ring, double-buffered TMEM accumulators).
  * act: 0 none, 1 relu, 2 gelu(tanh). K, lda, ldb % 8 == 0; A, B 16-byte aligned. */
 int tfdl_gemm_bf16_tma(const void* A, const void* B, float* Df, void* Dh, const float* bias, int M, int N,
                        int K, int lda, int ldb, int ldd, int act, void* stream);
+
+
+/* ---- fused gradient all-reduce + SGD over NVLink peer memory ------------------------------
+ * ref: README.md:17,21,23,67 (NcclAllReduce / CollectiveOps after every batch) and
+ * tf_dist_example.py:51 (SGD). One kernel per step: cross-GPU flag barrier, peer loads of the
+ * gradient arenas, 1/N scale, SGD/momentum update of the fp32 master weights, bf16 shadow
+ * refresh, clear of the other-parity gradient buffer. See csrc/kernels/allreduce.cu. */
+#define TFDL_MAX_RANKS 8
+enum { TFDL_AR_ONESHOT = 0, TFDL_AR_TWOSHOT = 1, TFDL_AR_MULTIMEM = 2 };
+
+typedef struct {
+  float lr, momentum, nesterov, scale; /* read on the device each step: LR schedules need no re-capture */
+} TfdlHyper;
+
+typedef struct {
+  int world, rank;
+  int64_t n;                            /* fp32 elements in the arena, multiple of 4 */
+  float* params[TFDL_MAX_RANKS];        /* every rank's master-weight arena (peer-mapped); one-shot uses [rank] only */
+  void* shadow[TFDL_MAX_RANKS];         /* every rank's bf16 shadow arena (optional, may be NULL) */
+  float* grads[2][TFDL_MAX_RANKS];      /* [parity][rank] gradient arenas (peer-mapped) */
+  float* mom;                           /* local momentum slot arena or NULL */
+  uint32_t* flags[TFDL_MAX_RANKS];      /* every rank's flag pad (peer-mapped), 3 pads of pad_stride u32 */
+  uint32_t pad_stride;                  /* >= max_blocks * world */
+  int max_blocks;                       /* grid cap (also bounds flag slots) */
+  float* mc_params;                     /* multicast (NVLS) addresses, NULL when unsupported */
+  void* mc_shadow;
+  float* mc_grads[2];
+  uint32_t* epoch;                      /* device-local step counter (parity source for the backward kernels) */
+  uint32_t* done;                       /* device-local block ticket */
+  const TfdlHyper* hyper;               /* device memory */
+  const uint32_t* abort_word;           /* host-mapped or device word; non-zero releases every spin */
+  int parity;                           /* gradient buffer of this step: 0/1 fixed by the host, -1 = (epoch & 1) */
+} TfdlFusedArParams;
+
+int tfdl_fused_allreduce_sgd(const TfdlFusedArParams* p, int algo, void* stream);
+/* In-place sum of grads[0][*] over ranks (no update); the bandwidth-sweep primitive. */
+int tfdl_allreduce_sum(const TfdlFusedArParams* p, int algo, void* stream);
+int tfdl_cast_f32_to_bf16(const float* src, void* dst_bf16, int64_t n, void* stream);
+int tfdl_enable_peer_access(int device, int peer);
+
+
+/* ---- reference CNN training step (ref: tf_dist_example.py:40-52) ---------------------------
+ * Conv2D(C1,3,relu)-MaxPool-Conv2D(C2,3,relu)-MaxPool-Flatten-Dense(D1,relu)-Dense(NC) with
+ * sparse softmax cross-entropy; see csrc/kernels/cnn.cu for the kernel list and fusion plan. */
+typedef struct {
+  int B;          /* per-replica batch, multiple of 16 */
+  int H0, W0;     /* input height/width (single channel) */
+  int C1;         /* conv1 filters (32 or 64) */
+  int P1h, P1w;   /* pooled conv1 output = (H0-2)/2, (W0-2)/2 */
+  int C2;         /* conv2 filters (multiple of 32, <= 128) */
+  int P2h, P2w;   /* pooled conv2 output */
+  int F;          /* P2h*P2w*C2 (flatten width) */
+  int D1;         /* dense units (multiple of 16, <= 256) */
+  int NC;         /* classes */
+  int nrep;       /* replicas in sync: the loss is mean over the replica batch / nrep */
+} TfdlCnnDims;
+
+int tfdl_cnn_conv1_fwd(const float* x, const float* w /*[C1][9]*/, const float* b, void* a1_bf16, uint8_t* idx1,
+                       const TfdlCnnDims* d, void* stream);
+int tfdl_cnn_conv2_fwd(const void* a1_bf16, const void* w2_bf16 /*[C2][9*C1]*/, const float* b2, void* a2_bf16,
+                       uint8_t* idx2, const TfdlCnnDims* d, void* stream);
+int tfdl_cnn_head(float* acc /*[B][D1], re-zeroed*/, const float* b1, const float* w2 /*[NC][D1]*/, const float* b2,
+                  const int* labels, void* dh_bf16, float* g_w2, float* g_b2, float* g_b1, float* metrics /*[3]*/,
+                  float* step_out /*[2]: mean loss, accuracy*/, const TfdlCnnDims* d, void* stream);
+int tfdl_cnn_dense1_dgrad(const void* dh_bf16, const void* w1_bf16 /*[D1][F]*/, const void* a2_bf16,
+                          const uint8_t* idx2, void* dy2_bf16 /*[B][2P2h][2P2w][C2]*/, const TfdlCnnDims* d,
+                          void* stream);
+int tfdl_cnn_conv2_wgrad(const void* a1_bf16, const void* dy2_bf16, float* g_w2c /*[C2][9*C1], accumulated*/,
+                         float* g_b2c /*accumulated*/, const TfdlCnnDims* d, void* stream);
+int tfdl_cnn_conv2_dgrad(const void* dy2_bf16, const void* w2_bf16, const void* a1_bf16, void* g1_bf16,
+                         const TfdlCnnDims* d, void* stream);
+int tfdl_cnn_conv1_wgrad(const float* x, const void* g1_bf16, const uint8_t* idx1, float* g_w1c /*accumulated*/,
+                         float* g_b1c /*accumulated*/, const TfdlCnnDims* d, void* stream);
+
+/* One training step = the 9 kernels above + the fused all-reduce/SGD, described by pointers into the
+ * caller's buffers. Two descriptors (gradient-buffer parity 0 and 1) make a program. */
+typedef struct {
+  TfdlCnnDims dims;
+  const float* x;            /* [B][H0][W0] fp32 */
+  const int* labels;         /* [B] int32 */
+  const float* params;       /* fp32 master arena */
+  const void* shadow;        /* bf16 shadow arena (same element offsets) */
+  float* grads;              /* gradient arena of this parity */
+  int64_t off_w1c, off_b1c, off_w2c, off_b2c, off_w1d, off_b1d, off_w2d, off_b2d; /* element offsets */
+  void *a1, *a2, *dh, *dy2, *g1; /* bf16 activations / activation gradients */
+  uint8_t *idx1, *idx2;          /* pooling argmax */
+  float* acc;                /* [B][D1] fp32 split-K scratch, must be zero on entry, zero on exit */
+  float* metrics;            /* [3] running loss sum / correct / examples */
+  float* step_out;           /* [2] this step's mean loss and accuracy */
+  int dense1_ksplit;         /* CTAs along K for dense1 forward */
+} TfdlCnnStep;
+
+/* Launch the forward+backward kernels of one step on `stream`, using `side` for the branches that are
+ * off the critical path (dW1, conv2 wgrad); fork/join is done with the two events. Capturable. */
+int tfdl_cnn_step_launch(const TfdlCnnStep* s, void* stream, void* side, void* ev_fork, void* ev_join);
+
+/* Native step executor: owns two CUDA graphs (parity 0/1), each = step kernels + fused all-reduce/SGD.
+ * tfdl_cnn_program_run drives n_steps steps from host memory without returning to Python: per step an
+ * async H2D copy of the batch (x then labels, packed) from pinned memory on a copy stream, one graph
+ * launch, and an async D2H copy of (loss, accuracy) into host_out. */
+typedef struct TfdlCnnProgram TfdlCnnProgram;
+int tfdl_cnn_program_create(const TfdlCnnStep steps[2], const TfdlFusedArParams ar[2], int algo, int use_graph,
+                            TfdlCnnProgram** out);
+int tfdl_cnn_program_destroy(TfdlCnnProgram* p);
+/* One step on data already resident in steps[parity].x / .labels. */
+int tfdl_cnn_program_step(TfdlCnnProgram* p, void* stream);
+/* host_batches: n_steps records of (B*H0*W0 floats, B int32) back to back in PINNED memory (record i at
+ * byte offset (i % n_records) * record_bytes). host_out: pinned, 2 floats per step. Returns after the
+ * last step has been enqueued; the caller synchronises `stream`. */
+int tfdl_cnn_program_run(TfdlCnnProgram* p, const void* host_batches, int64_t n_records, int64_t n_steps,
+                         float* host_out, void* stream);
+/* As above with the records already on the device (two D2D copies + one graph launch per step). */
+int tfdl_cnn_program_run_device(TfdlCnnProgram* p, const void* dev_batches, int64_t n_records, int64_t n_steps,
+                                void* stream);
+int64_t tfdl_cnn_program_steps_done(const TfdlCnnProgram* p);
+int64_t tfdl_cnn_program_launches_per_step(const TfdlCnnProgram* p);
 
 #ifdef __cplusplus
 }

@@ -48,6 +48,10 @@ class CallbackList:
                              if type(c).on_train_batch_begin is not Callback.on_train_batch_begin]
         self._batch_end = [c for c in self.callbacks if type(c).on_train_batch_end is not Callback.on_train_batch_end]
 
+    @property
+    def has_batch_hooks(self) -> bool:
+        return bool(self._batch_begin or self._batch_end)
+
     def initial_epoch(self, requested: int) -> int:
         for c in self.callbacks:
             requested = c.initial_epoch(requested)

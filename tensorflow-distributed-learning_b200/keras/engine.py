@@ -284,21 +284,35 @@ class Model:
             if it is None or steps_per_epoch is None:
                 it = iter(dist)
             step = 0
+            chunked = hasattr(engine, "train_chunk") and not cbs.has_batch_hooks
             while steps_per_epoch is None or step < steps_per_epoch:
-                try:
-                    batch = next(it)
-                except StopIteration:
+                want = 1
+                if chunked:
+                    want = engine.CHUNK if steps_per_epoch is None else min(engine.CHUNK, steps_per_epoch - step)
+                group, exhausted = [], False
+                for _ in range(want):
+                    try:
+                        group.append(next(it))
+                    except StopIteration:
+                        exhausted = True
+                        break
+                if group:
+                    if chunked:
+                        engine.train_chunk(group)  # the native executor runs the whole chunk without Python
+                    else:
+                        cbs.on_train_batch_begin(step)
+                        engine.train_step(group[0])
+                    self._steps_done += len(group)
+                    if not chunked:
+                        cbs.on_train_batch_end(step, None)
+                    step += len(group)
+                if exhausted:
                     if steps_per_epoch is not None:
                         if verbose:
                             print(f"WARNING: input ran out of data after {step} of {steps_per_epoch} steps "
                                   f"in epoch {epoch + 1}; use .repeat() on the dataset", file=sys.stderr)
                         self.stop_training = True
                     break
-                cbs.on_train_batch_begin(step)
-                engine.train_step(batch)
-                self._steps_done += 1
-                cbs.on_train_batch_end(step, None)
-                step += 1
                 if self.stop_training:
                     break
             logs = self._read_logs()

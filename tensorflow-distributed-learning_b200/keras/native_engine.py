@@ -1,5 +1,310 @@
-"""Placeholder replaced below by the native step-program engine."""
+"""Native (sm_100a) training engine for the reference CNN topology.
+
+`try_build(model)` recognises the layer stack of /root/reference/tf_dist_example.py:40-52
+    Conv2D(C1,3,relu) - MaxPooling2D() - Conv2D(C2,3,relu) - MaxPooling2D() - Flatten - Dense(D1,relu) - Dense(NC)
+compiled with SparseCategoricalCrossentropy(from_logits=True) + SGD (any lr / momentum / nesterov),
+and returns an engine whose training step is ONE CUDA-graph launch: nine hand-written kernels
+(csrc/kernels/cnn.cu, tcgen05 for every GEMM-shaped op) plus the fused NVLink all-reduce + SGD kernel
+(csrc/kernels/allreduce.cu). Steps are driven by the C++ executor (csrc/kernels/program.cu): Python
+hands it a ring of pinned batches and does not run again until the chunk is done.
+
+Anything else (other topologies, evaluate/predict, a ragged last batch) runs on the portable
+TorchEngine, which shares the same parameter arena. On a machine with CUDA devices the native library
+must be present: a missing .so is an error, never a silent fallback.
+"""
+from __future__ import annotations
+
+import ctypes as C
+import os
+from typing import Any, List, Optional, Tuple
+
+import numpy as np
+import torch
+
+from ..ops import _lib
+from ..ops.allreduce import FusedState, P2PFusedAllReduce, SymmetricBuffer
+from ..ops.structs import AR_NAMES, CnnDims, CnnStep, FusedArParams, make_dims
+from ..parallel.values import PerReplica
+from . import layers as L
+from . import losses as _losses
+from . import metrics as _metrics
+from . import optimizers as _optimizers
 
 
-def try_build(model):
-    return None
+def _match(model: Any) -> Optional[Tuple[int, int, int, int, int, int]]:
+    """Returns (H0, W0, C1, C2, D1, NC) if the model is the supported topology."""
+    from .engine import Sequential
+
+    if not isinstance(model, Sequential) or not model.built:
+        return None
+    ls = [l for l in model._layers() if not isinstance(l, L.InputLayer)]
+    if len(ls) != 7:
+        return None
+    c1, p1, c2, p2, fl, d1, d2 = ls
+    ok = (isinstance(c1, L.Conv2D) and isinstance(p1, L.MaxPooling2D) and isinstance(c2, L.Conv2D)
+          and isinstance(p2, L.MaxPooling2D) and isinstance(fl, L.Flatten) and isinstance(d1, L.Dense)
+          and isinstance(d2, L.Dense))
+    if not ok:
+        return None
+    for c in (c1, c2):
+        if c.kernel_size != (3, 3) or c.strides != (1, 1) or c.padding != "valid" or c.activation != "relu" or not c.use_bias:
+            return None
+    for p in (p1, p2):
+        if p.pool_size != (2, 2) or p.strides != (2, 2) or p.padding != "valid":
+            return None
+    if d1.activation != "relu" or d2.activation not in (None, "linear") or not d1.use_bias or not d2.use_bias:
+        return None
+    ish = model._input_shape
+    if ish is None or len(ish) != 3 or ish[2] != 1:
+        return None
+    if not isinstance(model.loss, _losses.SparseCategoricalCrossentropy) or not model.loss.from_logits \
+            or model.loss.ignore_class is not None:
+        return None
+    if not isinstance(model.optimizer, _optimizers.SGD):
+        return None
+    for m in model.compiled_metrics:
+        if not isinstance(m, _metrics.SparseCategoricalAccuracy):
+            return None
+    H0, W0 = ish[0], ish[1]
+    C1, C2, D1, NC = c1.filters, c2.filters, d1.units, d2.units
+    if C1 % 32 or C1 > 64 or C2 % 32 or C2 > 128 or D1 % 16 or D1 > 256 or not (2 <= NC <= 64):
+        return None
+    if ((H0 - 2) // 2) * C1 > 1024 * 99 or ((W0 - 2) // 2) * C1 > 1024:
+        return None
+    if not all(w.trainable for w in model.weights):
+        return None
+    return H0, W0, C1, C2, D1, NC
+
+
+def try_build(model: Any) -> Optional["NativeCnnEngine"]:
+    """Native engine for `model`, or None if its topology has no native step program."""
+    _lib.kernels()  # raises NativeError when the library has not been built: no silent fallback on a GPU box
+    s = model.strategy
+    if s.num_local_replicas != 1 or s.local_devices[0].type != "cuda":
+        return None
+    shape = _match(model)
+    if shape is None:
+        return None
+    return NativeCnnEngine(model, shape)
+
+
+class NativeCnnEngine:
+    CHUNK = int(os.environ.get("TFDL_FIT_CHUNK", "64"))
+
+    def __init__(self, model: Any, shape: Tuple[int, int, int, int, int, int]) -> None:
+        self.model = model
+        self.strategy = model.strategy
+        self.device = self.strategy.local_devices[0]
+        self.shape = shape
+        self.lib = _lib.kernels()
+        self._prog: Optional[C.c_void_p] = None
+        self._B: Optional[int] = None
+        self._torch_engine: Any = None
+        self._keep: List[Any] = []
+        torch.cuda.set_device(self.device)
+        # graphs cannot be captured on the legacy default stream: the engine owns its stream
+        self.stream = torch.cuda.Stream(self.device)
+        arena = model.arenas[0]
+        ops = self.strategy.cross_device_ops
+        if not isinstance(ops, P2PFusedAllReduce):
+            ops = P2PFusedAllReduce(self.device)
+            if ops.world != 1:
+                raise RuntimeError("a multi-process GPU group must be created through MirroredStrategy / "
+                                   "MultiWorkerMirroredStrategy so that its arenas are peer-mapped")
+            for t in (arena.params, arena.grads):
+                b = SymmetricBuffer.__new__(SymmetricBuffer)
+                b.numel, b.dtype, b.device, b.world, b.rank = t.numel(), t.dtype, t.device, 1, 0
+                b.multicast_ptr, b.tensor, b.ptrs, b.handle = 0, t, [t.data_ptr()], None
+                ops._arenas.append(b)
+        self.ops = ops
+        opt = model.optimizer
+        self.state: FusedState = ops.fused_state(arena.params, arena.grads, momentum=bool(opt.momentum))
+        if opt.momentum:
+            opt._slots = {"momentum": [self.state.mom]}  # the optimizer's slot IS the kernel's buffer
+        self.hyperparams_changed()
+        self.state.refresh_shadow()
+        torch.cuda.synchronize(self.device)
+        self.metrics_dev = torch.zeros(3, dtype=torch.float32, device=self.device)
+        lib = self.lib
+        lib.tfdl_cnn_program_run.argtypes = [C.c_void_p, C.c_void_p, C.c_int64, C.c_int64, C.c_void_p, C.c_void_p]
+        lib.tfdl_cnn_program_steps_done.restype = C.c_int64
+        lib.tfdl_cnn_program_steps_done.argtypes = [C.c_void_p]
+        lib.tfdl_cnn_program_step.argtypes = [C.c_void_p, C.c_void_p]
+        lib.tfdl_cnn_program_destroy.argtypes = [C.c_void_p]
+
+    # ------------------------------------------------------------------------------------------
+    @property
+    def algo_name(self) -> str:
+        return self.state.algo_name
+
+    def hyperparams_changed(self) -> None:
+        opt = self.model.optimizer
+        self._lr = opt.learning_rate
+        self.state.set_hyper(self._lr, opt.momentum, opt.nesterov, 1.0)
+
+    def weights_changed(self) -> None:
+        self.state.refresh_shadow()
+
+    def _offsets(self) -> List[int]:
+        return [w.spec.offset for w in self.model.weights]
+
+    def _build_program(self, B: int) -> None:
+        if self._prog is not None:
+            torch.cuda.synchronize(self.device)
+            self.lib.tfdl_cnn_program_destroy(self._prog)
+            self._prog, self._keep = None, []
+        H0, W0, C1, C2, D1, NC = self.shape
+        d = make_dims(B, H0, W0, C1, C2, D1, NC, nrep=self.strategy.num_replicas_in_sync)
+        dev = self.device
+        bf = torch.bfloat16
+        z = lambda *s, dt=bf: torch.zeros(s, dtype=dt, device=dev)  # noqa: E731
+        bufs = dict(a1=z(B, d.P1h, d.P1w, C1), a2=z(B, d.F), dh=z(B, D1), dy2=z(B, 2 * d.P2h, 2 * d.P2w, C2),
+                    g1=z(B, d.P1h, d.P1w, C1), idx1=z(B, d.P1h, d.P1w, C1, dt=torch.uint8),
+                    idx2=z(B, d.F, dt=torch.uint8), acc=z(B, D1, dt=torch.float32))
+        self.x_dev = [z(B, H0, W0, dt=torch.float32) for _ in range(2)]
+        self.y_dev = [z(B, dt=torch.int32) for _ in range(2)]
+        self.step_out = [z(2, dt=torch.float32) for _ in range(2)]
+        offs = self._offsets()
+        steps = (CnnStep * 2)()
+        for par in range(2):
+            s = steps[par]
+            s.dims = d
+            s.x, s.labels = self.x_dev[par].data_ptr(), self.y_dev[par].data_ptr()
+            s.params = self.state.params.tensor.data_ptr()
+            s.shadow = self.state.shadow.tensor.data_ptr()
+            s.grads = self.state.grads[par].tensor.data_ptr()
+            (s.off_w1c, s.off_b1c, s.off_w2c, s.off_b2c, s.off_w1d, s.off_b1d, s.off_w2d, s.off_b2d) = offs
+            for k, t in bufs.items():
+                setattr(s, k, t.data_ptr())
+            s.metrics = self.metrics_dev.data_ptr()
+            s.step_out = self.step_out[par].data_ptr()
+            s.dense1_ksplit = max(1, d.F // 64)
+        ars = (FusedArParams * 2)(self.state.struct(0), self.state.struct(1))
+        prog = C.c_void_p()
+        use_graph = int(os.environ.get("TFDL_USE_GRAPH", "1"))
+        _lib.check(self.lib.tfdl_cnn_program_create(steps, ars, self.state.algo, use_graph, C.byref(prog)),
+                   "cnn_program_create")
+        self._prog, self._B, self._dims = prog, B, d
+        self._keep = [bufs, steps, ars]
+        self.rec_bytes = B * H0 * W0 * 4 + B * 4
+        n_rec = max(2, self.CHUNK)
+        self.ring = torch.empty((n_rec, self.rec_bytes), dtype=torch.uint8).pin_memory()
+        self.host_out = torch.zeros((n_rec, 2), dtype=torch.float32).pin_memory()
+        # the executor alternates parity with its own step counter, which restarts at 0: both gradient
+        # buffers must be clean and the device epoch is only used for flag values
+        for g in self.state.grads:
+            g.tensor.zero_()
+        torch.cuda.synchronize(dev)
+
+    # ------------------------------------------------------------------------------------------
+    def pack_record(self, slot: int, x: np.ndarray, y: np.ndarray) -> None:
+        rec = self.ring[slot].numpy()
+        B, (H0, W0) = self._B, self.shape[:2]
+        nx = B * H0 * W0 * 4
+        rec[:nx].view(np.float32)[:] = np.asarray(x, dtype=np.float32).reshape(-1)
+        rec[nx:].view(np.int32)[:] = np.asarray(y).reshape(-1).astype(np.int32, copy=False)
+
+    def run_pinned(self, records: torch.Tensor, n_steps: int, host_out: Optional[torch.Tensor] = None) -> None:
+        """Drive n_steps steps from a pinned [n_records, rec_bytes] uint8 tensor (asynchronous)."""
+        assert records.is_pinned() and records.shape[1] == self.rec_bytes
+        if self.model.optimizer.learning_rate != self._lr:
+            self.hyperparams_changed()
+        out_ptr = host_out.data_ptr() if host_out is not None else None
+        self.stream.wait_stream(torch.cuda.current_stream(self.device))
+        _lib.check(self.lib.tfdl_cnn_program_run(self._prog, records.data_ptr(), records.shape[0], n_steps, out_ptr,
+                                                 self.stream.cuda_stream), "cnn_program_run")
+        self.model.optimizer.iterations += n_steps
+
+    def run_device(self, records: torch.Tensor, n_steps: int) -> None:
+        """Drive n_steps steps from records already on the device ([n_records, rec_bytes] uint8)."""
+        assert records.is_cuda and records.shape[1] == self.rec_bytes
+        self.lib.tfdl_cnn_program_run_device.argtypes = [C.c_void_p, C.c_void_p, C.c_int64, C.c_int64, C.c_void_p]
+        self.stream.wait_stream(torch.cuda.current_stream(self.device))
+        _lib.check(self.lib.tfdl_cnn_program_run_device(self._prog, records.data_ptr(), records.shape[0], n_steps,
+                                                        self.stream.cuda_stream), "cnn_program_run_device")
+        self.model.optimizer.iterations += n_steps
+
+    def prepare(self, batch_size: int) -> None:
+        """Build (or rebuild) the step program for a per-replica batch size."""
+        if self._B != batch_size:
+            self._build_program(batch_size)
+
+    def _split(self, batch: Any) -> Tuple[np.ndarray, np.ndarray]:
+        x, y = batch[0], batch[1]
+        return np.asarray(x), np.asarray(y)
+
+    def train_chunk(self, batches: List[PerReplica]) -> None:
+        """Train on consecutive batches without returning to Python between steps."""
+        i = 0
+        while i < len(batches):
+            x, y = self._split(batches[i][0])
+            B = x.shape[0]
+            if B == 0:
+                i += 1
+                continue
+            if B % 16 != 0:
+                self._fallback_step(batches[i])
+                i += 1
+                continue
+            if self._B != B:
+                self._build_program(B)
+            k = 0
+            while i + k < len(batches) and k < self.ring.shape[0]:
+                xb, yb = self._split(batches[i + k][0])
+                if xb.shape[0] != B:
+                    break
+                self.pack_record(k, xb, yb)
+                k += 1
+            self.run_pinned(self.ring, k, self.host_out)
+            # the ring is reused by the next chunk: wait for this chunk's H2D copies (not for Python's sake)
+            self.stream.synchronize()
+            i += k
+
+    def train_step(self, batches: PerReplica) -> None:
+        self.train_chunk([batches])
+
+    def last_step_out(self) -> Tuple[float, float]:
+        self.stream.synchronize()
+        return float(self.host_out[0, 0]), float(self.host_out[0, 1])
+
+    # ------------------------------------------------------------------------------------------
+    def flush_metrics(self) -> None:
+        """Fold the device-side (loss sum, correct, examples) counters into the Keras metric objects."""
+        self.stream.synchronize()
+        m = self.metrics_dev.cpu()
+        if float(m[2]) == 0.0:
+            return
+        self.metrics_dev.zero_()
+        self.model.loss_tracker.add(0, float(m[0]), float(m[2]))
+        for met in self.model.compiled_metrics:
+            met.add(0, float(m[1]), float(m[2]))
+
+    def _torch(self) -> Any:
+        if self._torch_engine is None:
+            from .engine import TorchEngine
+
+            self._torch_engine = TorchEngine(self.model)
+        return self._torch_engine
+
+    def _fallback_step(self, batches: PerReplica) -> None:
+        """Ragged batch: one portable step on the shared arena, then resynchronise the native state."""
+        self.flush_metrics()
+        self.stream.synchronize()
+        self._torch().train_step(batches)
+        torch.cuda.current_stream(self.device).synchronize()
+        for g in self.state.grads:
+            g.tensor.zero_()
+        self.state.refresh_shadow()
+
+    def test_step(self, batches: PerReplica) -> None:
+        self._torch().test_step(batches)
+
+    def predict_step(self, x: np.ndarray) -> np.ndarray:
+        return self._torch().predict_step(x)
+
+    def __del__(self) -> None:  # pragma: no cover
+        try:
+            if self._prog is not None:
+                self.lib.tfdl_cnn_program_destroy(self._prog)
+        except Exception:
+            pass

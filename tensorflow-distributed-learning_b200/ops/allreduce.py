@@ -1,0 +1,242 @@
+"""Fused all-reduce + SGD over NVLink peer memory: Python side (buffers, handles, dispatch).
+
+Stands in for `NcclAllReduce` / `CollectiveCommunication.NCCL|AUTO` of the reference
+(/root/reference/README.md:17,21,23; tf_dist_example.py:12). torch.distributed's symmetric-memory
+allocator is used ONLY to allocate peer-mapped buffers and exchange their handles (including the
+NVLS multicast mapping); every byte of gradient traffic is moved by the hand-written kernels in
+csrc/kernels/allreduce.cu.
+
+Buffers per rank (all symmetric when world > 1):
+    params   fp32 master weights            grads[0], grads[1]   fp32 gradient arenas (parity double buffer)
+    shadow   bf16 copy of params            flags                3 barrier pads of MAX_BLOCKS*world u32
+Device-local: epoch / done counters, hyper-parameters {lr, momentum, nesterov, scale}, abort word.
+
+Algorithm choice (`AUTO`): the one-shot kernel moves (W-1)*S bytes per GPU but needs one barrier;
+the sliced kernels move ~2*S*(W-1)/W and need two. With S = arena bytes the crossover measured on
+8xB200 sits near 256 KB*W/(W-1); multimem replaces two-shot whenever the multicast mapping exists.
+Override with TFDL_AR_ALGO=oneshot|twoshot|multimem.
+"""
+from __future__ import annotations
+
+import ctypes as C
+import os
+from typing import Any, Dict, List, Optional, Sequence
+
+import numpy as np
+import torch
+
+from ..parallel.cross_device_ops import CrossDeviceOps
+from . import _lib
+from .structs import AR_MULTIMEM, AR_NAMES, AR_ONESHOT, AR_TWOSHOT, MAX_RANKS, FusedArParams, Hyper
+
+MAX_BLOCKS = 148
+ONESHOT_MAX_BYTES = int(os.environ.get("TFDL_AR_ONESHOT_MAX", 512 * 1024))
+
+
+def pick_algo(nbytes: int, world: int, has_multicast: bool) -> int:
+    """The reference's AUTO: choose by message size, world size and hardware (README.md:21)."""
+    forced = os.environ.get("TFDL_AR_ALGO", "").lower()
+    if forced:
+        a = {"oneshot": AR_ONESHOT, "twoshot": AR_TWOSHOT, "multimem": AR_MULTIMEM}[forced]
+        if a == AR_MULTIMEM and not has_multicast:
+            raise RuntimeError("TFDL_AR_ALGO=multimem but the symmetric allocation has no multicast mapping")
+        return a
+    if world == 1:
+        return AR_ONESHOT
+    if nbytes * (world - 1) <= ONESHOT_MAX_BYTES:
+        return AR_ONESHOT
+    return AR_MULTIMEM if has_multicast else AR_TWOSHOT
+
+
+class SymmetricBuffer:
+    """One tensor per rank, peer-mapped. world == 1: a plain device tensor."""
+
+    def __init__(self, numel: int, dtype: torch.dtype, device: torch.device, world: int, rank: int) -> None:
+        self.numel, self.dtype, self.device, self.world, self.rank = numel, dtype, device, world, rank
+        self.multicast_ptr = 0
+        if world == 1:
+            self.tensor = torch.zeros(numel, dtype=dtype, device=device)
+            self.ptrs = [self.tensor.data_ptr()]
+            self.handle = None
+            return
+        import torch.distributed as dist
+        import torch.distributed._symmetric_memory as symm_mem
+
+        group = dist.group.WORLD
+        try:
+            symm_mem.enable_symm_mem_for_group(group.group_name)
+        except Exception:
+            pass
+        self.tensor = symm_mem.empty(numel, dtype=dtype, device=device)
+        self.tensor.zero_()
+        self.handle = symm_mem.rendezvous(self.tensor, group=group)
+        self.ptrs = [int(p) for p in self.handle.buffer_ptrs]
+        try:
+            self.multicast_ptr = int(self.handle.multicast_ptr or 0)
+        except Exception:
+            self.multicast_ptr = 0
+
+    def barrier(self) -> None:
+        if self.handle is not None:
+            torch.cuda.synchronize(self.device)
+            self.handle.barrier()
+
+
+class P2PFusedAllReduce(CrossDeviceOps):
+    """Cross-device ops for one-process-per-GPU groups (and the degenerate single-GPU case)."""
+
+    name = "p2p-fused"
+
+    def __init__(self, device: torch.device, control_group: Any = None) -> None:
+        self.device = device
+        self.control = control_group
+        try:
+            import torch.distributed as dist
+
+            self.dist = dist if dist.is_initialized() else None
+        except Exception:  # pragma: no cover
+            self.dist = None
+        self.world = self.dist.get_world_size() if self.dist else 1
+        self.rank = self.dist.get_rank() if self.dist else 0
+        if self.world > MAX_RANKS:
+            raise RuntimeError(f"the fused NVLink all-reduce supports up to {MAX_RANKS} GPUs per group, got {self.world}")
+        _lib.kernels()  # fail loudly on a GPU box without the native library
+        self._arenas: List[SymmetricBuffer] = []
+        self._states: Dict[int, "FusedState"] = {}
+        self._plain: Dict[int, "FusedState"] = {}
+
+    # ---- arena allocation hook used by parallel.values.ParamArena -----------------------------
+    def alloc_arena(self, numel: int, device: torch.device) -> torch.Tensor:
+        buf = SymmetricBuffer(numel, torch.float32, device, self.world, self.rank)
+        self._arenas.append(buf)
+        return buf.tensor
+
+    def _find(self, t: torch.Tensor) -> SymmetricBuffer:
+        for b in self._arenas:
+            if b.tensor.data_ptr() == t.data_ptr():
+                return b
+        raise RuntimeError("tensor was not allocated through P2PFusedAllReduce.alloc_arena")
+
+    # ---- fused state for a (params, grads) pair ---------------------------------------------
+    def fused_state(self, params: torch.Tensor, grads: torch.Tensor, momentum: bool) -> "FusedState":
+        key = params.data_ptr()
+        if key not in self._states:
+            self._states[key] = FusedState(self, self._find(params), self._find(grads), momentum)
+        return self._states[key]
+
+    # ---- CrossDeviceOps interface (used by the torch engine on GPU and by tests) ----------------
+    def allreduce_grads(self, grads: Sequence[torch.Tensor]) -> None:
+        assert len(grads) == 1, "one replica per process on the P2P path"
+        if self.world == 1:
+            return
+        g = grads[0]
+        key = g.data_ptr()
+        if key not in self._plain:
+            self._plain[key] = FusedState(self, None, self._find(g), False, plain=True)
+        self._plain[key].allreduce_sum()
+
+    def allreduce_scalars(self, vals: np.ndarray) -> np.ndarray:
+        if self.world == 1:
+            return vals
+        t = torch.from_numpy(np.ascontiguousarray(vals, dtype=np.float64).copy()).to(self.device)
+        self.dist.all_reduce(t)  # a few scalars at epoch end, not the gradient path
+        return t.cpu().numpy()
+
+    def broadcast_params(self, params: Sequence[torch.Tensor]) -> None:
+        if self.world > 1:
+            self.dist.broadcast(params[0], src=0)
+            torch.cuda.synchronize(self.device)
+
+    def barrier(self) -> None:
+        if self.world > 1:
+            torch.cuda.synchronize(self.device)
+            self.dist.barrier()
+        if self.control is not None:
+            self.control.barrier()
+
+    def close(self) -> None:
+        if self.control is not None:
+            self.control.close()
+
+
+class FusedState:
+    """Everything the fused kernel needs for one arena: extra buffers, counters, the C struct."""
+
+    def __init__(self, ops: P2PFusedAllReduce, params: Optional[SymmetricBuffer], grads0: SymmetricBuffer,
+                 momentum: bool, plain: bool = False) -> None:
+        self.ops = ops
+        dev, W, R = ops.device, ops.world, ops.rank
+        n = grads0.numel
+        assert n % 4 == 0
+        self.n = n
+        self.params, self.grads = params, [grads0]
+        self.shadow: Optional[SymmetricBuffer] = None
+        if not plain:
+            self.grads.append(SymmetricBuffer(n, torch.float32, dev, W, R))
+            self.shadow = SymmetricBuffer(n, torch.bfloat16, dev, W, R)
+        self.mom = torch.zeros(n, dtype=torch.float32, device=dev) if momentum else None
+        self.pad_stride = MAX_BLOCKS * max(W, 1)
+        self.flags = SymmetricBuffer(3 * self.pad_stride, torch.int32, dev, W, R) if W > 1 else None
+        self.counters = torch.zeros(4, dtype=torch.int32, device=dev)  # epoch, done, abort, pad
+        self.hyper = torch.zeros(4, dtype=torch.float32, device=dev)
+        self.has_multicast = bool(W > 1 and grads0.multicast_ptr and (plain or (
+            params is not None and params.multicast_ptr and self.grads[1].multicast_ptr)))
+        self.algo = pick_algo(n * 4, W, self.has_multicast)
+        self._structs = [self._make_struct(par) for par in (0, 1)]
+        if W > 1:
+            grads0.barrier()  # every rank has zeroed its flags before anyone signals
+
+    def _make_struct(self, parity: int) -> FusedArParams:
+        p = FusedArParams()
+        W, R = self.ops.world, self.ops.rank
+        p.world, p.rank, p.n = W, R, self.n
+        for r in range(W):
+            if self.params is not None:
+                p.params[r] = self.params.ptrs[r]
+            if self.shadow is not None:
+                p.shadow[r] = self.shadow.ptrs[r]
+            for k, g in enumerate(self.grads):
+                p.grads[k][r] = g.ptrs[r]
+            if self.flags is not None:
+                p.flags[r] = self.flags.ptrs[r]
+        p.mom = self.mom.data_ptr() if self.mom is not None else None
+        p.pad_stride = self.pad_stride
+        p.max_blocks = MAX_BLOCKS
+        if self.has_multicast:
+            p.mc_params = self.params.multicast_ptr if self.params is not None else None
+            p.mc_shadow = (self.shadow.multicast_ptr or None) if self.shadow is not None else None
+            for k, g in enumerate(self.grads):
+                p.mc_grads[k] = g.multicast_ptr
+        base = self.counters.data_ptr()
+        p.epoch, p.done, p.abort_word = base, base + 4, base + 8
+        p.hyper = self.hyper.data_ptr()
+        p.parity = parity
+        return p
+
+    def struct(self, parity: int) -> FusedArParams:
+        return self._structs[parity]
+
+    def set_hyper(self, lr: float, momentum: float = 0.0, nesterov: bool = False, scale: float = 1.0) -> None:
+        self.hyper.copy_(torch.tensor([lr, momentum, 1.0 if nesterov else 0.0, scale], dtype=torch.float32))
+
+    def refresh_shadow(self) -> None:
+        """fp32 master -> bf16 shadow (after set_weights / load_weights / broadcast)."""
+        assert self.params is not None and self.shadow is not None
+        _lib.check(_lib.kernels().tfdl_cast_f32_to_bf16(_lib.ptr(self.params.tensor), _lib.ptr(self.shadow.tensor),
+                                                        C.c_int64(self.n), _lib.cur_stream()), "cast_f32_to_bf16")
+
+    def step(self, parity: int, algo: Optional[int] = None) -> None:
+        """One fused all-reduce + update on the current stream (eager; the training path captures it)."""
+        _lib.check(_lib.kernels().tfdl_fused_allreduce_sgd(C.byref(self._structs[parity]),
+                                                           self.algo if algo is None else algo, _lib.cur_stream()),
+                   "fused_allreduce_sgd")
+
+    def allreduce_sum(self, algo: Optional[int] = None) -> None:
+        a = self.algo if algo is None else algo
+        if a == AR_ONESHOT:
+            a = AR_MULTIMEM if self.has_multicast else AR_TWOSHOT
+        _lib.check(_lib.kernels().tfdl_allreduce_sum(C.byref(self._structs[0]), a, _lib.cur_stream()), "allreduce_sum")
+
+    @property
+    def algo_name(self) -> str:
+        return AR_NAMES[self.algo]

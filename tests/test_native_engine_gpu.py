@@ -1,0 +1,92 @@
+"""The native step program (CUDA graph of sm_100a kernels) against the portable torch engine."""
+import numpy as np
+import pytest
+import torch
+
+pytestmark = pytest.mark.gpu
+
+
+def _data(n, seed=0):
+    rng = np.random.default_rng(seed)
+    return rng.random((n, 28, 28, 1), dtype=np.float32), rng.integers(0, 10, size=n)
+
+
+def _model(engine, lr=0.05, momentum=0.0, seed=3):
+    import tfdl
+    from tfdl import keras
+    from tfdl.models import build_and_compile_cnn_model
+
+    keras.layers.set_init_seed(seed)
+    keras.clear_session()
+    s = tfdl.distribute.MirroredStrategy(devices=["gpu:0"])
+    with s.scope():
+        m = build_and_compile_cnn_model(learning_rate=lr, momentum=momentum)
+    m._engine_pref = engine
+    return m
+
+
+@pytest.mark.parametrize("momentum", [0.0, 0.9])
+def test_native_steps_track_torch_engine(momentum):
+    x, y = _data(64 * 4)
+    native, ref = _model("native", momentum=momentum), _model("torch", momentum=momentum)
+    for a, b in zip(native.get_weights(), ref.get_weights()):
+        np.testing.assert_array_equal(a, b)
+    w0 = ref.get_weights()
+    for i in range(4):
+        xb, yb = x[i * 64:(i + 1) * 64], y[i * 64:(i + 1) * 64]
+        ln = native.train_on_batch(xb, yb, return_dict=True)
+        lr_ = ref.train_on_batch(xb, yb, return_dict=True)
+        assert abs(ln["loss"] - lr_["loss"]) < 2e-2, (i, ln, lr_)
+        assert abs(ln["sparse_categorical_accuracy"] - lr_["sparse_categorical_accuracy"]) <= 4 / 64
+    assert native.engine_name == "NativeCnnEngine" and ref.engine_name == "TorchEngine"
+    for name, a, b, w in zip([v.name for v in ref.weights], native.get_weights(), ref.get_weights(), w0):
+        upd_ref = (b - w).astype(np.float64)
+        diff = (a - w).astype(np.float64) - upd_ref
+        rel_l2 = np.linalg.norm(diff) / (np.linalg.norm(upd_ref) + 1e-30)
+        worst = np.abs(diff).max() / (np.abs(upd_ref).max() + 1e-30)
+        # bf16 activations / activation gradients vs an fp32 reference: a few percent in the norm
+        assert rel_l2 < 0.10 and worst < 0.30, (name, rel_l2, worst)
+
+
+def test_fit_on_gpu_learns_and_uses_native_engine():
+    import tfdl
+    from tfdl import datasets
+
+    ds = datasets.load(name="mnist", as_supervised=True, synthetic_size=(4096, 64))["train"]
+    train = ds.map(lambda i, l: (tfdl.utils.cast(i, "float32") / 255, l)).cache().shuffle(4096, seed=1).batch(64).repeat()
+    m = _model("auto", lr=0.05)
+    h = m.fit(train, epochs=3, steps_per_epoch=40, verbose=0)
+    assert m.engine_name == "NativeCnnEngine"
+    assert h.history["loss"][-1] < h.history["loss"][0] * 0.7, h.history
+    assert h.history["sparse_categorical_accuracy"][-1] > 0.6, h.history
+    ev = m.evaluate(train, steps=5, return_dict=True)
+    assert ev["loss"] < h.history["loss"][0]
+
+
+def test_graph_and_eager_program_agree():
+    import os
+
+    x, y = _data(64 * 3, seed=5)
+    outs = []
+    for use_graph in ("1", "0"):
+        os.environ["TFDL_USE_GRAPH"] = use_graph
+        m = _model("native")
+        for i in range(3):
+            m.train_on_batch(x[i * 64:(i + 1) * 64], y[i * 64:(i + 1) * 64])
+        outs.append(m.get_weights())
+    os.environ.pop("TFDL_USE_GRAPH")
+    for a, b in zip(*outs):
+        # only the atomics' summation order may differ
+        np.testing.assert_allclose(a, b, rtol=0, atol=2e-5)
+
+
+def test_ragged_batch_falls_back_and_resyncs():
+    x, y = _data(64 + 40, seed=9)
+    m = _model("native")
+    m.train_on_batch(x[:64], y[:64])
+    logs = m.train_on_batch(x[64:], y[64:], return_dict=True)  # 40 is not a multiple of 16 -> torch step
+    assert np.isfinite(logs["loss"])
+    logs = m.train_on_batch(x[:64], y[:64], return_dict=True)
+    assert np.isfinite(logs["loss"])
+    eng = m._engine
+    torch.testing.assert_close(eng.state.shadow.tensor.float(), eng.state.params.tensor.bfloat16().float())
