@@ -38,6 +38,13 @@ int tfdl_gemm_bf16_gather_ex(const void* A, const void* B, float* D, void* Dh, c
                              int K, int lda, int ldb, int ldd, int a_mn, int b_mn, int relu, int k_split,
                              int n_tile, int k_block, int trans_out, void* stream);
 
+/* Small-batch Dense forward (ref: tf_dist_example.py:46-47): out[B][N] (bf16) = act(x[B][K] * W[N][K]^T + bias).
+ * Split-K tcgen05 GEMM (k_split CTAs along K, 0 = one per 64 columns) accumulating with RED into
+ * `scratch` (B*N floats, all zero on entry; handed back all zero), then bias + optional ReLU + cast.
+ * B multiple of 16 and <= 256, K multiple of 16. */
+int tfdl_dense_fwd_splitk(const void* x_bf16, const void* w_bf16, const float* bias, void* out_bf16, float* scratch,
+                          int B, int N, int K, int relu, int k_split, void* stream);
+
 /* D[M,N] = act(A[M,K] * B[N,K]^T + bias): persistent warp-specialised TMA + tcgen05 kernel
  * (128B-swizzled tiles, 4-8 stage mbarrier ring, double-buffered TMEM accumulators).
  * act: 0 none, 1 relu, 2 gelu(tanh). K, lda, ldb % 8 == 0; A, B 16-byte aligned. */

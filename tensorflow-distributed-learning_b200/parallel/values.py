@@ -132,7 +132,9 @@ class MirroredVariable:
         if not self._views:
             return self._init.copy()
         a = self._views[replica].detach().cpu().numpy()
-        return a if self.spec.to_keras is None else np.ascontiguousarray(np.transpose(a, self.spec.to_keras))
+        if self.spec.to_keras is None:
+            return a.copy()  # never hand out a view of the live arena
+        return np.ascontiguousarray(np.transpose(a, self.spec.to_keras))
 
     def value(self, replica: int = 0) -> torch.Tensor:
         """Storage-layout tensor of one replica (a view into its arena)."""

@@ -71,3 +71,20 @@ def test_tma_gemm_bias_act_bf16():
         out = gemm_tma(a, b, bias=bias, act=act)
         ref = f(a.float() @ b.float().t() + bias)
         torch.testing.assert_close(out.float(), ref, rtol=2e-2, atol=0.15)
+
+
+@pytest.mark.parametrize("B,N,K,relu", [(64, 128, 1600, True), (16, 10 * 16, 128, False), (256, 256, 512, True)])
+def test_dense_forward_splitk_scratch_roundtrip(B, N, K, relu):
+    from tfdl.ops.dense import dense_forward
+
+    torch.manual_seed(11)
+    x = (torch.randn(B, K, device="cuda") * 0.5).bfloat16()
+    w = (torch.randn(N, K, device="cuda") * 0.1).bfloat16()
+    bias = torch.randn(N, device="cuda")
+    scratch = torch.zeros(B * N, device="cuda")
+    for _ in range(2):  # the scratch comes back zeroed, so it can be reused as is
+        out = dense_forward(x, w, bias, relu=relu, scratch=scratch)
+        ref = x.float() @ w.float().t() + bias
+        ref = torch.relu(ref) if relu else ref
+        torch.testing.assert_close(out.float(), ref, rtol=2e-2, atol=0.1)
+        assert torch.count_nonzero(scratch) == 0
