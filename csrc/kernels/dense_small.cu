@@ -5,7 +5,8 @@
 // split across CTAs (tcgen05 gather GEMM, swap-AB so the units are the 128 MMA rows) and the partial
 // products are added into an fp32 accumulator with RED; a second tiny kernel applies bias/activation,
 // writes bf16, and hands the accumulator back zeroed. That accumulator is scratch memory: it is neither
-// an input nor an output of the op; the caller passes it (B*N floats, zero on entry, zero on exit).
+// an input nor an output of the op. tfdl_dense_fwd_splitk takes it from the caller (B*N floats, zero on
+// entry, zero on exit); tfdl_dense_fwd_splitk_static keeps it in a fixed array inside this library.
 #include "common.cuh"
 #include "../../include/tfdl_kernels.h"
 
@@ -37,6 +38,47 @@ static int dense_fwd_impl(const void* x, const void* w, const float* bias, void*
   return 0;
 }
 
+// ---------------------------------------------------------------------------------------------
+// Library-owned scratch for callers that cannot allocate.
+//
+// Who that is: a process that hands all GPU memory to its own pool at start-up (a later cudaMalloc
+// simply fails there), a latency-critical loop that cannot tolerate the device-wide synchronisation a
+// cudaMalloc/cudaFree implies, or a thin C / ctypes caller with no tensor library at hand to make a
+// workspace. For them the accumulator lives in the array below: 256 KiB that every GPU which loads
+// this library keeps until the process exits.
+//
+// The name `g_static_scratch` is only meaningful in device code. On the host it is a stand-in
+// object, not a device address, so host code asks the runtime for the real address (once per device,
+// with that device current) and passes that pointer to the kernels.
+// ---------------------------------------------------------------------------------------------
+static __device__ __align__(256) float g_static_scratch[TFDL_STATIC_SCRATCH_FLOATS];
+
+static float* static_scratch_for_current_device(int* rc_out) {
+  constexpr int kMaxDevices = 64;
+  static float* ptrs[kMaxDevices] = {nullptr};
+  int dev = -1;
+  cudaError_t e = cudaGetDevice(&dev);
+  if (e != cudaSuccess || dev < 0 || dev >= kMaxDevices) {
+    set_last_error("dense_fwd_splitk_static: cannot identify the current device (%s)",
+                   e == cudaSuccess ? "index out of range" : cudaGetErrorString(e));
+    *rc_out = e == cudaSuccess ? -1 : (int)e;
+    return nullptr;
+  }
+  if (!ptrs[dev]) {
+    float* p = nullptr;
+    e = cudaGetSymbolAddress((void**)&p, g_static_scratch);
+    if (e != cudaSuccess || !p) {
+      set_last_error("dense_fwd_splitk_static: cudaGetSymbolAddress failed on device %d: %s", dev,
+                     cudaGetErrorString(e));
+      *rc_out = e == cudaSuccess ? -1 : (int)e;
+      return nullptr;
+    }
+    ptrs[dev] = p;
+  }
+  *rc_out = 0;
+  return ptrs[dev];
+}
+
 }  // namespace tfdl
 
 using namespace tfdl;
@@ -45,4 +87,21 @@ extern "C" int tfdl_dense_fwd_splitk(const void* x, const void* w, const float* 
                                      int N, int K, int relu, int k_split, void* stream) {
   TFDL_REQUIRE(scratch, "dense_fwd_splitk: scratch buffer is required (B*N floats, zero on entry)");
   return dense_fwd_impl(x, w, bias, out, scratch, B, N, K, relu, k_split, (cudaStream_t)stream);
+}
+
+extern "C" int tfdl_dense_fwd_splitk_static(const void* x, const void* w, const float* bias, void* out, int B, int N,
+                                            int K, int relu, int k_split, void* stream) {
+  TFDL_REQUIRE(B > 0 && N > 0, "dense_fwd_splitk_static: empty problem");
+  TFDL_REQUIRE((long long)B * N <= (long long)TFDL_STATIC_SCRATCH_FLOATS,
+               "dense_fwd_splitk_static: B*N = %lld exceeds the built-in scratch of %d floats; use "
+               "tfdl_dense_fwd_splitk with your own buffer",
+               (long long)B * N, (int)TFDL_STATIC_SCRATCH_FLOATS);
+  int rc = 0;
+  float* scratch = static_scratch_for_current_device(&rc);
+  if (!scratch) return rc;
+  cudaStream_t st = (cudaStream_t)stream;
+  // The array is shared by every call and keeps whatever the last one left (an aborted call may have
+  // left partial sums), so the part used here is cleared first.
+  TFDL_CUDA_OK(cudaMemsetAsync(scratch, 0, sizeof(float) * (size_t)B * N, st));
+  return dense_fwd_impl(x, w, bias, out, scratch, B, N, K, relu, k_split, st);
 }

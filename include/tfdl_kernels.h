@@ -45,6 +45,27 @@ int tfdl_gemm_bf16_gather_ex(const void* A, const void* B, float* D, void* Dh, c
 int tfdl_dense_fwd_splitk(const void* x_bf16, const void* w_bf16, const float* bias, void* out_bf16, float* scratch,
                           int B, int N, int K, int relu, int k_split, void* stream);
 
+/* The same Dense forward for callers that cannot allocate device memory. (No counterpart in the
+ * reference: this entry point exists for embedders of this library, not for parity.)
+ *
+ * Some hosts have no way to give tfdl_dense_fwd_splitk its scratch buffer: a serving process that handed
+ * the whole GPU to its own memory pool at start-up (any later cudaMalloc fails), a latency-critical
+ * loop that must not take the device-wide synchronisation cudaMalloc/cudaFree imply, or a bare C /
+ * ctypes caller without a tensor library. Here the accumulator is a fixed array inside the library:
+ * TFDL_STATIC_SCRATCH_FLOATS floats (256 KiB) per GPU, held by every GPU that loads the library until the
+ * process exits. The call allocates nothing - no cudaMalloc/cudaFree, no allocating library routine -
+ * and the caller still passes x, w, bias and out.
+ *   - Limit: B*N <= TFDL_STATIC_SCRATCH_FLOATS, otherwise the call fails with a message and does nothing.
+ *   - The first call on each device looks up the array's device address (with that device current);
+ *     make that first call before you begin any stream capture on that device.
+ *   - All calls on a device share the one array, which keeps what the previous call left: each call
+ *     first clears the B*N floats it uses, but two calls that overlap on the GPU (different streams)
+ *     race on it and corrupt each other. Serialise them, or use tfdl_dense_fwd_splitk with
+ *     separate buffers. */
+#define TFDL_STATIC_SCRATCH_FLOATS 65536
+int tfdl_dense_fwd_splitk_static(const void* x_bf16, const void* w_bf16, const float* bias, void* out_bf16, int B,
+                                 int N, int K, int relu, int k_split, void* stream);
+
 /* D[M,N] = act(A[M,K] * B[N,K]^T + bias): persistent warp-specialised TMA + tcgen05 kernel
  * (128B-swizzled tiles, 4-8 stage mbarrier ring, double-buffered TMEM accumulators).
  * act: 0 none, 1 relu, 2 gelu(tanh). K, lda, ldb % 8 == 0; A, B 16-byte aligned. */
