@@ -107,10 +107,10 @@ class NativeCnnEngine:
         arena = model.arenas[0]
         ops = self.strategy.cross_device_ops
         if not isinstance(ops, P2PFusedAllReduce):
-            ops = P2PFusedAllReduce(self.device)
-            if ops.world != 1:
+            if self.strategy.num_workers != 1:
                 raise RuntimeError("a multi-process GPU group must be created through MirroredStrategy / "
                                    "MultiWorkerMirroredStrategy so that its arenas are peer-mapped")
+            ops = P2PFusedAllReduce(self.device, single=True)
             for t in (arena.params, arena.grads):
                 b = SymmetricBuffer.__new__(SymmetricBuffer)
                 b.numel, b.dtype, b.device, b.world, b.rank = t.numel(), t.dtype, t.device, 1, 0

@@ -87,15 +87,17 @@ class P2PFusedAllReduce(CrossDeviceOps):
 
     name = "p2p-fused"
 
-    def __init__(self, device: torch.device, control_group: Any = None) -> None:
+    def __init__(self, device: torch.device, control_group: Any = None, single: bool = False) -> None:
         self.device = device
         self.control = control_group
-        try:
-            import torch.distributed as dist
+        self.dist = None
+        if not single:  # single=True: a private one-GPU instance even if a process group exists
+            try:
+                import torch.distributed as dist
 
-            self.dist = dist if dist.is_initialized() else None
-        except Exception:  # pragma: no cover
-            self.dist = None
+                self.dist = dist if dist.is_initialized() else None
+            except Exception:  # pragma: no cover
+                self.dist = None
         self.world = self.dist.get_world_size() if self.dist else 1
         self.rank = self.dist.get_rank() if self.dist else 0
         if self.world > MAX_RANKS:

@@ -1,0 +1,129 @@
+"""Multi-GPU checks, one process per GPU (launched by tests/test_multigpu.py through torch.distributed.run).
+Prints one JSON line per rank-0 check; exits non-zero on the first failed assertion."""
+import json
+import os
+import sys
+
+import numpy as np
+import torch
+
+ROOT = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
+sys.path.insert(0, ROOT)
+
+import tfdl  # noqa: E402
+from tfdl import keras  # noqa: E402
+from tfdl.ops.allreduce import P2PFusedAllReduce  # noqa: E402
+from tfdl.ops.structs import AR_MULTIMEM, AR_NAMES, AR_ONESHOT, AR_TWOSHOT  # noqa: E402
+
+
+def main() -> None:
+    import torch.distributed as dist
+
+    strategy = tfdl.distribute.MirroredStrategy()
+    rank, world = strategy.worker_index, strategy.num_workers
+    dev = strategy.local_devices[0]
+    ops = strategy.cross_device_ops
+    assert isinstance(ops, P2PFusedAllReduce) and ops.world == world
+    report = {"world": world}
+
+    # ---- fused all-reduce + SGD, every algorithm, several sizes, back-to-back steps with skewed ranks ----
+    for n in (1024, 225280, 4 * 1024 * 1024 + 64):
+        params, grads = ops.alloc_arena(n, dev), ops.alloc_arena(n, dev)
+        st = ops.fused_state(params, grads, momentum=True)
+        algos = [AR_ONESHOT, AR_TWOSHOT] + ([AR_MULTIMEM] if st.has_multicast else [])
+        report["multicast"] = bool(st.has_multicast)
+        for algo in algos:
+            torch.manual_seed(1)
+            w0 = torch.randn(n, device=dev)
+            params.copy_(w0)
+            st.mom.zero_()
+            for g in st.grads:
+                g.tensor.zero_()
+            st.set_hyper(0.1, 0.9, False, 1.0 / world)
+            torch.cuda.synchronize(dev)
+            dist.barrier()
+            w_ref, v_ref = w0.clone(), torch.zeros(n, device=dev)
+            steps = 6
+            all_g = [[torch.Generator(device="cpu").manual_seed(100 * s + r) for r in range(world)] for s in range(steps)]
+            for s in range(steps):
+                par = s & 1
+                gs = [torch.randn(n, generator=all_g[s][r]).to(dev) for r in range(world)]
+                if (s + rank) % 2 == 0:
+                    torch.cuda._sleep(20_000_000)  # skew the ranks: ~10 ms
+                st.grads[par].tensor.copy_(gs[rank])
+                st.step(par, algo)  # no host sync between steps
+                gsum = gs[0].clone()
+                for r in range(1, world):
+                    gsum += gs[r]
+                gsum *= 1.0 / world
+                v_ref = 0.9 * v_ref - 0.1 * gsum
+                w_ref = w_ref + v_ref
+            torch.cuda.synchronize(dev)
+            if algo == AR_ONESHOT:
+                torch.testing.assert_close(params, w_ref, rtol=1e-5, atol=1e-5)
+            else:
+                torch.testing.assert_close(params, w_ref, rtol=1e-4, atol=1e-4)  # in-switch / sliced order differs
+            torch.testing.assert_close(st.shadow.tensor.float(), params.bfloat16().float(), rtol=0, atol=0)
+            gathered = [torch.empty_like(params) for _ in range(world)]
+            dist.all_gather(gathered, params)
+            for r in range(1, world):
+                assert torch.equal(gathered[0], gathered[r]), f"rank {r} diverged ({AR_NAMES[algo]}, n={n})"
+            report[f"fused_{AR_NAMES[algo]}_{n}"] = "ok"
+
+    # ---- plain in-place sum (odd sizes) --------------------------------------------------------------
+    for n in (4, 1000, 1 << 20):
+        buf = ops.alloc_arena(n, dev)
+        buf.copy_(torch.arange(n, device=dev, dtype=torch.float32) * (rank + 1))
+        torch.cuda.synchronize(dev)
+        dist.barrier()
+        ops.allreduce_grads([buf])
+        ops.allreduce_grads([buf])  # twice in a row: x -> x*T -> x*T*world
+        torch.cuda.synchronize(dev)
+        tot = sum(r + 1 for r in range(world))
+        torch.testing.assert_close(buf, torch.arange(n, device=dev, dtype=torch.float32) * tot * world, rtol=1e-6, atol=0)
+    report["plain_sum"] = "ok"
+
+    # ---- training: N GPUs at global batch 64*N == one GPU fed the same global batches -----------------------
+    from tfdl.models import build_and_compile_cnn_model
+
+    keras.clear_session()
+    keras.layers.set_init_seed(7 + rank)  # different local inits: the chief's broadcast must win
+    with strategy.scope():
+        model = build_and_compile_cnn_model(learning_rate=0.05, momentum=0.9)
+    rng = np.random.default_rng(0)
+    G = 64 * world
+    x, y = rng.random((G * 6, 28, 28, 1), dtype=np.float32), rng.integers(0, 10, size=G * 6)
+    ds = tfdl.data.Dataset.from_tensor_slices((x, y)).batch(G)
+    o = tfdl.data.Options()
+    o.experimental_distribute.auto_shard_policy = tfdl.data.AutoShardPolicy.DATA
+    h = model.fit(ds.with_options(o), epochs=2, verbose=0)
+    assert model.engine_name == "NativeCnnEngine"
+    ws = [torch.from_numpy(w).to(dev) for w in model.get_weights()]
+    for w in ws:
+        got = [torch.empty_like(w) for _ in range(world)]
+        dist.all_gather(got, w.contiguous())
+        for r in range(1, world):
+            assert torch.equal(got[0], got[r]), "mirrored variables diverged"
+    report["train_identical"] = "ok"
+    report["train_loss"] = h.history["loss"]
+    report["algo"] = model._engine.algo_name
+    if rank == 0:
+        # single-GPU reference on the same global batches (per-replica 64*world is a multiple of 16)
+        keras.clear_session()
+        keras.layers.set_init_seed(7)
+        solo = tfdl.distribute.MirroredStrategy(devices=[f"gpu:{dev.index}"])
+        with solo.scope():
+            ref = build_and_compile_cnn_model(learning_rate=0.05, momentum=0.9)
+        hr = ref.fit(ds, epochs=2, verbose=0)
+        np.testing.assert_allclose(h.history["loss"], hr.history["loss"], rtol=2e-2)
+        for a, b, v in zip(model.get_weights(), ref.get_weights(), ref.weights):
+            den = np.abs(b).max() + 1e-9
+            assert np.abs(a - b).max() / den < 5e-2, v.name
+        report["train_matches_single_gpu"] = "ok"
+        print("MGPU_REPORT " + json.dumps(report), flush=True)
+    dist.barrier()
+    strategy.close()
+
+
+if __name__ == "__main__":
+    main()
