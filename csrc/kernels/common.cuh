@@ -286,16 +286,18 @@ __device__ __forceinline__ void stage_kmajor(uint32_t smem_base, const __nv_bflo
   }
 }
 // Stage an MN-major operand: global is [K][cols] (pitch ld); tile covers cols [c0, c0+tile_cols).
+// A quarter-warp writes the 8 k-rows of one core matrix (128 contiguous bytes: conflict-free).
 __device__ __forceinline__ void stage_mnmajor(uint32_t smem_base, const __nv_bfloat16* X, int ld, int c0,
                                               int cols_valid_end, int k0, int tile_cols, int kcols) {
   const int kchunks = kcols >> 3;
   const int groups = tile_cols >> 3;
   const int total = groups * kcols;
   for (int i = threadIdx.x; i < total; i += blockDim.x) {
-    // consecutive threads -> consecutive MN chunks of one k row (coalesced 16B global reads)
-    int g = i % groups;
-    int k = i / groups;
-    bool ok = (c0 + g * 8) < cols_valid_end;
+    const int k_in = i & 7;
+    const int rest = i >> 3;
+    const int g = rest % groups;
+    const int k = (rest / groups) * 8 + k_in;
+    const bool ok = (c0 + g * 8) < cols_valid_end;
     const __nv_bfloat16* src = ok ? X + (size_t)(k0 + k) * ld + c0 + g * 8 : X;
     cp_async16(smem_base + core_off_mnmajor(k, g, kchunks), src, ok);
   }

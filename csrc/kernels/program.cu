@@ -29,7 +29,7 @@ extern "C" int tfdl_cnn_step_launch(const TfdlCnnStep* s, void* stream, void* si
   float* G = s->grads;
   const bool forked = sd != nullptr && sd != st && ef != nullptr && ej != nullptr;
   // ---- forward ----
-  TFDL_RC(tfdl_cnn_conv1_fwd(s->x, P + s->off_w1c, P + s->off_b1c, s->a1, s->idx1, d, st));
+  TFDL_RC(tfdl_cnn_conv1_fwd(s->x, P + s->off_w1c, P + s->off_b1c, s->a1, s->idx1, s->step_out, d, st));
   TFDL_RC(tfdl_cnn_conv2_fwd(s->a1, H + s->off_w2c, P + s->off_b2c, s->a2, s->idx2, d, st));
   // dense1: acc[s][u] += sum_k W1[u][k] a2[s][k]   (swap-AB: M = units, N = samples, split-K, transposed RED)
   TFDL_RC(tfdl_gemm_bf16_gather_ex(H + s->off_w1d, s->a2, s->acc, nullptr, nullptr, d->D1, d->B, d->F, d->F, d->F,
@@ -42,9 +42,10 @@ extern "C" int tfdl_cnn_step_launch(const TfdlCnnStep* s, void* stream, void* si
     TFDL_CUDA_OK(cudaStreamWaitEvent(sd, ef, 0));
   }
   cudaStream_t off = forked ? sd : st;
-  // dW1[u][f] = sum_s dh[s][u] a2[s][f]: both operands MN-major (off the critical path)
-  TFDL_RC(tfdl_gemm_bf16_gather_ex(s->dh, s->a2, G + s->off_w1d, nullptr, nullptr, d->D1, d->F, d->B, d->D1, d->F,
-                                   d->F, 1, 1, 0, 1, 64, 0, 0, off));
+  // dW1[u][f] = sum_s a2[s][f] dh[s][u]: both operands MN-major; rows = features so that the transposed
+  // store walks f (the contiguous index of dW1) across the lanes of a warp (off the critical path)
+  TFDL_RC(tfdl_gemm_bf16_gather_ex(s->a2, s->dh, G + s->off_w1d, nullptr, nullptr, d->F, d->D1, d->B, d->F, d->D1,
+                                   d->F, 1, 1, 0, 1, 64, 0, 1, off));
   TFDL_RC(tfdl_cnn_dense1_dgrad(s->dh, H + s->off_w1d, s->a2, s->idx2, s->dy2, d, st));
   if (forked) {
     // conv2 wgrad needs dy2 (main branch) but nothing downstream needs it before the all-reduce

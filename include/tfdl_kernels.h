@@ -128,10 +128,12 @@ typedef struct {
   int nrep;       /* replicas in sync: the loss is mean over the replica batch / nrep */
 } TfdlCnnDims;
 
+/* clear2: optional pointer to two floats that the kernel zeroes (the step's loss/accuracy slot). */
 int tfdl_cnn_conv1_fwd(const float* x, const float* w /*[C1][9]*/, const float* b, void* a1_bf16, uint8_t* idx1,
-                       const TfdlCnnDims* d, void* stream);
+                       float* clear2, const TfdlCnnDims* d, void* stream);
 int tfdl_cnn_conv2_fwd(const void* a1_bf16, const void* w2_bf16 /*[C2][9*C1]*/, const float* b2, void* a2_bf16,
                        uint8_t* idx2, const TfdlCnnDims* d, void* stream);
+/* g_w2 / g_b2 / g_b1, metrics and step_out are ACCUMULATED (the caller clears them between steps). */
 int tfdl_cnn_head(float* acc /*[B][D1], re-zeroed*/, const float* b1, const float* w2 /*[NC][D1]*/, const float* b2,
                   const int* labels, void* dh_bf16, float* g_w2, float* g_b2, float* g_b1, float* metrics /*[3]*/,
                   float* step_out /*[2]: mean loss, accuracy*/, const TfdlCnnDims* d, void* stream);
@@ -187,6 +189,15 @@ int tfdl_cnn_program_run_device(TfdlCnnProgram* p, const void* dev_batches, int6
                                 void* stream);
 int64_t tfdl_cnn_program_steps_done(const TfdlCnnProgram* p);
 int64_t tfdl_cnn_program_launches_per_step(const TfdlCnnProgram* p);
+
+
+/* ---- hardware probes (csrc/kernels/probe.cu): pin down descriptor semantics the conv kernels rely on */
+int tfdl_probe_shifted_umma(const void* A_bf16 /*[rows][kc]*/, const void* B_bf16 /*[N][kc]*/, float* D /*[128][N]*/,
+                            int rows, int N, int kc /*64: 128B swizzle, 32: 64B swizzle*/, int shift,
+                            int base_offset_mode, void* stream);
+int tfdl_probe_mn_umma(const void* A_bf16 /*[krows][128|64]*/, const void* B_bf16 /*[krows+64][32]*/, float* D /*[128][32]*/,
+                       int krows, int shift, int lbo_mode, void* stream);
+int tfdl_probe_tma_coremajor(const void* W_bf16 /*[rows][K]*/, void* out_bf16 /*rows*K*/, int rows, int K, void* stream);
 
 #ifdef __cplusplus
 }

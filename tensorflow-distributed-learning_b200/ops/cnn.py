@@ -19,7 +19,7 @@ def conv1_fwd(x: torch.Tensor, w: torch.Tensor, b: torch.Tensor, d: CnnDims) -> 
     """x [B,H0,W0] fp32, w [C1,9] fp32 (OHWI with I=1), b [C1] -> a1 bf16 [B,P1h,P1w,C1], idx1 uint8."""
     a1 = torch.empty((d.B, d.P1h, d.P1w, d.C1), dtype=torch.bfloat16, device=x.device)
     idx = torch.empty((d.B, d.P1h, d.P1w, d.C1), dtype=torch.uint8, device=x.device)
-    _lib.check(_lib.kernels().tfdl_cnn_conv1_fwd(_p(x), _p(w), _p(b), _p(a1), _p(idx), C.byref(d), _s()), "conv1_fwd")
+    _lib.check(_lib.kernels().tfdl_cnn_conv1_fwd(_p(x), _p(w), _p(b), _p(a1), _p(idx), None, C.byref(d), _s()), "conv1_fwd")
     return a1, idx
 
 
@@ -35,9 +35,9 @@ def head(acc: torch.Tensor, b1: torch.Tensor, w2: torch.Tensor, b2: torch.Tensor
     """acc fp32 [B,D1] (zeroed on return), returns dh bf16, g_w2, g_b2, g_b1, metrics[3], step_out[2]."""
     dev = acc.device
     dh = torch.empty((d.B, d.D1), dtype=torch.bfloat16, device=dev)
-    g_w2 = torch.empty((d.NC, d.D1), device=dev)
-    g_b2 = torch.empty((d.NC,), device=dev)
-    g_b1 = torch.empty((d.D1,), device=dev)
+    g_w2 = torch.zeros((d.NC, d.D1), device=dev)  # the kernel accumulates into these
+    g_b2 = torch.zeros((d.NC,), device=dev)
+    g_b1 = torch.zeros((d.D1,), device=dev)
     metrics = torch.zeros(3, device=dev)
     step_out = torch.zeros(2, device=dev)
     _lib.check(_lib.kernels().tfdl_cnn_head(_p(acc), _p(b1), _p(w2), _p(b2), _p(labels), _p(dh), _p(g_w2), _p(g_b2),
