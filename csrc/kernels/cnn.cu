@@ -332,7 +332,7 @@ template <int C2, int D1>
 __global__ void __launch_bounds__(TC_THREADS, 1)
 dense1_dgrad_kernel(const __nv_bfloat16* __restrict__ dh, const __nv_bfloat16* __restrict__ w1h /*[D1][F]*/,
                     const __nv_bfloat16* __restrict__ a2, const uint8_t* __restrict__ idx2,
-                    __nv_bfloat16* __restrict__ dy2 /*[B][2P2h][2P2w][C2]*/, TfdlCnnDims d) {
+                    __nv_bfloat16* __restrict__ dy2 /*[B][P1h][P1w][C2], only [0:2P2h, 0:2P2w] written*/, TfdlCnnDims d) {
   extern __shared__ __align__(1024) uint8_t smem[];
   __shared__ uint64_t bar;
   __shared__ uint32_t slot;
@@ -352,7 +352,7 @@ dense1_dgrad_kernel(const __nv_bfloat16* __restrict__ dh, const __nv_bfloat16* _
   const int lq = tc.warp & 3;
   const int s = s0 + lq * 32 + (int)lane_id();
   const uint32_t t_row = tc.tmem + ((uint32_t)(lq * 32) << 16);
-  const int ph = pix / d.P2w, pw = pix % d.P2w, R = 2 * d.P2h, R2 = 2 * d.P2w;
+  const int ph = pix / d.P2w, pw = pix % d.P2w;
   mbar_wait(&bar, 0);
   tc_fence_after_sync();
 #pragma unroll 1
@@ -382,7 +382,7 @@ dense1_dgrad_kernel(const __nv_bfloat16* __restrict__ dh, const __nv_bfloat16* _
           const bool on1 = ((a_pair >> 16) & 0x7FFFu) != 0 && !((a_pair >> 16) & 0x8000u) && i1 == (uint32_t)q;
           outw[i >> 1] = pack_bf16x2(on0 ? __uint_as_float(v[i]) : 0.f, on1 ? __uint_as_float(v[i + 1]) : 0.f);
         }
-        __nv_bfloat16* dst = dy2 + (((size_t)s * R + 2 * ph + (q >> 1)) * R2 + 2 * pw + (q & 1)) * C2 + c0;
+        __nv_bfloat16* dst = dy2 + (((size_t)s * d.P1h + 2 * ph + (q >> 1)) * d.P1w + 2 * pw + (q & 1)) * C2 + c0;
 #pragma unroll
         for (int k = 0; k < 4; ++k)
           reinterpret_cast<uint4*>(dst)[k] = make_uint4(outw[4 * k], outw[4 * k + 1], outw[4 * k + 2], outw[4 * k + 3]);
@@ -397,6 +397,7 @@ dense1_dgrad_kernel(const __nv_bfloat16* __restrict__ dh, const __nv_bfloat16* _
 // GEMM view: M = (tap,ci) = 9*C1 rows in ceil(9*C1/128) accumulator tiles, N = C2, reduction = pixels.
 // Each CTA reduces KP = 128 pixels and adds its partial result to the gradient arena (fp32 RED).
 // Both operands are MN-major (the reduction index is the slow index of a1 and of dy2).
+// dy2 is stored on the a1 pixel grid [B][P1h][P1w][C2] (non-zero only in [0:2P2h, 0:2P2w]).
 // grid = ceil(B*R*R2 / 128), block = 256
 // =============================================================================================
 template <int C1, int C2>
@@ -436,9 +437,10 @@ conv2_wgrad_kernel(const __nv_bfloat16* __restrict__ a1, const __nv_bfloat16* __
 #pragma unroll 2
     for (int i = threadIdx.x >> 3; i < 16 * G2; i += TC_THREADS / 8) {
       const int g2 = i % G2, kg = i / G2, k = kg * 8 + k_in;
-      const int pix = blockIdx.x * KP + k;
-      const bool ok = pix < Ptot;
-      cp_async16(b_smem + g2 * (KCH * 128u) + kg * 128u + k_in * 16u, dy2 + (ok ? (size_t)pix * C2 + g2 * 8 : 0), ok);
+      const int off = rowoff[k];  // a1 and dy2 share the pixel grid: a1 offset / C1 = pixel index
+      const bool ok = off >= 0;
+      cp_async16(b_smem + g2 * (KCH * 128u) + kg * 128u + k_in * 16u,
+                 dy2 + (ok ? (size_t)(off / C1) * C2 + g2 * 8 : 0), ok);
     }
   }
   staging_done();
@@ -501,7 +503,7 @@ conv2_dgrad_kernel(const __nv_bfloat16* __restrict__ dy2, const __nv_bfloat16* _
   if (threadIdx.x < 128) {
     const int m = blockIdx.x * 128 + threadIdx.x;
     const int iw = m % d.P1w, t2 = m / d.P1w, ih = t2 % d.P1h, n = t2 / d.P1h;
-    rowbase[threadIdx.x] = m < Mtot ? (n * R + ih) * R2 + iw : -(1 << 28);  // dy2 pixel index if (ih,iw) were an output pixel
+    rowbase[threadIdx.x] = m < Mtot ? m : -(1 << 28);  // dy2 lives on the same P1h x P1w grid as a1
     rowpos[threadIdx.x] = (ih << 8) | iw;
   }
   __syncthreads();
@@ -514,7 +516,7 @@ conv2_dgrad_kernel(const __nv_bfloat16* __restrict__ dy2, const __nv_bfloat16* _
       const int pos = rowpos[r], base = rowbase[r];
       const int oh = (pos >> 8) - kh, ow = (pos & 0xFF) - kw;
       const bool ok = base >= 0 && oh >= 0 && oh < R && ow >= 0 && ow < R2;
-      const __nv_bfloat16* src = dy2 + (ok ? (size_t)(base - kh * R2 - kw) * C2 + c8 * 8 : 0);
+      const __nv_bfloat16* src = dy2 + (ok ? (size_t)(base - kh * d.P1w - kw) * C2 + c8 * 8 : 0);
       cp_async16(a_smem + core_off_kmajor(r, tap * CPT + c8, KCH), src, ok);
     }
     // B: chunk (k=(tap,co), g=ci8) <- w2h[co][tap][g*8..]; a quarter-warp fills one core matrix

@@ -30,7 +30,9 @@ extern "C" int tfdl_cnn_step_launch(const TfdlCnnStep* s, void* stream, void* si
   const bool forked = sd != nullptr && sd != st && ef != nullptr && ej != nullptr;
   // ---- forward ----
   TFDL_RC(tfdl_cnn_conv1_fwd(s->x, P + s->off_w1c, P + s->off_b1c, s->a1, s->idx1, s->step_out, d, st));
-  TFDL_RC(tfdl_cnn_conv2_fwd(s->a1, H + s->off_w2c, P + s->off_b2c, s->a2, s->idx2, d, st));
+  const bool tma = s->use_tma_conv != 0;
+  if (tma) TFDL_RC(tfdl_cnn_conv2_fwd_tma(s->a1, H + s->off_w2c, P + s->off_b2c, s->a2, s->idx2, d, st));
+  else TFDL_RC(tfdl_cnn_conv2_fwd(s->a1, H + s->off_w2c, P + s->off_b2c, s->a2, s->idx2, d, st));
   // dense1: acc[s][u] += sum_k W1[u][k] a2[s][k]   (swap-AB: M = units, N = samples, split-K, transposed RED)
   TFDL_RC(tfdl_gemm_bf16_gather_ex(H + s->off_w1d, s->a2, s->acc, nullptr, nullptr, d->D1, d->B, d->F, d->F, d->F,
                                    d->D1, 0, 0, 0, s->dense1_ksplit > 0 ? s->dense1_ksplit : 1, 0, 64, 1, st));
@@ -52,8 +54,13 @@ extern "C" int tfdl_cnn_step_launch(const TfdlCnnStep* s, void* stream, void* si
     TFDL_CUDA_OK(cudaEventRecord(ef, st));
     TFDL_CUDA_OK(cudaStreamWaitEvent(sd, ef, 0));
   }
-  TFDL_RC(tfdl_cnn_conv2_wgrad(s->a1, s->dy2, G + s->off_w2c, G + s->off_b2c, d, off));
-  TFDL_RC(tfdl_cnn_conv2_dgrad(s->dy2, H + s->off_w2c, s->a1, s->g1, d, st));
+  if (tma) {
+    TFDL_RC(tfdl_cnn_conv2_wgrad_tma(s->a1, s->dy2, G + s->off_w2c, G + s->off_b2c, d, off));
+    TFDL_RC(tfdl_cnn_conv2_dgrad_tma(s->dy2, H + s->off_w2c, s->a1, s->g1, d, st));
+  } else {
+    TFDL_RC(tfdl_cnn_conv2_wgrad(s->a1, s->dy2, G + s->off_w2c, G + s->off_b2c, d, off));
+    TFDL_RC(tfdl_cnn_conv2_dgrad(s->dy2, H + s->off_w2c, s->a1, s->g1, d, st));
+  }
   TFDL_RC(tfdl_cnn_conv1_wgrad(s->x, s->g1, s->idx1, G + s->off_w1c, G + s->off_b1c, d, st));
   if (forked) {
     TFDL_CUDA_OK(cudaEventRecord(ej, sd));

@@ -137,8 +137,10 @@ int tfdl_cnn_conv2_fwd(const void* a1_bf16, const void* w2_bf16 /*[C2][9*C1]*/, 
 int tfdl_cnn_head(float* acc /*[B][D1], re-zeroed*/, const float* b1, const float* w2 /*[NC][D1]*/, const float* b2,
                   const int* labels, void* dh_bf16, float* g_w2, float* g_b2, float* g_b1, float* metrics /*[3]*/,
                   float* step_out /*[2]: mean loss, accuracy*/, const TfdlCnnDims* d, void* stream);
+/* dy2 lives on the conv2 INPUT pixel grid, [B][P1h][P1w][C2]; only [0:2P2h, 0:2P2w] is ever written, the
+ * rest must stay zero (allocate it zeroed). */
 int tfdl_cnn_dense1_dgrad(const void* dh_bf16, const void* w1_bf16 /*[D1][F]*/, const void* a2_bf16,
-                          const uint8_t* idx2, void* dy2_bf16 /*[B][2P2h][2P2w][C2]*/, const TfdlCnnDims* d,
+                          const uint8_t* idx2, void* dy2_bf16 /*[B][P1h][P1w][C2]*/, const TfdlCnnDims* d,
                           void* stream);
 int tfdl_cnn_conv2_wgrad(const void* a1_bf16, const void* dy2_bf16, float* g_w2c /*[C2][9*C1], accumulated*/,
                          float* g_b2c /*accumulated*/, const TfdlCnnDims* d, void* stream);
@@ -146,6 +148,17 @@ int tfdl_cnn_conv2_dgrad(const void* dy2_bf16, const void* w2_bf16, const void* 
                          const TfdlCnnDims* d, void* stream);
 int tfdl_cnn_conv1_wgrad(const float* x, const void* g1_bf16, const uint8_t* idx1, float* g_w1c /*accumulated*/,
                          float* g_b1c /*accumulated*/, const TfdlCnnDims* d, void* stream);
+
+/* TMA-fed, im2col-free versions of the three conv2 kernels (csrc/kernels/cnn_tma.cu): one raw activation tile
+ * per image in shared memory, the 3x3 filter as nine MMAs on shifted operand descriptors. Same arguments and
+ * results as the gather versions; available when tfdl_cnn_tma_supported(d) (the reference geometry). */
+int tfdl_cnn_tma_supported(const TfdlCnnDims* d);
+int tfdl_cnn_conv2_fwd_tma(const void* a1_bf16, const void* w2_bf16, const float* b2, void* a2_bf16, uint8_t* idx2,
+                           const TfdlCnnDims* d, void* stream);
+int tfdl_cnn_conv2_dgrad_tma(const void* dy2_bf16, const void* w2_bf16, const void* a1_bf16, void* g1_bf16,
+                             const TfdlCnnDims* d, void* stream);
+int tfdl_cnn_conv2_wgrad_tma(const void* a1_bf16, const void* dy2_bf16, float* g_w2c, float* g_b2c,
+                             const TfdlCnnDims* d, void* stream);
 
 /* One training step = the 9 kernels above + the fused all-reduce/SGD, described by pointers into the
  * caller's buffers. Two descriptors (gradient-buffer parity 0 and 1) make a program. */
@@ -163,6 +176,7 @@ typedef struct {
   float* metrics;            /* [3] running loss sum / correct / examples */
   float* step_out;           /* [2] this step's mean loss and accuracy */
   int dense1_ksplit;         /* CTAs along K for dense1 forward */
+  int use_tma_conv;          /* 1: conv2 fwd/dgrad/wgrad via cnn_tma.cu (requires tfdl_cnn_tma_supported) */
 } TfdlCnnStep;
 
 /* Launch the forward+backward kernels of one step on `stream`, using `side` for the branches that are

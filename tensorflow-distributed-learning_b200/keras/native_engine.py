@@ -158,7 +158,7 @@ class NativeCnnEngine:
         dev = self.device
         bf = torch.bfloat16
         z = lambda *s, dt=bf: torch.zeros(s, dtype=dt, device=dev)  # noqa: E731
-        bufs = dict(a1=z(B, d.P1h, d.P1w, C1), a2=z(B, d.F), dh=z(B, D1), dy2=z(B, 2 * d.P2h, 2 * d.P2w, C2),
+        bufs = dict(a1=z(B, d.P1h, d.P1w, C1), a2=z(B, d.F), dh=z(B, D1), dy2=z(B, d.P1h, d.P1w, C2),
                     g1=z(B, d.P1h, d.P1w, C1), idx1=z(B, d.P1h, d.P1w, C1, dt=torch.uint8),
                     idx2=z(B, d.F, dt=torch.uint8), acc=z(B, D1, dt=torch.float32))
         self.x_dev = [z(B, H0, W0, dt=torch.float32) for _ in range(2)]
@@ -179,6 +179,8 @@ class NativeCnnEngine:
             s.metrics = self.metrics_dev.data_ptr()
             s.step_out = self.step_out[par].data_ptr()
             s.dense1_ksplit = max(1, d.F // 64)
+            s.use_tma_conv = int(bool(self.lib.tfdl_cnn_tma_supported(C.byref(d))) and
+                                 os.environ.get("TFDL_CONV_IMPL", "tma") == "tma")
         ars = (FusedArParams * 2)(self.state.struct(0), self.state.struct(1))
         prog = C.c_void_p()
         use_graph = int(os.environ.get("TFDL_USE_GRAPH", "1"))

@@ -23,11 +23,14 @@ def conv1_fwd(x: torch.Tensor, w: torch.Tensor, b: torch.Tensor, d: CnnDims) -> 
     return a1, idx
 
 
-def conv2_fwd(a1: torch.Tensor, w2h: torch.Tensor, b2: torch.Tensor, d: CnnDims) -> Tuple[torch.Tensor, torch.Tensor]:
-    """a1 bf16 [B,P1h,P1w,C1], w2h bf16 [C2,3,3,C1], b2 fp32 -> a2 bf16 [B,P2h,P2w,C2], idx2 uint8."""
+def conv2_fwd(a1: torch.Tensor, w2h: torch.Tensor, b2: torch.Tensor, d: CnnDims,
+              impl: str = "gather") -> Tuple[torch.Tensor, torch.Tensor]:
+    """a1 bf16 [B,P1h,P1w,C1], w2h bf16 [C2,3,3,C1], b2 fp32 -> a2 bf16 [B,P2h,P2w,C2], idx2 uint8.
+    impl: "gather" (cp.async im2col tile) or "tma" (im2col-free, shifted descriptors)."""
     a2 = torch.empty((d.B, d.P2h, d.P2w, d.C2), dtype=torch.bfloat16, device=a1.device)
     idx = torch.empty((d.B, d.P2h, d.P2w, d.C2), dtype=torch.uint8, device=a1.device)
-    _lib.check(_lib.kernels().tfdl_cnn_conv2_fwd(_p(a1), _p(w2h), _p(b2), _p(a2), _p(idx), C.byref(d), _s()), "conv2_fwd")
+    fn = _lib.kernels().tfdl_cnn_conv2_fwd_tma if impl == "tma" else _lib.kernels().tfdl_cnn_conv2_fwd
+    _lib.check(fn(_p(a1), _p(w2h), _p(b2), _p(a2), _p(idx), C.byref(d), _s()), "conv2_fwd")
     return a2, idx
 
 
@@ -46,22 +49,25 @@ def head(acc: torch.Tensor, b1: torch.Tensor, w2: torch.Tensor, b2: torch.Tensor
 
 
 def dense1_dgrad(dh: torch.Tensor, w1h: torch.Tensor, a2: torch.Tensor, idx2: torch.Tensor, d: CnnDims) -> torch.Tensor:
-    dy2 = torch.empty((d.B, 2 * d.P2h, 2 * d.P2w, d.C2), dtype=torch.bfloat16, device=dh.device)
+    dy2 = torch.zeros((d.B, d.P1h, d.P1w, d.C2), dtype=torch.bfloat16, device=dh.device)  # conv2 input grid
     _lib.check(_lib.kernels().tfdl_cnn_dense1_dgrad(_p(dh), _p(w1h), _p(a2), _p(idx2), _p(dy2), C.byref(d), _s()),
                "dense1_dgrad")
     return dy2
 
 
-def conv2_wgrad(a1: torch.Tensor, dy2: torch.Tensor, d: CnnDims) -> Tuple[torch.Tensor, torch.Tensor]:
+def conv2_wgrad(a1: torch.Tensor, dy2: torch.Tensor, d: CnnDims, impl: str = "gather") -> Tuple[torch.Tensor, torch.Tensor]:
+    """dy2 bf16 on the conv2 input grid [B,P1h,P1w,C2] (zero outside [0:2P2h, 0:2P2w])."""
     g_w = torch.zeros((d.C2, 3, 3, d.C1), device=a1.device)
     g_b = torch.zeros((d.C2,), device=a1.device)
-    _lib.check(_lib.kernels().tfdl_cnn_conv2_wgrad(_p(a1), _p(dy2), _p(g_w), _p(g_b), C.byref(d), _s()), "conv2_wgrad")
+    fn = _lib.kernels().tfdl_cnn_conv2_wgrad_tma if impl == "tma" else _lib.kernels().tfdl_cnn_conv2_wgrad
+    _lib.check(fn(_p(a1), _p(dy2), _p(g_w), _p(g_b), C.byref(d), _s()), "conv2_wgrad")
     return g_w, g_b
 
 
-def conv2_dgrad(dy2: torch.Tensor, w2h: torch.Tensor, a1: torch.Tensor, d: CnnDims) -> torch.Tensor:
+def conv2_dgrad(dy2: torch.Tensor, w2h: torch.Tensor, a1: torch.Tensor, d: CnnDims, impl: str = "gather") -> torch.Tensor:
     g1 = torch.empty((d.B, d.P1h, d.P1w, d.C1), dtype=torch.bfloat16, device=a1.device)
-    _lib.check(_lib.kernels().tfdl_cnn_conv2_dgrad(_p(dy2), _p(w2h), _p(a1), _p(g1), C.byref(d), _s()), "conv2_dgrad")
+    fn = _lib.kernels().tfdl_cnn_conv2_dgrad_tma if impl == "tma" else _lib.kernels().tfdl_cnn_conv2_dgrad
+    _lib.check(fn(_p(dy2), _p(w2h), _p(a1), _p(g1), C.byref(d), _s()), "conv2_dgrad")
     return g1
 
 

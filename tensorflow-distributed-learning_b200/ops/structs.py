@@ -50,6 +50,7 @@ class CnnStep(C.Structure):
         ("idx1", C.c_void_p), ("idx2", C.c_void_p),
         ("acc", C.c_void_p), ("metrics", C.c_void_p), ("step_out", C.c_void_p),
         ("dense1_ksplit", C.c_int),
+        ("use_tma_conv", C.c_int),
     ]
 
 

@@ -39,7 +39,8 @@ def test_conv1_fwd_matches_conv_bias_pool_relu():
     torch.testing.assert_close(picked, yw.max(-1).values, rtol=0, atol=1e-5)
 
 
-def test_conv2_fwd_tcgen05_matches_reference():
+@pytest.mark.parametrize("impl", ["gather", "tma"])
+def test_conv2_fwd_tcgen05_matches_reference(impl):
     from tfdl.ops import cnn
 
     d = _dims()
@@ -47,7 +48,7 @@ def test_conv2_fwd_tcgen05_matches_reference():
     a1 = _bf(torch.relu(torch.randn(B, 13, 13, 32, device="cuda")))
     w = _bf(torch.randn(64, 3, 3, 32, device="cuda") * 0.1)
     b = torch.randn(64, device="cuda") * 0.1
-    a2, idx = cnn.conv2_fwd(a1, w, b, d)
+    a2, idx = cnn.conv2_fwd(a1, w, b, d, impl=impl)
     y = F.conv2d(a1.float().permute(0, 3, 1, 2), w.float().permute(0, 3, 1, 2), b)  # [B,64,11,11]
     ref = torch.relu(F.max_pool2d(y, 2)).permute(0, 2, 3, 1)  # floor: row/col 10 dropped
     torch.testing.assert_close(a2.float(), ref, rtol=2e-2, atol=2e-2)
@@ -98,38 +99,45 @@ def test_dense1_dgrad_unpool_epilogue():
     ref = torch.zeros(B, 10, 10, 64, device="cuda")
     for q in range(4):
         ref[:, (q >> 1)::2, (q & 1)::2, :] = torch.where((iv == q) & (a2v > 0), da2, torch.zeros_like(da2))
-    torch.testing.assert_close(dy2.float(), ref, rtol=2e-2, atol=2e-3)
+    assert dy2.shape == (B, 13, 13, 64)  # stored on the conv2 input grid; the margin stays zero
+    torch.testing.assert_close(dy2[:, :10, :10].float(), ref, rtol=2e-2, atol=2e-3)
+    assert torch.count_nonzero(dy2[:, 10:]) == 0 and torch.count_nonzero(dy2[:, :, 10:]) == 0
 
 
 def _sparse_dy2():
-    dy2 = torch.randn(B, 10, 10, 64, device="cuda") * 0.1
-    keep = torch.rand(B, 10, 10, 64, device="cuda") < 0.25
-    return _bf(dy2 * keep)
+    """(dy2 on the 13x13 grid as the kernels expect it, the dense 10x10 core for the reference)"""
+    core = torch.randn(B, 10, 10, 64, device="cuda") * 0.1
+    core = _bf(core * (torch.rand(B, 10, 10, 64, device="cuda") < 0.25))
+    grid = torch.zeros(B, 13, 13, 64, dtype=torch.bfloat16, device="cuda")
+    grid[:, :10, :10] = core
+    return grid, core
 
 
-def test_conv2_wgrad_split_reduction():
+@pytest.mark.parametrize("impl", ["gather", "tma"])
+def test_conv2_wgrad_split_reduction(impl):
     from tfdl.ops import cnn
 
     d = _dims()
     torch.manual_seed(4)
     a1 = _bf(torch.relu(torch.randn(B, 13, 13, 32, device="cuda")))
-    dy2 = _sparse_dy2()
-    g_w, g_b = cnn.conv2_wgrad(a1, dy2, d)
+    grid, dy2 = _sparse_dy2()
+    g_w, g_b = cnn.conv2_wgrad(a1, grid, d, impl=impl)
     xin = a1.float().permute(0, 3, 1, 2)[:, :, :12, :12].contiguous()
     gw_ref = torch.nn.grad.conv2d_weight(xin, (64, 32, 3, 3), dy2.float().permute(0, 3, 1, 2).contiguous())
     torch.testing.assert_close(g_w, gw_ref.permute(0, 2, 3, 1), rtol=5e-3, atol=5e-3)
     torch.testing.assert_close(g_b, dy2.float().sum((0, 1, 2)), rtol=1e-3, atol=1e-3)
 
 
-def test_conv2_dgrad_relu_masked():
+@pytest.mark.parametrize("impl", ["gather", "tma"])
+def test_conv2_dgrad_relu_masked(impl):
     from tfdl.ops import cnn
 
     d = _dims()
     torch.manual_seed(5)
     a1 = _bf(torch.relu(torch.randn(B, 13, 13, 32, device="cuda")))
     w = _bf(torch.randn(64, 3, 3, 32, device="cuda") * 0.1)
-    dy2 = _sparse_dy2()
-    g1 = cnn.conv2_dgrad(dy2, w, a1, d)
+    grid, dy2 = _sparse_dy2()
+    g1 = cnn.conv2_dgrad(grid, w, a1, d, impl=impl)
     gi = torch.nn.grad.conv2d_input((B, 32, 12, 12), w.float().permute(0, 3, 1, 2).contiguous(),
                                     dy2.float().permute(0, 3, 1, 2).contiguous())
     ref = torch.zeros(B, 13, 13, 32, device="cuda")

@@ -33,36 +33,3 @@ for it in range(int(os.environ.get("ITERS", "5"))):
 torch.cuda.synchronize()
 print("ok", float(so[0]))
 
-if os.environ.get("TIME"):
-    # warm, back-to-back, same-stream timing of each kernel (includes the launch gap between dependent kernels)
-    import ctypes as C
-    from tfdl.ops import _lib
-    accT = torch.zeros(B, 128, device=dev)
-    st = torch.cuda.Stream()
-    def timeit(name, fn, n=300):
-        with torch.cuda.stream(st):
-            for _ in range(20): fn()
-            e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
-            e0.record(st)
-            for _ in range(n): fn()
-            e1.record(st)
-        st.synchronize()
-        print(f"{name:16s} {1000*e0.elapsed_time(e1)/n:7.2f} us/launch")
-    L = _lib.kernels()
-    timeit("empty(memset4B)", lambda: torch.cuda.current_stream() and met.zero_())
-    timeit("conv1_fwd", lambda: cnn.conv1_fwd(x, w1, b1, d))
-    timeit("conv2_fwd", lambda: cnn.conv2_fwd(a1, w2, b2, d))
-    a2f = a2.view(B, 1600)
-    from tfdl.ops.structs import make_dims
-    def d1f():
-        _lib.check(L.tfdl_gemm_bf16_gather_ex(_lib.ptr(wd), _lib.ptr(a2f), _lib.ptr(accT), None, None, 128, B, 1600, 1600, 1600, 128, 0, 0, 0, 25, 0, 64, 1, _lib.cur_stream()))
-    timeit("dense1_fwd", d1f)
-    timeit("head", lambda: cnn.head(accT, bd, wo, bo, y, d))
-    gW = torch.zeros(128, 1600, device=dev)
-    def dw1():
-        _lib.check(L.tfdl_gemm_bf16_gather_ex(_lib.ptr(dh), _lib.ptr(a2f), _lib.ptr(gW), None, None, 128, 1600, B, 128, 1600, 1600, 1, 1, 0, 1, 64, 0, 0, _lib.cur_stream()))
-    timeit("dense1_wgrad", dw1)
-    timeit("dense1_dgrad", lambda: cnn.dense1_dgrad(dh, wd, a2f, i2.view(B, 1600), d))
-    timeit("conv2_wgrad", lambda: cnn.conv2_wgrad(a1, dy2, d))
-    timeit("conv2_dgrad", lambda: cnn.conv2_dgrad(dy2, w2, a1, d))
-    timeit("conv1_wgrad", lambda: cnn.conv1_wgrad(x, g1, i1, d))

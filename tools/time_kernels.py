@@ -29,7 +29,8 @@ acc = torch.zeros(B, 128, device=dev)
 dh = torch.zeros(B, 128, dtype=torch.bfloat16, device=dev)
 gw2, gb2, gb1 = torch.zeros(10, 128, device=dev), torch.zeros(10, device=dev), torch.zeros(128, device=dev)
 met, so = torch.zeros(3, device=dev), torch.zeros(2, device=dev)
-dy2 = torch.zeros(B, 10, 10, 64, dtype=torch.bfloat16, device=dev)
+dy2 = torch.zeros(B, 13, 13, 64, dtype=torch.bfloat16, device=dev)
+dy2[:, :10, :10] = (torch.randn(B, 10, 10, 64, device=dev) * 0.1).bfloat16()
 g1 = torch.zeros(B, 13, 13, 32, dtype=torch.bfloat16, device=dev)
 gW1 = torch.zeros(128, 1600, device=dev)
 gwc, gbc = torch.zeros(64, 288, device=dev), torch.zeros(64, device=dev)
@@ -49,6 +50,9 @@ kernels = {
     "dense1_dgrad": lambda: L.tfdl_cnn_dense1_dgrad(p(dh), p(wd), p(a2), p(i2), p(dy2), D, S()),
     "conv2_wgrad": lambda: L.tfdl_cnn_conv2_wgrad(p(a1), p(dy2), p(gwc), p(gbc), D, S()),
     "conv2_dgrad": lambda: L.tfdl_cnn_conv2_dgrad(p(dy2), p(w2), p(a1), p(g1), D, S()),
+    "conv2_fwd_tma": lambda: L.tfdl_cnn_conv2_fwd_tma(p(a1), p(w2), p(b2), p(a2), p(i2), D, S()),
+    "conv2_wgrad_tma": lambda: L.tfdl_cnn_conv2_wgrad_tma(p(a1), p(dy2), p(gwc), p(gbc), D, S()),
+    "conv2_dgrad_tma": lambda: L.tfdl_cnn_conv2_dgrad_tma(p(dy2), p(w2), p(a1), p(g1), D, S()),
     "conv1_wgrad": lambda: L.tfdl_cnn_conv1_wgrad(p(x), p(g1), p(i1), p(gw1c), p(gb1c), D, S()),
 }
 N = 50
@@ -70,7 +74,7 @@ for name, fn in kernels.items():
         e1.record(st)
     st.synchronize()
     us = 1000 * e0.elapsed_time(e1) / (10 * N)
-    if name != "memset_16B" and name not in ("dense1_wgrad", "conv2_wgrad"):
+    if name != "memset_16B" and name not in ("dense1_wgrad", "conv2_wgrad", "conv2_wgrad_tma", "conv2_fwd", "conv2_dgrad"):
         total += us
     print(f"{name:14s} {us:7.2f} us per launch (in-graph, chained)")
 print(f"critical-path kernels sum: {total:.1f} us (+ all-reduce)")
