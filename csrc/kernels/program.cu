@@ -33,22 +33,28 @@ extern "C" int tfdl_cnn_step_launch(const TfdlCnnStep* s, void* stream, void* si
   const bool tma = s->use_tma_conv != 0;
   if (tma) TFDL_RC(tfdl_cnn_conv2_fwd_tma(s->a1, H + s->off_w2c, P + s->off_b2c, s->a2, s->idx2, d, st));
   else TFDL_RC(tfdl_cnn_conv2_fwd(s->a1, H + s->off_w2c, P + s->off_b2c, s->a2, s->idx2, d, st));
-  // dense1: acc[s][u] += sum_k W1[u][k] a2[s][k]   (swap-AB: M = units, N = samples, split-K, transposed RED)
-  TFDL_RC(tfdl_gemm_bf16_gather_ex(H + s->off_w1d, s->a2, s->acc, nullptr, nullptr, d->D1, d->B, d->F, d->F, d->F,
-                                   d->D1, 0, 0, 0, s->dense1_ksplit > 0 ? s->dense1_ksplit : 1, 0, 64, 1, st));
-  TFDL_RC(tfdl_cnn_head(s->acc, P + s->off_b1d, P + s->off_w2d, P + s->off_b2d, s->labels, s->dh, G + s->off_w2d,
-                        G + s->off_b2d, G + s->off_b1d, s->metrics, s->step_out, d, st));
-  // ---- backward ----
-  if (forked) {
-    TFDL_CUDA_OK(cudaEventRecord(ef, st));
-    TFDL_CUDA_OK(cudaStreamWaitEvent(sd, ef, 0));
-  }
   cudaStream_t off = forked ? sd : st;
-  // dW1[u][f] = sum_s a2[s][f] dh[s][u]: both operands MN-major; rows = features so that the transposed
-  // store walks f (the contiguous index of dW1) across the lanes of a warp (off the critical path)
-  TFDL_RC(tfdl_gemm_bf16_gather_ex(s->a2, s->dh, G + s->off_w1d, nullptr, nullptr, d->F, d->D1, d->B, d->F, d->D1,
-                                   d->F, 1, 1, 0, 1, 64, 0, 1, off));
-  TFDL_RC(tfdl_cnn_dense1_dgrad(s->dh, H + s->off_w1d, s->a2, s->idx2, s->dy2, d, st));
+  if (s->use_dense_block) {
+    // Dense(128)+Dense(NC)+loss forward and backward down to dy2, and all four dense gradients, in one kernel
+    TFDL_RC(tfdl_cnn_dense_block(s->a2, s->idx2, H + s->off_w1d, H + s->off_w2d, P + s->off_b1d, P + s->off_b2d,
+                                 s->labels, s->acc, s->acc_next, s->sync, s->dy2, G + s->off_w1d, G + s->off_b1d,
+                                 G + s->off_w2d, G + s->off_b2d, s->metrics, s->step_out, nullptr, d, st));
+  } else {
+    // dense1: acc[s][u] += sum_k W1[u][k] a2[s][k]   (swap-AB: M = units, N = samples, split-K, transposed RED)
+    TFDL_RC(tfdl_gemm_bf16_gather_ex(H + s->off_w1d, s->a2, s->acc, nullptr, nullptr, d->D1, d->B, d->F, d->F, d->F,
+                                     d->D1, 0, 0, 0, s->dense1_ksplit > 0 ? s->dense1_ksplit : 1, 0, 64, 1, st));
+    TFDL_RC(tfdl_cnn_head(s->acc, P + s->off_b1d, P + s->off_w2d, P + s->off_b2d, s->labels, s->dh, G + s->off_w2d,
+                          G + s->off_b2d, G + s->off_b1d, s->metrics, s->step_out, d, st));
+    if (forked) {
+      TFDL_CUDA_OK(cudaEventRecord(ef, st));
+      TFDL_CUDA_OK(cudaStreamWaitEvent(sd, ef, 0));
+    }
+    // dW1[u][f] = sum_s a2[s][f] dh[s][u]: both operands MN-major; rows = features so that the transposed
+    // store walks f (the contiguous index of dW1) across the lanes of a warp (off the critical path)
+    TFDL_RC(tfdl_gemm_bf16_gather_ex(s->a2, s->dh, G + s->off_w1d, nullptr, nullptr, d->F, d->D1, d->B, d->F, d->D1,
+                                     d->F, 1, 1, 0, 1, 64, 0, 1, off));
+    TFDL_RC(tfdl_cnn_dense1_dgrad(s->dh, H + s->off_w1d, s->a2, s->idx2, s->dy2, d, st));
+  }
   if (forked) {
     // conv2 wgrad needs dy2 (main branch) but nothing downstream needs it before the all-reduce
     TFDL_CUDA_OK(cudaEventRecord(ef, st));

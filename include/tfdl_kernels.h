@@ -160,6 +160,18 @@ int tfdl_cnn_conv2_dgrad_tma(const void* dy2_bf16, const void* w2_bf16, const vo
 int tfdl_cnn_conv2_wgrad_tma(const void* a1_bf16, const void* dy2_bf16, float* g_w2c, float* g_b2c,
                              const TfdlCnnDims* d, void* stream);
 
+/* Fused dense block (csrc/kernels/dense_block.cu): Dense(128,relu) + Dense(NC) + softmax-xent forward AND
+ * backward down to dy2, plus dW1/db1/dW2/db2, loss and accuracy, in one kernel of P2h*P2w CTAs with one
+ * grid barrier. acc: [B][128] fp32, zero on entry; acc_next: the other parity's accumulator (cleared here);
+ * sync: one uint32 arrival counter (zero-initialised once, never reset). Gradients are STORED (not
+ * accumulated). dh_out optional (tests). Requires tfdl_cnn_dense_block_supported(d). */
+int tfdl_cnn_dense_block_supported(const TfdlCnnDims* d);
+int tfdl_cnn_dense_block(const void* a2_bf16, const uint8_t* idx2, const void* w1_bf16 /*[128][F]*/,
+                         const void* w2_bf16 /*[NC][128]*/, const float* b1, const float* b2, const int* labels,
+                         float* acc, float* acc_next, uint32_t* sync, void* dy2_bf16, float* g_w1, float* g_b1,
+                         float* g_w2, float* g_b2, float* metrics, float* step_out, void* dh_out_bf16,
+                         const TfdlCnnDims* d, void* stream);
+
 /* One training step = the 9 kernels above + the fused all-reduce/SGD, described by pointers into the
  * caller's buffers. Two descriptors (gradient-buffer parity 0 and 1) make a program. */
 typedef struct {
@@ -177,6 +189,9 @@ typedef struct {
   float* step_out;           /* [2] this step's mean loss and accuracy */
   int dense1_ksplit;         /* CTAs along K for dense1 forward */
   int use_tma_conv;          /* 1: conv2 fwd/dgrad/wgrad via cnn_tma.cu (requires tfdl_cnn_tma_supported) */
+  int use_dense_block;       /* 1: dense1 fwd + head + dense1 dgrad/wgrad fused (tfdl_cnn_dense_block) */
+  float* acc_next;           /* the other parity's split-K accumulator (dense block clears it) */
+  uint32_t* sync;            /* grid-barrier arrival counter of the dense block */
 } TfdlCnnStep;
 
 /* Launch the forward+backward kernels of one step on `stream`, using `side` for the branches that are

@@ -160,7 +160,9 @@ class NativeCnnEngine:
         z = lambda *s, dt=bf: torch.zeros(s, dtype=dt, device=dev)  # noqa: E731
         bufs = dict(a1=z(B, d.P1h, d.P1w, C1), a2=z(B, d.F), dh=z(B, D1), dy2=z(B, d.P1h, d.P1w, C2),
                     g1=z(B, d.P1h, d.P1w, C1), idx1=z(B, d.P1h, d.P1w, C1, dt=torch.uint8),
-                    idx2=z(B, d.F, dt=torch.uint8), acc=z(B, D1, dt=torch.float32))
+                    idx2=z(B, d.F, dt=torch.uint8))
+        accs = [z(B, D1, dt=torch.float32) for _ in range(2)]  # split-K accumulator, one per step parity
+        sync = z(4, dt=torch.int32)
         self.x_dev = [z(B, H0, W0, dt=torch.float32) for _ in range(2)]
         self.y_dev = [z(B, dt=torch.int32) for _ in range(2)]
         self.step_out = [z(2, dt=torch.float32) for _ in range(2)]
@@ -176,6 +178,13 @@ class NativeCnnEngine:
             (s.off_w1c, s.off_b1c, s.off_w2c, s.off_b2c, s.off_w1d, s.off_b1d, s.off_w2d, s.off_b2d) = offs
             for k, t in bufs.items():
                 setattr(s, k, t.data_ptr())
+            fused = bool(self.lib.tfdl_cnn_dense_block_supported(C.byref(d))) and \
+                os.environ.get("TFDL_DENSE_IMPL", "fused") == "fused"
+            s.use_dense_block = int(fused)
+            # the fused dense block clears the OTHER parity's accumulator; the unfused head re-zeroes its own
+            s.acc = accs[par].data_ptr() if fused else accs[0].data_ptr()
+            s.acc_next = accs[par ^ 1].data_ptr()
+            s.sync = sync.data_ptr()
             s.metrics = self.metrics_dev.data_ptr()
             s.step_out = self.step_out[par].data_ptr()
             s.dense1_ksplit = max(1, d.F // 64)
@@ -187,7 +196,7 @@ class NativeCnnEngine:
         _lib.check(self.lib.tfdl_cnn_program_create(steps, ars, self.state.algo, use_graph, C.byref(prog)),
                    "cnn_program_create")
         self._prog, self._B, self._dims = prog, B, d
-        self._keep = [bufs, steps, ars]
+        self._keep = [bufs, steps, ars, accs, sync]
         self.rec_bytes = B * H0 * W0 * 4 + B * 4
         n_rec = max(2, self.CHUNK)
         self.ring = torch.empty((n_rec, self.rec_bytes), dtype=torch.uint8).pin_memory()

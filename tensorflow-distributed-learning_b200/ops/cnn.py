@@ -79,5 +79,26 @@ def conv1_wgrad(x: torch.Tensor, g1: torch.Tensor, idx1: torch.Tensor, d: CnnDim
     return g_w, g_b
 
 
-__all__ = ["conv1_fwd", "conv2_fwd", "head", "dense1_dgrad", "conv2_wgrad", "conv2_dgrad", "conv1_wgrad", "make_dims",
+def dense_block(a2: torch.Tensor, idx2: torch.Tensor, w1h: torch.Tensor, w2h: torch.Tensor, b1: torch.Tensor,
+                b2: torch.Tensor, labels: torch.Tensor, d: CnnDims, acc: torch.Tensor = None,
+                acc_next: torch.Tensor = None, sync: torch.Tensor = None):
+    """Fused Dense(128,relu)+Dense(NC)+softmax-xent forward/backward (csrc/kernels/dense_block.cu).
+    Returns dict(dy2, g_w1, g_b1, g_w2, g_b2, metrics, step_out, dh)."""
+    dev = a2.device
+    acc = torch.zeros(d.B, d.D1, device=dev) if acc is None else acc
+    acc_next = torch.ones(d.B, d.D1, device=dev) if acc_next is None else acc_next
+    sync = torch.zeros(4, dtype=torch.int32, device=dev) if sync is None else sync
+    out = dict(dy2=torch.zeros((d.B, d.P1h, d.P1w, d.C2), dtype=torch.bfloat16, device=dev),
+               g_w1=torch.zeros(d.D1, d.F, device=dev), g_b1=torch.zeros(d.D1, device=dev),
+               g_w2=torch.zeros(d.NC, d.D1, device=dev), g_b2=torch.zeros(d.NC, device=dev),
+               metrics=torch.zeros(3, device=dev), step_out=torch.zeros(2, device=dev),
+               dh=torch.zeros(d.B, d.D1, dtype=torch.bfloat16, device=dev), acc=acc, acc_next=acc_next, sync=sync)
+    _lib.check(_lib.kernels().tfdl_cnn_dense_block(
+        _p(a2), _p(idx2), _p(w1h), _p(w2h), _p(b1), _p(b2), _p(labels), _p(acc), _p(acc_next), _p(sync), _p(out["dy2"]),
+        _p(out["g_w1"]), _p(out["g_b1"]), _p(out["g_w2"]), _p(out["g_b2"]), _p(out["metrics"]), _p(out["step_out"]),
+        _p(out["dh"]), C.byref(d), _s()), "dense_block")
+    return out
+
+
+__all__ = ["dense_block", "conv1_fwd", "conv2_fwd", "head", "dense1_dgrad", "conv2_wgrad", "conv2_dgrad", "conv1_wgrad", "make_dims",
            "CnnDims"]

@@ -51,6 +51,9 @@ class CnnStep(C.Structure):
         ("acc", C.c_void_p), ("metrics", C.c_void_p), ("step_out", C.c_void_p),
         ("dense1_ksplit", C.c_int),
         ("use_tma_conv", C.c_int),
+        ("use_dense_block", C.c_int),
+        ("acc_next", C.c_void_p),
+        ("sync", C.c_void_p),
     ]
 
 

@@ -188,3 +188,50 @@ def test_fused_allreduce_sgd_single_gpu_matches_sgd():
         torch.testing.assert_close(st.shadow.tensor.float(), params.bfloat16().float(), rtol=0, atol=0)
         assert torch.count_nonzero(st.grads[par ^ 1].tensor) == 0
         assert st.counters[0].item() == step + 1
+
+
+@pytest.mark.parametrize("b", [64, 32, 128])
+def test_fused_dense_block_matches_fp32_reference(b):
+    """Dense(128,relu)+Dense(10)+xent forward AND backward in one kernel vs torch autograd."""
+    from tfdl.ops import cnn
+
+    d = _dims(b)
+    torch.manual_seed(8)
+    a2 = _bf(torch.relu(torch.randn(b, 1600, device="cuda")))
+    idx2 = torch.randint(0, 4, (b, 1600), device="cuda", dtype=torch.uint8)
+    w1 = _bf(torch.randn(128, 1600, device="cuda") * 0.03)
+    w2 = _bf(torch.randn(10, 128, device="cuda") * 0.2)
+    b1 = torch.randn(128, device="cuda") * 0.1
+    b2 = torch.randn(10, device="cuda") * 0.1
+    y = torch.randint(0, 10, (b,), device="cuda", dtype=torch.int32)
+    sync = torch.zeros(4, dtype=torch.int32, device="cuda")
+    for rep in range(2):  # twice: the barrier counter and the accumulator hand-over must survive reuse
+        out = cnn.dense_block(a2, idx2, w1, w2, b1, b2, y, d, sync=sync)
+        torch.cuda.synchronize()
+        A2 = a2.float().requires_grad_()
+        W1, W2 = w1.float().requires_grad_(), w2.float().requires_grad_()
+        B1, B2 = b1.clone().requires_grad_(), b2.clone().requires_grad_()
+        pre = A2 @ W1.t() + B1
+        pre.retain_grad()
+        # the kernel feeds h to the second layer in bf16
+        h = torch.relu(pre)
+        hq = h + (h.detach().bfloat16().float() - h.detach())
+        logits = hq @ W2.t() + B2
+        loss = F.cross_entropy(logits, y.long())
+        loss.backward()
+        torch.testing.assert_close(out["step_out"][0], loss.detach(), rtol=2e-3, atol=2e-3)
+        assert out["metrics"][2].item() == b
+        assert abs(out["metrics"][1].item() - (logits.argmax(-1) == y.long()).sum().item()) <= 1
+        torch.testing.assert_close(out["g_b2"], B2.grad, rtol=2e-2, atol=2e-4)
+        torch.testing.assert_close(out["g_w2"], W2.grad, rtol=3e-2, atol=3e-4)
+        torch.testing.assert_close(out["g_b1"], B1.grad, rtol=3e-2, atol=3e-4)
+        torch.testing.assert_close(out["dh"].float(), pre.grad, rtol=3e-2, atol=1e-4)
+        torch.testing.assert_close(out["g_w1"], W1.grad, rtol=5e-2, atol=6e-4)
+        da2 = A2.grad.view(b, 5, 5, 64)
+        a2v, iv = a2.view(b, 5, 5, 64), idx2.view(b, 5, 5, 64)
+        ref = torch.zeros(b, 10, 10, 64, device="cuda")
+        for q in range(4):
+            ref[:, (q >> 1)::2, (q & 1)::2, :] = torch.where((iv == q) & (a2v > 0), da2, torch.zeros_like(da2))
+        torch.testing.assert_close(out["dy2"][:, :10, :10].float(), ref, rtol=5e-2, atol=6e-4)
+        assert torch.count_nonzero(out["acc_next"]) == 0  # the other parity's accumulator was cleared
+        assert sync[0].item() == 25 * (rep + 1)
