@@ -185,7 +185,7 @@ def run_ours(args) -> dict:
                 "ms_per_step": round(e2e_ms / args.steps, 5), "api": "model.fit(dataset, steps_per_epoch=K)",
                 "h2d_bytes_per_step": rec, "d2h_bytes_per_step": 8,
                 "final_loss": float(hist.history["loss"][-1])},
-        "gpu_launches": int(args.steps * 10),
+        "gpu_launches": int(args.steps * engine.launches_per_step),
         "impl": "tfdl",
     }
     strategy.close()

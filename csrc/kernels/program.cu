@@ -21,6 +21,12 @@ using namespace tfdl;
   } while (0)
 
 extern "C" int tfdl_cnn_step_launch(const TfdlCnnStep* s, void* stream, void* side, void* ev_fork, void* ev_join) {
+  return tfdl_cnn_step_launch_overlap(s, nullptr, 0, stream, side, nullptr, ev_fork, ev_join, nullptr, nullptr);
+}
+
+extern "C" int tfdl_cnn_step_launch_overlap(const TfdlCnnStep* s, const TfdlFusedArParams* early, int early_algo,
+                                            void* stream, void* side, void* ar_stream, void* ev_fork, void* ev_join,
+                                            void* ev_ar_fork, void* ev_ar_join) {
   const TfdlCnnDims* d = &s->dims;
   cudaStream_t st = (cudaStream_t)stream, sd = (cudaStream_t)side;
   cudaEvent_t ef = (cudaEvent_t)ev_fork, ej = (cudaEvent_t)ev_join;
@@ -55,6 +61,15 @@ extern "C" int tfdl_cnn_step_launch(const TfdlCnnStep* s, void* stream, void* si
                                      d->F, 1, 1, 0, 1, 64, 0, 1, off));
     TFDL_RC(tfdl_cnn_dense1_dgrad(s->dh, H + s->off_w1d, s->a2, s->idx2, s->dy2, d, st));
   }
+  const bool overlap = early != nullptr && s->use_dense_block && ar_stream != nullptr && ev_ar_fork && ev_ar_join;
+  if (overlap) {
+    // the dense-layer gradients (91% of the arena) are final: reduce + apply them now, on their own stream,
+    // while the conv backward kernels run (bucketed overlap; README.md:67 only requires completion per batch)
+    TFDL_CUDA_OK(cudaEventRecord((cudaEvent_t)ev_ar_fork, st));
+    TFDL_CUDA_OK(cudaStreamWaitEvent((cudaStream_t)ar_stream, (cudaEvent_t)ev_ar_fork, 0));
+    TFDL_RC(tfdl_fused_allreduce_sgd(early, early_algo, ar_stream));
+    TFDL_CUDA_OK(cudaEventRecord((cudaEvent_t)ev_ar_join, (cudaStream_t)ar_stream));
+  }
   if (forked) {
     // conv2 wgrad needs dy2 (main branch) but nothing downstream needs it before the all-reduce
     TFDL_CUDA_OK(cudaEventRecord(ef, st));
@@ -72,12 +87,18 @@ extern "C" int tfdl_cnn_step_launch(const TfdlCnnStep* s, void* stream, void* si
     TFDL_CUDA_OK(cudaEventRecord(ej, sd));
     TFDL_CUDA_OK(cudaStreamWaitEvent(st, ej, 0));
   }
+  if (overlap) TFDL_CUDA_OK(cudaStreamWaitEvent(st, (cudaEvent_t)ev_ar_join, 0));
   return 0;
 }
 
 struct TfdlCnnProgram {
   TfdlCnnStep steps[2];
   TfdlFusedArParams ar[2];
+  TfdlFusedArParams ar_early[2];
+  bool has_early = false;
+  int algo_early = 0;
+  cudaStream_t ar_stream = nullptr;
+  cudaEvent_t ev_ar_fork = nullptr, ev_ar_join = nullptr;
   int algo = 0;
   int use_graph = 1;
   cudaGraphExec_t exec[2] = {nullptr, nullptr};
@@ -90,7 +111,8 @@ struct TfdlCnnProgram {
 };
 
 static int enqueue_step(TfdlCnnProgram* p, int par, cudaStream_t st) {
-  TFDL_RC(tfdl_cnn_step_launch(&p->steps[par], st, p->side, p->ev_fork, p->ev_join));
+  TFDL_RC(tfdl_cnn_step_launch_overlap(&p->steps[par], p->has_early ? &p->ar_early[par] : nullptr, p->algo_early, st,
+                                       p->side, p->ar_stream, p->ev_fork, p->ev_join, p->ev_ar_fork, p->ev_ar_join));
   TFDL_RC(tfdl_fused_allreduce_sgd(&p->ar[par], p->algo, st));
   return 0;
 }
@@ -115,8 +137,25 @@ static int ensure_graph(TfdlCnnProgram* p, int par, cudaStream_t st) {
 
 extern "C" int tfdl_cnn_program_create(const TfdlCnnStep steps[2], const TfdlFusedArParams ar[2], int algo,
                                        int use_graph, TfdlCnnProgram** out) {
+  return tfdl_cnn_program_create2(steps, ar, algo, nullptr, 0, use_graph, out);
+}
+
+extern "C" int tfdl_cnn_program_create2(const TfdlCnnStep steps[2], const TfdlFusedArParams ar[2], int algo,
+                                        const TfdlFusedArParams ar_early[2], int algo_early, int use_graph,
+                                        TfdlCnnProgram** out) {
   TFDL_REQUIRE(steps && ar && out, "cnn_program_create: null argument");
   auto* p = new TfdlCnnProgram();
+  if (ar_early) {
+    p->has_early = true;
+    p->algo_early = algo_early;
+    for (int i = 0; i < 2; ++i) {
+      p->ar_early[i] = ar_early[i];
+      p->ar_early[i].parity = i;
+    }
+    TFDL_CUDA_OK(cudaStreamCreateWithFlags(&p->ar_stream, cudaStreamNonBlocking));
+    TFDL_CUDA_OK(cudaEventCreateWithFlags(&p->ev_ar_fork, cudaEventDisableTiming));
+    TFDL_CUDA_OK(cudaEventCreateWithFlags(&p->ev_ar_join, cudaEventDisableTiming));
+  }
   for (int i = 0; i < 2; ++i) {
     p->steps[i] = steps[i];
     p->ar[i] = ar[i];
@@ -149,6 +188,9 @@ extern "C" int tfdl_cnn_program_destroy(TfdlCnnProgram* p) {
     if (p->ev_step[i]) cudaEventDestroy(p->ev_step[i]);
     if (p->ev_out[i]) cudaEventDestroy(p->ev_out[i]);
   }
+  if (p->ev_ar_fork) cudaEventDestroy(p->ev_ar_fork);
+  if (p->ev_ar_join) cudaEventDestroy(p->ev_ar_join);
+  if (p->ar_stream) cudaStreamDestroy(p->ar_stream);
   if (p->ev_fork) cudaEventDestroy(p->ev_fork);
   if (p->ev_join) cudaEventDestroy(p->ev_join);
   if (p->side) cudaStreamDestroy(p->side);
@@ -241,4 +283,9 @@ extern "C" int tfdl_cnn_program_run_device(TfdlCnnProgram* p, const void* dev_ba
 }
 
 extern "C" int64_t tfdl_cnn_program_steps_done(const TfdlCnnProgram* p) { return p ? p->steps_done : 0; }
-extern "C" int64_t tfdl_cnn_program_launches_per_step(const TfdlCnnProgram*) { return 10; }
+extern "C" int64_t tfdl_cnn_program_launches_per_step(const TfdlCnnProgram* p) {
+  if (!p) return 0;
+  const TfdlCnnStep& s = p->steps[0];
+  // conv1_fwd, conv2_fwd, [dense block | dense1_fwd, head, dW1, dense1_dgrad], conv2_wgrad, conv2_dgrad, conv1_wgrad, AR(s)
+  return 2 + (s.use_dense_block ? 1 : 4) + 3 + 1 + (p->has_early ? 1 : 0);
+}

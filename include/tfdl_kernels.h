@@ -197,6 +197,12 @@ typedef struct {
 /* Launch the forward+backward kernels of one step on `stream`, using `side` for the branches that are
  * off the critical path (dW1, conv2 wgrad); fork/join is done with the two events. Capturable. */
 int tfdl_cnn_step_launch(const TfdlCnnStep* s, void* stream, void* side, void* ev_fork, void* ev_join);
+/* Same, with bucketed overlap: `early` (may be NULL) is the fused all-reduce+SGD of the dense-layer gradient
+ * bucket; it is launched on `ar_stream` as soon as the dense block has produced those gradients and runs
+ * concurrently with the conv backward kernels. The caller launches the remaining bucket after this returns. */
+int tfdl_cnn_step_launch_overlap(const TfdlCnnStep* s, const TfdlFusedArParams* early, int early_algo, void* stream,
+                                 void* side, void* ar_stream, void* ev_fork, void* ev_join, void* ev_ar_fork,
+                                 void* ev_ar_join);
 
 /* Native step executor: owns two CUDA graphs (parity 0/1), each = step kernels + fused all-reduce/SGD.
  * tfdl_cnn_program_run drives n_steps steps from host memory without returning to Python: per step an
@@ -205,6 +211,9 @@ int tfdl_cnn_step_launch(const TfdlCnnStep* s, void* stream, void* side, void* e
 typedef struct TfdlCnnProgram TfdlCnnProgram;
 int tfdl_cnn_program_create(const TfdlCnnStep steps[2], const TfdlFusedArParams ar[2], int algo, int use_graph,
                             TfdlCnnProgram** out);
+/* Two gradient buckets: `ar_early` (dense layers; reduced while the conv backward still runs) and `ar` (the rest). */
+int tfdl_cnn_program_create2(const TfdlCnnStep steps[2], const TfdlFusedArParams ar[2], int algo,
+                             const TfdlFusedArParams ar_early[2], int algo_early, int use_graph, TfdlCnnProgram** out);
 int tfdl_cnn_program_destroy(TfdlCnnProgram* p);
 /* One step on data already resident in steps[parity].x / .labels. */
 int tfdl_cnn_program_step(TfdlCnnProgram* p, void* stream);

@@ -121,6 +121,14 @@ class NativeCnnEngine:
         self.state: FusedState = ops.fused_state(arena.params, arena.grads, momentum=bool(opt.momentum))
         if opt.momentum:
             opt._slots = {"momentum": [self.state.mom]}  # the optimizer's slot IS the kernel's buffer
+        # Gradient buckets (reverse layer order, like the reference's backward): the dense layers' gradients
+        # - 91% of the arena - are final right after the fused dense block, so their all-reduce + update runs
+        # on its own stream while the conv backward kernels execute; the conv bucket follows at the end.
+        self.buckets: List[FusedState] = [self.state]
+        self.overlap = os.environ.get("TFDL_AR_OVERLAP", "1") == "1"
+        if self.overlap:
+            cut = self.model.weights[4].spec.offset  # first dense variable
+            self.buckets = [self.state.bucket(0, cut), self.state.bucket(cut, self.state.n - cut, max_blocks=64)]
         self.hyperparams_changed()
         self.state.refresh_shadow()
         torch.cuda.synchronize(self.device)
@@ -135,12 +143,20 @@ class NativeCnnEngine:
     # ------------------------------------------------------------------------------------------
     @property
     def algo_name(self) -> str:
-        return self.state.algo_name
+        return "+".join(b.algo_name for b in self.buckets)
+
+    @property
+    def launches_per_step(self) -> int:
+        """Kernels of this library launched per training step (graph nodes), as counted by the executor."""
+        self.lib.tfdl_cnn_program_launches_per_step.restype = C.c_int64
+        self.lib.tfdl_cnn_program_launches_per_step.argtypes = [C.c_void_p]
+        return int(self.lib.tfdl_cnn_program_launches_per_step(self._prog)) if self._prog else 0
 
     def hyperparams_changed(self) -> None:
         opt = self.model.optimizer
         self._lr = opt.learning_rate
-        self.state.set_hyper(self._lr, opt.momentum, opt.nesterov, 1.0)
+        for b in getattr(self, "buckets", [self.state]):
+            b.set_hyper(self._lr, opt.momentum, opt.nesterov, 1.0)
 
     def weights_changed(self) -> None:
         self.state.refresh_shadow()
@@ -190,17 +206,31 @@ class NativeCnnEngine:
             s.dense1_ksplit = max(1, d.F // 64)
             s.use_tma_conv = int(bool(self.lib.tfdl_cnn_tma_supported(C.byref(d))) and
                                  os.environ.get("TFDL_CONV_IMPL", "tma") == "tma")
-        ars = (FusedArParams * 2)(self.state.struct(0), self.state.struct(1))
+        last = self.buckets[0]
+        ars = (FusedArParams * 2)(last.struct(0), last.struct(1))
         prog = C.c_void_p()
         use_graph = int(os.environ.get("TFDL_USE_GRAPH", "1"))
-        _lib.check(self.lib.tfdl_cnn_program_create(steps, ars, self.state.algo, use_graph, C.byref(prog)),
-                   "cnn_program_create")
+        if len(self.buckets) == 2 and steps[0].use_dense_block:
+            early = self.buckets[1]
+            ars_early = (FusedArParams * 2)(early.struct(0), early.struct(1))
+            _lib.check(self.lib.tfdl_cnn_program_create2(steps, ars, last.algo, ars_early, early.algo, use_graph,
+                                                         C.byref(prog)), "cnn_program_create2")
+        else:
+            full = self.state
+            ars = (FusedArParams * 2)(full.struct(0), full.struct(1))
+            ars_early = None
+            _lib.check(self.lib.tfdl_cnn_program_create(steps, ars, full.algo, use_graph, C.byref(prog)),
+                       "cnn_program_create")
         self._prog, self._B, self._dims = prog, B, d
-        self._keep = [bufs, steps, ars, accs, sync]
+        self._keep = [bufs, steps, ars, ars_early, accs, sync]
         self.rec_bytes = B * H0 * W0 * 4 + B * 4
         n_rec = max(2, self.CHUNK)
-        self.ring = torch.empty((n_rec, self.rec_bytes), dtype=torch.uint8).pin_memory()
-        self.host_out = torch.zeros((n_rec, 2), dtype=torch.float32).pin_memory()
+        # two pinned rings: Python packs chunk k+1 while the executor is still consuming chunk k
+        self.rings = [torch.empty((n_rec, self.rec_bytes), dtype=torch.uint8).pin_memory() for _ in range(2)]
+        self.host_outs = [torch.zeros((n_rec, 2), dtype=torch.float32).pin_memory() for _ in range(2)]
+        self.ring_done = [torch.cuda.Event(), torch.cuda.Event()]
+        self._ring_i = 0
+        self.ring, self.host_out = self.rings[0], self.host_outs[0]
         # the executor alternates parity with its own step counter, which restarts at 0: both gradient
         # buffers must be clean and the device epoch is only used for flag values
         for g in self.state.grads:
@@ -259,6 +289,10 @@ class NativeCnnEngine:
                 continue
             if self._B != B:
                 self._build_program(B)
+            r = self._ring_i
+            self._ring_i ^= 1
+            self.ring, self.host_out = self.rings[r], self.host_outs[r]
+            self.ring_done[r].synchronize()  # the run that last read this ring has finished (no-op if never used)
             k = 0
             while i + k < len(batches) and k < self.ring.shape[0]:
                 xb, yb = self._split(batches[i + k][0])
@@ -267,8 +301,8 @@ class NativeCnnEngine:
                 self.pack_record(k, xb, yb)
                 k += 1
             self.run_pinned(self.ring, k, self.host_out)
-            # the ring is reused by the next chunk: wait for this chunk's H2D copies (not for Python's sake)
-            self.stream.synchronize()
+            self.ring_done[r].record(self.stream)
+            self._last_k = k
             i += k
 
     def train_step(self, batches: PerReplica) -> None:
@@ -276,7 +310,8 @@ class NativeCnnEngine:
 
     def last_step_out(self) -> Tuple[float, float]:
         self.stream.synchronize()
-        return float(self.host_out[0, 0]), float(self.host_out[0, 1])
+        k = max(1, getattr(self, "_last_k", 1))
+        return float(self.host_out[k - 1, 0]), float(self.host_out[k - 1, 1])
 
     # ------------------------------------------------------------------------------------------
     def flush_metrics(self) -> None:

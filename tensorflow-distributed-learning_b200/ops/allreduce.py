@@ -30,7 +30,7 @@ from . import _lib
 from .structs import AR_MULTIMEM, AR_NAMES, AR_ONESHOT, AR_TWOSHOT, MAX_RANKS, FusedArParams, Hyper
 
 MAX_BLOCKS = 148
-ONESHOT_MAX_BYTES = int(os.environ.get("TFDL_AR_ONESHOT_MAX", 512 * 1024))
+ONESHOT_MAX_BYTES = int(os.environ.get("TFDL_AR_ONESHOT_MAX", 4 * 1024 * 1024))  # measured crossover, 2xB200
 
 
 def pick_algo(nbytes: int, world: int, has_multicast: bool) -> int:
@@ -184,31 +184,55 @@ class FusedState:
         self.has_multicast = bool(W > 1 and grads0.multicast_ptr and (plain or (
             params is not None and params.multicast_ptr and self.grads[1].multicast_ptr)))
         self.algo = pick_algo(n * 4, W, self.has_multicast)
+        self.offset = 0
+        self.max_blocks = MAX_BLOCKS
         self._structs = [self._make_struct(par) for par in (0, 1)]
         if W > 1:
             grads0.barrier()  # every rank has zeroed its flags before anyone signals
+
+    def bucket(self, offset: int, length: int, max_blocks: int = MAX_BLOCKS) -> "FusedState":
+        """A view of elements [offset, offset+length) of the same buffers with its OWN flag pad, step counter
+        and hyper-parameter words, so that it can be reduced by a separate kernel on a separate stream
+        (bucketed overlap with backward). offset/length must be multiples of 4 elements (16 bytes)."""
+        assert offset % 4 == 0 and length % 4 == 0 and offset + length <= self.n
+        b = FusedState.__new__(FusedState)
+        b.ops, b.n, b.offset, b.max_blocks = self.ops, length, offset, max_blocks
+        b.params, b.grads, b.shadow, b.mom = self.params, self.grads, self.shadow, self.mom
+        dev, W, R = self.ops.device, self.ops.world, self.ops.rank
+        b.pad_stride = self.pad_stride
+        b.flags = SymmetricBuffer(3 * b.pad_stride, torch.int32, dev, W, R) if W > 1 else None
+        b.counters = torch.zeros(4, dtype=torch.int32, device=dev)
+        b.hyper = torch.zeros(4, dtype=torch.float32, device=dev)
+        b.has_multicast = self.has_multicast
+        b.algo = pick_algo(length * 4, W, b.has_multicast)
+        b._structs = [b._make_struct(par) for par in (0, 1)]
+        if W > 1:
+            b.flags.barrier()
+        return b
 
     def _make_struct(self, parity: int) -> FusedArParams:
         p = FusedArParams()
         W, R = self.ops.world, self.ops.rank
         p.world, p.rank, p.n = W, R, self.n
+        o4, o2 = self.offset * 4, self.offset * 2  # byte offsets of this bucket in fp32 / bf16 buffers
         for r in range(W):
             if self.params is not None:
-                p.params[r] = self.params.ptrs[r]
+                p.params[r] = self.params.ptrs[r] + o4
             if self.shadow is not None:
-                p.shadow[r] = self.shadow.ptrs[r]
+                p.shadow[r] = self.shadow.ptrs[r] + o2
             for k, g in enumerate(self.grads):
-                p.grads[k][r] = g.ptrs[r]
+                p.grads[k][r] = g.ptrs[r] + o4
             if self.flags is not None:
                 p.flags[r] = self.flags.ptrs[r]
-        p.mom = self.mom.data_ptr() if self.mom is not None else None
+        p.mom = self.mom.data_ptr() + o4 if self.mom is not None else None
         p.pad_stride = self.pad_stride
-        p.max_blocks = MAX_BLOCKS
+        p.max_blocks = self.max_blocks
         if self.has_multicast:
-            p.mc_params = self.params.multicast_ptr if self.params is not None else None
-            p.mc_shadow = (self.shadow.multicast_ptr or None) if self.shadow is not None else None
+            p.mc_params = self.params.multicast_ptr + o4 if self.params is not None else None
+            p.mc_shadow = (self.shadow.multicast_ptr + o2 if self.shadow.multicast_ptr else None) \
+                if self.shadow is not None else None
             for k, g in enumerate(self.grads):
-                p.mc_grads[k] = g.multicast_ptr
+                p.mc_grads[k] = g.multicast_ptr + o4
         base = self.counters.data_ptr()
         p.epoch, p.done, p.abort_word = base, base + 4, base + 8
         p.hyper = self.hyper.data_ptr()

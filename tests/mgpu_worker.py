@@ -96,6 +96,7 @@ def main() -> None:
     ds = tfdl.data.Dataset.from_tensor_slices((x, y)).batch(G)
     o = tfdl.data.Options()
     o.experimental_distribute.auto_shard_policy = tfdl.data.AutoShardPolicy.DATA
+    w_init = model.get_weights()  # on rank 0 these are the values every replica starts from (chief broadcast)
     h = model.fit(ds.with_options(o), epochs=2, verbose=0)
     assert model.engine_name == "NativeCnnEngine"
     ws = [torch.from_numpy(w).to(dev) for w in model.get_weights()]
@@ -116,9 +117,11 @@ def main() -> None:
             ref = build_and_compile_cnn_model(learning_rate=0.05, momentum=0.9)
         hr = ref.fit(ds, epochs=2, verbose=0)
         np.testing.assert_allclose(h.history["loss"], hr.history["loss"], rtol=2e-2)
-        for a, b, v in zip(model.get_weights(), ref.get_weights(), ref.weights):
-            den = np.abs(b).max() + 1e-9
-            assert np.abs(a - b).max() / den < 5e-2, v.name
+        for a, b, w0, v in zip(model.get_weights(), ref.get_weights(), w_init, ref.weights):
+            # compare the accumulated UPDATES (bf16 activations + fp32 atomics: a few percent in the norm)
+            ua, ub = (a - w0).astype(np.float64), (b - w0).astype(np.float64)
+            rel = np.linalg.norm(ua - ub) / (np.linalg.norm(ub) + 1e-30)
+            assert rel < 0.1, (v.name, rel)
         report["train_matches_single_gpu"] = "ok"
         print("MGPU_REPORT " + json.dumps(report), flush=True)
     dist.barrier()
