@@ -35,10 +35,15 @@ extern "C" int tfdl_cnn_step_launch_overlap(const TfdlCnnStep* s, const TfdlFuse
   float* G = s->grads;
   const bool forked = sd != nullptr && sd != st && ef != nullptr && ej != nullptr;
   // ---- forward ----
-  TFDL_RC(tfdl_cnn_conv1_fwd(s->x, P + s->off_w1c, P + s->off_b1c, s->a1, s->idx1, s->step_out, d, st));
-  const bool tma = s->use_tma_conv != 0;
-  if (tma) TFDL_RC(tfdl_cnn_conv2_fwd_tma(s->a1, H + s->off_w2c, P + s->off_b2c, s->a2, s->idx2, d, st));
-  else TFDL_RC(tfdl_cnn_conv2_fwd(s->a1, H + s->off_w2c, P + s->off_b2c, s->a2, s->idx2, d, st));
+  const bool tma = s->use_tma_conv != 0, fusedc = tma && s->use_fused_conv != 0;
+  if (fusedc) {
+    TFDL_RC(tfdl_cnn_conv12_fwd_tma(s->x, P + s->off_w1c, P + s->off_b1c, H + s->off_w2c, P + s->off_b2c, s->a1, s->idx1,
+                                    s->a2, s->idx2, s->step_out, d, st));
+  } else {
+    TFDL_RC(tfdl_cnn_conv1_fwd(s->x, P + s->off_w1c, P + s->off_b1c, s->a1, s->idx1, s->step_out, d, st));
+    if (tma) TFDL_RC(tfdl_cnn_conv2_fwd_tma(s->a1, H + s->off_w2c, P + s->off_b2c, s->a2, s->idx2, d, st));
+    else TFDL_RC(tfdl_cnn_conv2_fwd(s->a1, H + s->off_w2c, P + s->off_b2c, s->a2, s->idx2, d, st));
+  }
   cudaStream_t off = forked ? sd : st;
   if (s->use_dense_block) {
     // Dense(128)+Dense(NC)+loss forward and backward down to dy2, and all four dense gradients, in one kernel
@@ -75,14 +80,18 @@ extern "C" int tfdl_cnn_step_launch_overlap(const TfdlCnnStep* s, const TfdlFuse
     TFDL_CUDA_OK(cudaEventRecord(ef, st));
     TFDL_CUDA_OK(cudaStreamWaitEvent(sd, ef, 0));
   }
-  if (tma) {
+  if (fusedc) {
+    TFDL_RC(tfdl_cnn_conv2_wgrad_tma(s->a1, s->dy2, G + s->off_w2c, G + s->off_b2c, d, off));
+    TFDL_RC(tfdl_cnn_conv21_bwd_tma(s->dy2, H + s->off_w2c, s->a1, s->idx1, s->x, G + s->off_w1c, G + s->off_b1c, nullptr,
+                                    d, st));
+  } else if (tma) {
     TFDL_RC(tfdl_cnn_conv2_wgrad_tma(s->a1, s->dy2, G + s->off_w2c, G + s->off_b2c, d, off));
     TFDL_RC(tfdl_cnn_conv2_dgrad_tma(s->dy2, H + s->off_w2c, s->a1, s->g1, d, st));
   } else {
     TFDL_RC(tfdl_cnn_conv2_wgrad(s->a1, s->dy2, G + s->off_w2c, G + s->off_b2c, d, off));
     TFDL_RC(tfdl_cnn_conv2_dgrad(s->dy2, H + s->off_w2c, s->a1, s->g1, d, st));
   }
-  TFDL_RC(tfdl_cnn_conv1_wgrad(s->x, s->g1, s->idx1, G + s->off_w1c, G + s->off_b1c, d, st));
+  if (!fusedc) TFDL_RC(tfdl_cnn_conv1_wgrad(s->x, s->g1, s->idx1, G + s->off_w1c, G + s->off_b1c, d, st));
   if (forked) {
     TFDL_CUDA_OK(cudaEventRecord(ej, sd));
     TFDL_CUDA_OK(cudaStreamWaitEvent(st, ej, 0));
@@ -287,5 +296,6 @@ extern "C" int64_t tfdl_cnn_program_launches_per_step(const TfdlCnnProgram* p) {
   if (!p) return 0;
   const TfdlCnnStep& s = p->steps[0];
   // conv1_fwd, conv2_fwd, [dense block | dense1_fwd, head, dW1, dense1_dgrad], conv2_wgrad, conv2_dgrad, conv1_wgrad, AR(s)
-  return 2 + (s.use_dense_block ? 1 : 4) + 3 + 1 + (p->has_early ? 1 : 0);
+  const bool fusedc = s.use_tma_conv && s.use_fused_conv;
+  return (fusedc ? 1 : 2) + (s.use_dense_block ? 1 : 4) + (fusedc ? 2 : 3) + 1 + (p->has_early ? 1 : 0);
 }

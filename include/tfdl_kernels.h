@@ -172,6 +172,15 @@ int tfdl_cnn_dense_block(const void* a2_bf16, const uint8_t* idx2, const void* w
                          float* g_w2, float* g_b2, float* metrics, float* step_out, void* dh_out_bf16,
                          const TfdlCnnDims* d, void* stream);
 
+/* conv1 forward fused into the TMA conv2 forward (a1/idx1 are still stored for the backward pass), and conv1
+ * wgrad fused into the TMA conv2 dgrad (g1 never leaves the SM; g1_out optional, for tests). */
+int tfdl_cnn_conv12_fwd_tma(const float* x, const float* w1, const float* b1, const void* w2_bf16, const float* b2,
+                            void* a1_bf16, uint8_t* idx1, void* a2_bf16, uint8_t* idx2, float* clear2,
+                            const TfdlCnnDims* d, void* stream);
+int tfdl_cnn_conv21_bwd_tma(const void* dy2_bf16, const void* w2_bf16, const void* a1_bf16, const uint8_t* idx1,
+                            const float* x, float* g_w1c, float* g_b1c, void* g1_out_bf16, const TfdlCnnDims* d,
+                            void* stream);
+
 /* One training step = the 9 kernels above + the fused all-reduce/SGD, described by pointers into the
  * caller's buffers. Two descriptors (gradient-buffer parity 0 and 1) make a program. */
 typedef struct {
@@ -192,6 +201,7 @@ typedef struct {
   int use_dense_block;       /* 1: dense1 fwd + head + dense1 dgrad/wgrad fused (tfdl_cnn_dense_block) */
   float* acc_next;           /* the other parity's split-K accumulator (dense block clears it) */
   uint32_t* sync;            /* grid-barrier arrival counter of the dense block */
+  int use_fused_conv;        /* 1: conv1 fwd fused into conv2 fwd, conv1 wgrad fused into conv2 dgrad (needs use_tma_conv) */
 } TfdlCnnStep;
 
 /* Launch the forward+backward kernels of one step on `stream`, using `side` for the branches that are

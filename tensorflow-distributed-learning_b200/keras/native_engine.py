@@ -206,6 +206,7 @@ class NativeCnnEngine:
             s.dense1_ksplit = max(1, d.F // 64)
             s.use_tma_conv = int(bool(self.lib.tfdl_cnn_tma_supported(C.byref(d))) and
                                  os.environ.get("TFDL_CONV_IMPL", "tma") == "tma")
+            s.use_fused_conv = int(bool(s.use_tma_conv) and os.environ.get("TFDL_CONV_FUSE", "1") == "1")
         last = self.buckets[0]
         ars = (FusedArParams * 2)(last.struct(0), last.struct(1))
         prog = C.c_void_p()

@@ -79,6 +79,29 @@ def conv1_wgrad(x: torch.Tensor, g1: torch.Tensor, idx1: torch.Tensor, d: CnnDim
     return g_w, g_b
 
 
+def conv12_fwd(x: torch.Tensor, w1: torch.Tensor, b1: torch.Tensor, w2h: torch.Tensor, b2: torch.Tensor, d: CnnDims):
+    """Fused conv1+pool+relu -> conv2+pool+relu forward. Returns (a1, idx1, a2, idx2)."""
+    dev = x.device
+    a1 = torch.empty((d.B, d.P1h, d.P1w, d.C1), dtype=torch.bfloat16, device=dev)
+    i1 = torch.empty((d.B, d.P1h, d.P1w, d.C1), dtype=torch.uint8, device=dev)
+    a2 = torch.empty((d.B, d.P2h, d.P2w, d.C2), dtype=torch.bfloat16, device=dev)
+    i2 = torch.empty((d.B, d.P2h, d.P2w, d.C2), dtype=torch.uint8, device=dev)
+    _lib.check(_lib.kernels().tfdl_cnn_conv12_fwd_tma(_p(x), _p(w1), _p(b1), _p(w2h), _p(b2), _p(a1), _p(i1), _p(a2), _p(i2),
+                                                      None, C.byref(d), _s()), "conv12_fwd_tma")
+    return a1, i1, a2, i2
+
+
+def conv21_bwd(dy2: torch.Tensor, w2h: torch.Tensor, a1: torch.Tensor, idx1: torch.Tensor, x: torch.Tensor, d: CnnDims):
+    """Fused conv2 dgrad (+ReLU mask) -> conv1 wgrad. Returns (g_w1c [C1,9], g_b1c [C1], g1 bf16)."""
+    dev = x.device
+    g_w = torch.zeros((d.C1, 9), device=dev)
+    g_b = torch.zeros((d.C1,), device=dev)
+    g1 = torch.zeros((d.B, d.P1h, d.P1w, d.C1), dtype=torch.bfloat16, device=dev)
+    _lib.check(_lib.kernels().tfdl_cnn_conv21_bwd_tma(_p(dy2), _p(w2h), _p(a1), _p(idx1), _p(x), _p(g_w), _p(g_b), _p(g1),
+                                                      C.byref(d), _s()), "conv21_bwd_tma")
+    return g_w, g_b, g1
+
+
 def dense_block(a2: torch.Tensor, idx2: torch.Tensor, w1h: torch.Tensor, w2h: torch.Tensor, b1: torch.Tensor,
                 b2: torch.Tensor, labels: torch.Tensor, d: CnnDims, acc: torch.Tensor = None,
                 acc_next: torch.Tensor = None, sync: torch.Tensor = None):
@@ -100,5 +123,5 @@ def dense_block(a2: torch.Tensor, idx2: torch.Tensor, w1h: torch.Tensor, w2h: to
     return out
 
 
-__all__ = ["dense_block", "conv1_fwd", "conv2_fwd", "head", "dense1_dgrad", "conv2_wgrad", "conv2_dgrad", "conv1_wgrad", "make_dims",
+__all__ = ["conv12_fwd", "conv21_bwd", "dense_block", "conv1_fwd", "conv2_fwd", "head", "dense1_dgrad", "conv2_wgrad", "conv2_dgrad", "conv1_wgrad", "make_dims",
            "CnnDims"]

@@ -54,6 +54,7 @@ class CnnStep(C.Structure):
         ("use_dense_block", C.c_int),
         ("acc_next", C.c_void_p),
         ("sync", C.c_void_p),
+        ("use_fused_conv", C.c_int),
     ]
 
 

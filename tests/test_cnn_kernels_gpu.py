@@ -235,3 +235,29 @@ def test_fused_dense_block_matches_fp32_reference(b):
         torch.testing.assert_close(out["dy2"][:, :10, :10].float(), ref, rtol=5e-2, atol=6e-4)
         assert torch.count_nonzero(out["acc_next"]) == 0  # the other parity's accumulator was cleared
         assert sync[0].item() == 25 * (rep + 1)
+
+
+def test_fused_conv_kernels_match_the_unfused_ones():
+    """conv1 fused into conv2 forward, and conv1 wgrad fused into conv2 dgrad, against the separately
+    validated kernels (bitwise for the forward, RED-order tolerance for the weight gradient)."""
+    from tfdl.ops import cnn
+
+    d = _dims()
+    torch.manual_seed(9)
+    x = torch.rand(B, 28, 28, device="cuda")
+    w1 = torch.randn(32, 9, device="cuda") * 0.3
+    b1 = torch.randn(32, device="cuda") * 0.1
+    w2 = _bf(torch.randn(64, 3, 3, 32, device="cuda") * 0.1)
+    b2 = torch.randn(64, device="cuda") * 0.1
+    a1r, i1r = cnn.conv1_fwd(x, w1, b1, d)
+    a2r, i2r = cnn.conv2_fwd(a1r, w2, b2, d, impl="tma")
+    a1, i1, a2, i2 = cnn.conv12_fwd(x, w1, b1, w2, b2, d)
+    assert torch.equal(a1, a1r) and torch.equal(i1, i1r)
+    assert torch.equal(a2, a2r) and torch.equal(i2, i2r)
+    grid, _ = _sparse_dy2()
+    g1r = cnn.conv2_dgrad(grid, w2, a1, d, impl="tma")
+    gwr, gbr = cnn.conv1_wgrad(x, g1r, i1, d)
+    gw, gb, g1 = cnn.conv21_bwd(grid, w2, a1, i1, x, d)
+    assert torch.equal(g1, g1r)
+    torch.testing.assert_close(gw, gwr, rtol=1e-4, atol=1e-4)
+    torch.testing.assert_close(gb, gbr, rtol=1e-4, atol=1e-4)

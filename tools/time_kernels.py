@@ -53,6 +53,8 @@ kernels = {
     "conv2_fwd_tma": lambda: L.tfdl_cnn_conv2_fwd_tma(p(a1), p(w2), p(b2), p(a2), p(i2), D, S()),
     "conv2_wgrad_tma": lambda: L.tfdl_cnn_conv2_wgrad_tma(p(a1), p(dy2), p(gwc), p(gbc), D, S()),
     "conv2_dgrad_tma": lambda: L.tfdl_cnn_conv2_dgrad_tma(p(dy2), p(w2), p(a1), p(g1), D, S()),
+    "conv12_fwd_tma": lambda: L.tfdl_cnn_conv12_fwd_tma(p(x), p(w1), p(b1), p(w2), p(b2), p(a1), p(i1), p(a2), p(i2), None, D, S()),
+    "conv21_bwd_tma": lambda: L.tfdl_cnn_conv21_bwd_tma(p(dy2), p(w2), p(a1), p(i1), p(x), p(gw1c), p(gb1c), None, D, S()),
     "conv1_wgrad": lambda: L.tfdl_cnn_conv1_wgrad(p(x), p(g1), p(i1), p(gw1c), p(gb1c), D, S()),
 }
 N = 50
