@@ -2,7 +2,12 @@
 // layers of the larger configs in BASELINE.json: ResNet-50's classifier, BERT-base's QKV /
 // FFN projections; same op as tf.keras.layers.Dense in /root/reference/tf_dist_example.py:46).
 //
-//   D[M,N] = act(A[M,K] * B[N,K]^T + bias[N])      A, B bf16 row-major (K contiguous)
+//   D[M,N] = act(A[M,K] * B[N,K]^T + bias[N])      A, B bf16; each operand either K-major (row-major [rows][K])
+//                                                  or MN-major (stored transposed, [K][rows]) - the two layouts a
+//                                                  Dense layer's forward / dgrad / wgrad need, with no transposes:
+//       forward  y  = x  W^T      A = x  [tok][in]  K-major    B = W  [out][in]  K-major
+//       dgrad    dx = dy W        A = dy [tok][out] K-major    B = W  [out][in]  MN-major (K = out)
+//       wgrad    dW = dy^T x      A = dy [tok][out] MN-major   B = x  [tok][in]  MN-major (K = tok)
 //
 // Shape of the kernel (one CTA per SM, 192 threads):
 //   warp 0      TMA producer: cp.async.bulk.tensor.2d tiles (128B swizzle) into a STAGES-deep ring
@@ -27,6 +32,7 @@ struct TmaGemmParams {
   int M, N, K, ldd;
   int act;                 // 0 none, 1 relu, 2 gelu(tanh)
   int m_tiles, n_tiles;
+  int a_mn, b_mn;          // operand stored [K][rows] (MN-major) instead of [rows][K]
 };
 
 __device__ __forceinline__ float apply_act(float x, int act) {
@@ -91,8 +97,19 @@ tma_gemm_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__
           mbar_wait(&empty_bar[stage], phase ^ 1);
           mbar_expect_tx(&full_bar[stage], STAGE_BYTES);
           const uint32_t sa = smem_base + stage * STAGE_BYTES;
-          tma_load_2d(sa, &tmA, kb * BK, mt * BM, &full_bar[stage]);
-          tma_load_2d(sa + A_BYTES, &tmB, kb * BK, nt * BN, &full_bar[stage]);
+          if (!p.a_mn) {
+            tma_load_2d(sa, &tmA, kb * BK, mt * BM, &full_bar[stage]);
+          } else {  // [K rows][64 MN columns] blocks of 8 KB, one per 64 rows of the tile
+#pragma unroll
+            for (int b = 0; b < BM / 64; ++b) tma_load_2d(sa + b * 8192, &tmA, mt * BM + b * 64, kb * BK, &full_bar[stage]);
+          }
+          if (!p.b_mn) {
+            tma_load_2d(sa + A_BYTES, &tmB, kb * BK, nt * BN, &full_bar[stage]);
+          } else {
+#pragma unroll
+            for (int b = 0; b < BN / 64; ++b)
+              tma_load_2d(sa + A_BYTES + b * 8192, &tmB, nt * BN + b * 64, kb * BK, &full_bar[stage]);
+          }
           if (++stage == STAGES) { stage = 0; phase ^= 1; }
         }
       }
@@ -100,7 +117,7 @@ tma_gemm_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__
   } else if (warp == 1) {
     // ------------------------------ MMA issuer --------------------------------
     if (elect_one()) {
-      constexpr uint32_t idesc = umma_idesc_bf16(BM, BN, false, false);
+      const uint32_t idesc = umma_idesc_bf16(BM, BN, p.a_mn != 0, p.b_mn != 0);
       uint32_t stage = 0, phase = 0, as = 0, aphase = 0;
       for (int t = blockIdx.x; t < num_tiles; t += gridDim.x) {
         mbar_wait(&acc_empty[as], aphase ^ 1);
@@ -113,9 +130,12 @@ tma_gemm_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__
           const uint32_t sb = sa + A_BYTES;
 #pragma unroll
           for (int k = 0; k < BK / 16; ++k) {
-            // K-major, 128B swizzle: 8-row atoms 1024 B apart; a K step of 16 bf16 = +32 B
-            uint64_t ad = umma_smem_desc(sa + k * 32, 16, 1024, SWZ_128B);
-            uint64_t bd = umma_smem_desc(sb + k * 32, 16, 1024, SWZ_128B);
+            // K-major, 128B swizzle: 8-row atoms 1024 B apart; a K step of 16 bf16 = +32 B.
+            // MN-major: rows are K, 64-element MN blocks 8 KB apart (LBO); a K step = 16 rows = +2 KB.
+            uint64_t ad = p.a_mn ? umma_smem_desc(sa + k * 2048, 8192, 1024, SWZ_128B)
+                                 : umma_smem_desc(sa + k * 32, 16, 1024, SWZ_128B);
+            uint64_t bd = p.b_mn ? umma_smem_desc(sb + k * 2048, 8192, 1024, SWZ_128B)
+                                 : umma_smem_desc(sb + k * 32, 16, 1024, SWZ_128B);
             umma_bf16(d_tmem, ad, bd, idesc, (kb | k) != 0);
           }
           umma_commit(&empty_bar[stage]);
@@ -225,9 +245,10 @@ int make_tmap_bf16_2d(CUtensorMap* out, const void* base, uint64_t rows, uint64_
 template <int BN, int STAGES>
 static int launch_tma_gemm(const void* A, const void* B, TmaGemmParams p, int lda, int ldb, cudaStream_t s) {
   CUtensorMap tmA, tmB;
-  int rc = make_tmap_bf16_2d(&tmA, A, p.M, p.K, lda, BM, BK);
+  // K-major operand: matrix [rows][K], box (BK x tile rows). MN-major: matrix [K][rows], box (64 x BK).
+  int rc = p.a_mn ? make_tmap_bf16_2d(&tmA, A, p.K, p.M, lda, BK, 64) : make_tmap_bf16_2d(&tmA, A, p.M, p.K, lda, BM, BK);
   if (rc) return rc;
-  rc = make_tmap_bf16_2d(&tmB, B, p.N, p.K, ldb, BN, BK);
+  rc = p.b_mn ? make_tmap_bf16_2d(&tmB, B, p.K, p.N, ldb, BK, 64) : make_tmap_bf16_2d(&tmB, B, p.N, p.K, ldb, BN, BK);
   if (rc) return rc;
   p.m_tiles = (p.M + BM - 1) / BM;
   p.n_tiles = (p.N + BN - 1) / BN;
@@ -247,12 +268,21 @@ static int launch_tma_gemm(const void* A, const void* B, TmaGemmParams p, int ld
 
 extern "C" int tfdl_gemm_bf16_tma(const void* A, const void* B, float* Df, void* Dh, const float* bias, int M,
                                   int N, int K, int lda, int ldb, int ldd, int act, void* stream) {
+  return tfdl_gemm_bf16_tma_ex(A, B, Df, Dh, bias, M, N, K, lda, ldb, ldd, 0, 0, act, stream);
+}
+
+extern "C" int tfdl_gemm_bf16_tma_ex(const void* A, const void* B, float* Df, void* Dh, const float* bias, int M,
+                                     int N, int K, int lda, int ldb, int ldd, int a_mn, int b_mn, int act,
+                                     void* stream) {
   using namespace tfdl;
   TFDL_REQUIRE(M > 0 && N > 0 && K > 0, "gemm_tma: empty problem");
-  TFDL_REQUIRE(K % 8 == 0 && lda % 8 == 0 && ldb % 8 == 0, "gemm_tma: K, lda, ldb must be multiples of 8");
+  TFDL_REQUIRE(lda % 8 == 0 && ldb % 8 == 0, "gemm_tma: lda, ldb must be multiples of 8");
+  TFDL_REQUIRE((a_mn ? M : K) % 8 == 0 && (b_mn ? N : K) % 8 == 0,
+               "gemm_tma: the contiguous dimension of each operand must be a multiple of 8");
   TFDL_REQUIRE(((uintptr_t)A & 15) == 0 && ((uintptr_t)B & 15) == 0, "gemm_tma: A/B must be 16-byte aligned");
   TmaGemmParams p{};
   p.Df = Df; p.Dh = (__nv_bfloat16*)Dh; p.bias = bias; p.M = M; p.N = N; p.K = K; p.ldd = ldd; p.act = act;
+  p.a_mn = a_mn; p.b_mn = b_mn;
   cudaStream_t s = (cudaStream_t)stream;
   // Tile choice: 128x256 when there are enough tiles to fill the chip, else 128x128 / 128x64
   long tiles256 = (long)((M + 127) / 128) * ((N + 255) / 256);

@@ -71,6 +71,10 @@ int tfdl_dense_fwd_splitk_static(const void* x_bf16, const void* w_bf16, const f
  * act: 0 none, 1 relu, 2 gelu(tanh). K, lda, ldb % 8 == 0; A, B 16-byte aligned. */
 int tfdl_gemm_bf16_tma(const void* A, const void* B, float* Df, void* Dh, const float* bias, int M, int N,
                        int K, int lda, int ldb, int ldd, int act, void* stream);
+/* Same kernel with either operand MN-major (a_mn: A stored [K][M]; b_mn: B stored [K][N]), loaded as 64-wide
+ * 128B-swizzled column blocks: Dense dgrad (dy W) and wgrad (dy^T x) without transposing anything. */
+int tfdl_gemm_bf16_tma_ex(const void* A, const void* B, float* Df, void* Dh, const float* bias, int M, int N,
+                          int K, int lda, int ldb, int ldd, int a_mn, int b_mn, int act, void* stream);
 
 
 /* ---- fused gradient all-reduce + SGD over NVLink peer memory ------------------------------

@@ -473,6 +473,22 @@ class TorchEngine:
         self.strategy = model.strategy
         self.devices = self.strategy.local_devices
         self.leaves: List[Dict[int, torch.Tensor]] = []
+        self._fused = None
+        self._fused_lr = None
+        ops = self.strategy.cross_device_ops
+        if (type(ops).__name__ == "P2PFusedAllReduce" and isinstance(model.optimizer, _optimizers.SGD)
+                and len(self.devices) == 1 and os.environ.get("TFDL_TORCH_FUSED_AR", "1") == "1"):
+            # GPU process group + SGD: the gradient all-reduce, 1/N scale and the (momentum) update are ONE
+            # NVLink kernel over the arena (ops/allreduce.py) even though forward/backward run on torch ops.
+            # A single gradient buffer is used here, so only the variants with an end barrier are legal.
+            arena = model.arenas[0]
+            st = ops.fused_state(arena.params, arena.grads, momentum=bool(model.optimizer.momentum))
+            if model.optimizer.momentum:
+                model.optimizer._slots = {"momentum": [st.mom]}
+            from ..ops.structs import AR_MULTIMEM, AR_ONESHOT, AR_TWOSHOT
+
+            st.torch_algo = AR_ONESHOT if ops.world == 1 else (AR_MULTIMEM if st.has_multicast else AR_TWOSHOT)
+            self._fused = st
         for r, arena in enumerate(model.arenas):
             d: Dict[int, torch.Tensor] = {}
             for w in model.weights:
@@ -510,13 +526,24 @@ class TorchEngine:
             if n == 0:
                 continue
             xt, yt = self._to_device(x, dev), self._to_device(y, dev)
-            pred = m._forward(xt, self._ctx(r, True))
+            ctx = self._ctx(r, True)
+            pred = m._forward(xt, ctx)
             per = m.loss.per_example(yt, pred)
             (per.mean() / nrep).backward()
+            for fn in ctx.deferred:
+                fn()
             m.loss_tracker.add(r, per.detach().sum(), float(per.numel()))
             with torch.no_grad():
                 for met in m.compiled_metrics:
                     met.update_state(yt, pred.detach(), r)
+        if self._fused is not None:
+            opt = m.optimizer
+            if self._fused_lr != opt.learning_rate:
+                self._fused_lr = opt.learning_rate
+                self._fused.set_hyper(opt.learning_rate, opt.momentum, opt.nesterov, 1.0)
+            self._fused.step(0, self._fused.torch_algo)
+            m.optimizer.step_done()
+            return
         s.cross_device_ops.allreduce_grads([a.grads for a in m.arenas])
         with torch.no_grad():
             for r, arena in enumerate(m.arenas):

@@ -112,6 +112,9 @@ class CallContext:
     def __init__(self, replica: int, training: bool, param: Callable[[MirroredVariable], torch.Tensor],
                  compute_dtype: torch.dtype = torch.float32) -> None:
         self.replica, self.training, self.param, self.compute_dtype = replica, training, param, compute_dtype
+        # in-place updates of non-trainable variables (BatchNorm statistics) that must wait until autograd
+        # has finished: every variable is a view of one arena, so they share a version counter
+        self.deferred: List[Callable[[], None]] = []
 
 
 class Layer:
@@ -330,6 +333,13 @@ class Dense(Layer):
         assert self.kernel is not None
         w = ctx.param(self.kernel)
         b = ctx.param(self.bias) if self.bias is not None else None
+        if (x.is_cuda and ctx.compute_dtype == torch.bfloat16 and self.activation in (None, "linear", "relu", "gelu")
+                and x.shape[-1] % 8 == 0 and self.units % 8 == 0 and (x.numel() // x.shape[-1]) % 8 == 0):
+            # mixed_bfloat16 on a B200: forward, input-gradient and weight-gradient GEMMs on the persistent
+            # TMA + tcgen05 kernel (ops/gemm.py), fp32 master weights and fp32 weight gradients
+            from ..ops.gemm import linear as _tc_linear
+
+            return _tc_linear(x, w, b, None if self.activation == "linear" else self.activation)
         if ctx.compute_dtype != torch.float32:
             x, w = x.to(ctx.compute_dtype), w.to(ctx.compute_dtype)
             b = b.to(ctx.compute_dtype) if b is not None else None
@@ -386,9 +396,14 @@ class BatchNormalization(Layer):
         xf = x.float()
         if ctx.training:
             mean, var = xf.mean(dims), xf.var(dims, unbiased=False)
-            with torch.no_grad():
-                mm.mul_(self.momentum).add_(mean.detach(), alpha=1 - self.momentum)
-                mv.mul_(self.momentum).add_(var.detach(), alpha=1 - self.momentum)
+            m_d, v_d, mom = mean.detach(), var.detach(), self.momentum
+
+            def _update(mm=mm, mv=mv, m_d=m_d, v_d=v_d, mom=mom) -> None:
+                with torch.no_grad():
+                    mm.mul_(mom).add_(m_d, alpha=1 - mom)
+                    mv.mul_(mom).add_(v_d, alpha=1 - mom)
+
+            ctx.deferred.append(_update)
         else:
             mean, var = mm, mv
         y = (xf - mean) * torch.rsqrt(var + self.epsilon) * g + b

@@ -88,3 +88,36 @@ def test_dense_forward_splitk_scratch_roundtrip(B, N, K, relu):
         ref = torch.relu(ref) if relu else ref
         torch.testing.assert_close(out.float(), ref, rtol=2e-2, atol=0.1)
         assert torch.count_nonzero(scratch) == 0
+
+
+@pytest.mark.parametrize("a_mn,b_mn", [(False, True), (True, False), (True, True)])
+@pytest.mark.parametrize("M,N,K", [(256, 256, 512), (1000, 200, 1608), (768, 3072, 4096), (128, 64, 64)])
+def test_tma_gemm_mn_major_operands(M, N, K, a_mn, b_mn):
+    from tfdl.ops.gemm import gemm_tma
+
+    torch.manual_seed(5)
+    a = (torch.randn((K, M) if a_mn else (M, K), device="cuda") * 0.5).bfloat16()
+    b = (torch.randn((K, N) if b_mn else (N, K), device="cuda") * 0.5).bfloat16()
+    out = gemm_tma(a, b, a_mn=a_mn, b_mn=b_mn, out_dtype=torch.float32)
+    torch.testing.assert_close(out, _ref(a, b, a_mn, b_mn), rtol=2e-3, atol=2e-2 * (K ** 0.5) / 8)
+
+
+@pytest.mark.parametrize("act", [None, "relu", "gelu"])
+def test_linear_autograd_all_three_gemms_on_tcgen05(act):
+    from tfdl.ops.gemm import linear
+
+    torch.manual_seed(6)
+    x = (torch.randn(4, 128, 768, device="cuda") * 0.5).requires_grad_()
+    w = (torch.randn(3072, 768, device="cuda") * 0.03).requires_grad_()
+    b = torch.randn(3072, device="cuda").requires_grad_()
+    y = linear(x, w, b, act)
+    gy = torch.randn_like(y.float()) * 0.1
+    y.float().backward(gy)
+    xr, wr, br = [t.detach().clone().requires_grad_() for t in (x, w, b)]
+    pre = torch.nn.functional.linear(xr.bfloat16().float(), wr.bfloat16().float(), br)
+    yr = {None: lambda t: t, "relu": torch.relu, "gelu": lambda t: torch.nn.functional.gelu(t, approximate="tanh")}[act](pre)
+    yr.backward(gy)
+    torch.testing.assert_close(y.float(), yr, rtol=2e-2, atol=5e-2)
+    torch.testing.assert_close(x.grad, xr.grad, rtol=5e-2, atol=2e-2)
+    torch.testing.assert_close(w.grad, wr.grad, rtol=5e-2, atol=5e-2)
+    torch.testing.assert_close(b.grad, br.grad, rtol=2e-2, atol=5e-2)
