@@ -14,8 +14,11 @@
 //   warp 1      MMA issuer: one elected lane issues tcgen05.mma (128 x BN x 16) from smem descriptors,
 //               accumulating in TMEM; tcgen05.commit releases ring slots / publishes accumulators
 //   warps 2-5   epilogue: tcgen05.ld the accumulator (each warp its own 32-lane quarter), bias +
-//               activation, 128-bit global stores. Two TMEM accumulator stages let the epilogue
-//               of tile i overlap the MMAs of tile i+1.
+//               activation, then 128-byte rows staged in shared memory (128B swizzle, conflict-free) and
+//               written with cp.async.bulk.tensor stores - fully coalesced, clipped at the matrix edge by
+//               the tensor map; each warp double-buffers its own 32-row staging tile. (A row-per-thread
+//               direct store is kept for outputs whose pitch is not a multiple of 16 bytes.) Two TMEM
+//               accumulator stages let the epilogue of tile i overlap the MMAs of tile i+1.
 #include <cuda.h>
 #include "common.cuh"
 #include "../../include/tfdl_kernels.h"
@@ -33,22 +36,66 @@ struct TmaGemmParams {
   int act;                 // 0 none, 1 relu, 2 gelu(tanh)
   int m_tiles, n_tiles;
   int a_mn, b_mn;          // operand stored [K][rows] (MN-major) instead of [rows][K]
+  int tma_store;           // epilogue through smem + TMA store (needs a 16-byte-multiple output pitch)
 };
 
-__device__ __forceinline__ float apply_act(float x, int act) {
-  if (act == 1) return fmaxf(x, 0.f);
-  if (act == 2) {
+constexpr uint32_t EPI_STAGE_BYTES = 4096;                  // 32 rows x 128 B, per warp per buffer
+constexpr uint32_t EPI_SMEM_BYTES = 4 * 2 * EPI_STAGE_BYTES;  // 4 epilogue warps, double buffered
+
+// Activation as a compile-time choice: with a run-time switch per element the compiler evaluates the
+// tanh path unconditionally and the four epilogue warps, not the tensor core, set the tile time.
+template <int ACT>
+__device__ __forceinline__ float act_fn(float x) {
+  if (ACT == 1) return fmaxf(x, 0.f);
+  if (ACT == 2) {
     const float k0 = 0.7978845608028654f, k1 = 0.044715f;
-    float u = k0 * (x + k1 * x * x * x);
-    return 0.5f * x * (1.f + tanhf(u));
+    float t, u = k0 * (x + k1 * x * x * x);
+    asm("tanh.approx.f32 %0, %1;" : "=f"(t) : "f"(u));
+    return 0.5f * x * (1.f + t);
   }
   return x;
+}
+__device__ __forceinline__ uint32_t pack2(uint32_t lo, uint32_t hi) {
+  return pack_bf16x2(__uint_as_float(lo), __uint_as_float(hi));
+}
+// v[i] <- act(v[i] + bias[col0 + i]) for 32 accumulator columns held as fp32 bit patterns.
+template <int ACT, bool BIAS>
+__device__ __forceinline__ void epi_apply_t(uint32_t (&v)[32], const float* bias, int col0, int N) {
+  const bool vec = BIAS && col0 + 32 <= N && ((reinterpret_cast<uintptr_t>(bias + col0) & 15) == 0);
+#pragma unroll
+  for (int i = 0; i < 32; i += 4) {
+    float4 b = make_float4(0.f, 0.f, 0.f, 0.f);
+    if (BIAS) {
+      if (vec) {
+        b = __ldg(reinterpret_cast<const float4*>(bias + col0 + i));
+      } else {
+        b.x = col0 + i < N ? __ldg(bias + col0 + i) : 0.f;
+        b.y = col0 + i + 1 < N ? __ldg(bias + col0 + i + 1) : 0.f;
+        b.z = col0 + i + 2 < N ? __ldg(bias + col0 + i + 2) : 0.f;
+        b.w = col0 + i + 3 < N ? __ldg(bias + col0 + i + 3) : 0.f;
+      }
+    }
+    v[i] = __float_as_uint(act_fn<ACT>(__uint_as_float(v[i]) + b.x));
+    v[i + 1] = __float_as_uint(act_fn<ACT>(__uint_as_float(v[i + 1]) + b.y));
+    v[i + 2] = __float_as_uint(act_fn<ACT>(__uint_as_float(v[i + 2]) + b.z));
+    v[i + 3] = __float_as_uint(act_fn<ACT>(__uint_as_float(v[i + 3]) + b.w));
+  }
+}
+__device__ __forceinline__ void epi_apply(uint32_t (&v)[32], const float* bias, int col0, int N, int act) {
+  if (bias) {
+    if (act == 1) epi_apply_t<1, true>(v, bias, col0, N);
+    else if (act == 2) epi_apply_t<2, true>(v, bias, col0, N);
+    else epi_apply_t<0, true>(v, bias, col0, N);
+  } else {
+    if (act == 1) epi_apply_t<1, false>(v, bias, col0, N);
+    else if (act == 2) epi_apply_t<2, false>(v, bias, col0, N);
+  }
 }
 
 template <int BN, int STAGES>
 __global__ void __launch_bounds__(192, 1)
 tma_gemm_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ CUtensorMap tmB,
-                TmaGemmParams p) {
+                const __grid_constant__ CUtensorMap tmD, TmaGemmParams p) {
   extern __shared__ __align__(1024) uint8_t smem_raw[];
   // 1024-byte alignment is required by the 128B swizzle atom (8 rows x 128 B).
   uint8_t* smem = reinterpret_cast<uint8_t*>((reinterpret_cast<uintptr_t>(smem_raw) + 1023) & ~uintptr_t(1023));
@@ -67,6 +114,7 @@ tma_gemm_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__
     if (elect_one()) {
       tma_prefetch_desc(&tmA);
       tma_prefetch_desc(&tmB);
+      if (p.tma_store) tma_prefetch_desc(&tmD);
     }
     tmem_alloc(&tmem_slot, TMEM_COLS);
   }
@@ -148,48 +196,89 @@ tma_gemm_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__
   } else {
     // ------------------------------ epilogue ----------------------------------
     const int q = warp & 3;  // TMEM lane quarter this warp may read
-    uint32_t as = 0, aphase = 0;
+    uint32_t as = 0, aphase = 0, sb = 0;
+    const uint32_t stg_base = smem_base + STAGES * STAGE_BYTES + q * 2 * EPI_STAGE_BYTES;
     for (int t = blockIdx.x; t < num_tiles; t += gridDim.x) {
       const int mt = t % p.m_tiles, nt = t / p.m_tiles;
       mbar_wait(&acc_full[as], aphase);
       tc_fence_after_sync();
       const int row = mt * BM + q * 32 + (int)lane_id();
       const uint32_t t_row = tmem_base + as * BN + ((uint32_t)(q * 32) << 16);
+      if (p.tma_store) {
+        const int row0 = mt * BM + q * 32;
+        const int CH = p.Dh ? 64 : 32;  // output columns per 128-byte staged row
+        const uint32_t lane = lane_id();
 #pragma unroll 1
-      for (int c = 0; c < BN; c += 32) {
-        uint32_t v[32];
-        tmem_ld32(t_row + c, v);
-        tmem_ld_wait();
-        const int col0 = nt * BN + c;
-        if (row < p.M && col0 < p.N) {
-          float x[32];
-#pragma unroll
-          for (int i = 0; i < 32; ++i) {
-            float b = (p.bias && col0 + i < p.N) ? __ldg(p.bias + col0 + i) : 0.f;
-            x[i] = apply_act(__uint_as_float(v[i]) + b, p.act);
-          }
-          const bool full = (col0 + 32 <= p.N);
+        for (int c = 0; c < BN && row0 < p.M; c += CH) {
+          const int col0 = nt * BN + c;
+          if (col0 >= p.N) break;
+          uint32_t v[32], v2[32];
+          tmem_ld32(t_row + c, v);
+          if (p.Dh) tmem_ld32(t_row + c + 32, v2);
+          tmem_ld_wait();
+          epi_apply(v, p.bias, col0, p.N, p.act);
+          if (p.Dh) epi_apply(v2, p.bias, col0 + 32, p.N, p.act);
+          // the bulk store that last read this staging buffer (two chunks ago) must have drained it
+          if (lane == 0) asm volatile("cp.async.bulk.wait_group.read 1;" ::: "memory");
+          __syncwarp();
+          const uint32_t sbuf = stg_base + sb * EPI_STAGE_BYTES;
+          const uint32_t srow = sbuf + lane * 128;
           if (p.Dh) {
-            __nv_bfloat16* dst = p.Dh + (size_t)row * p.ldd + col0;
-            if (full && ((reinterpret_cast<uintptr_t>(dst) & 15) == 0)) {
 #pragma unroll
-              for (int i = 0; i < 32; i += 8) {
-                uint4 o = make_uint4(pack_bf16x2(x[i], x[i + 1]), pack_bf16x2(x[i + 2], x[i + 3]),
-                                     pack_bf16x2(x[i + 4], x[i + 5]), pack_bf16x2(x[i + 6], x[i + 7]));
-                *reinterpret_cast<uint4*>(dst + i) = o;
-              }
-            } else {
-              for (int i = 0; i < 32 && col0 + i < p.N; ++i) dst[i] = __float2bfloat16(x[i]);
+            for (int j = 0; j < 4; ++j) {
+              st_shared_v4(srow + ((uint32_t)(j ^ (lane & 7)) << 4), pack2(v[j * 8], v[j * 8 + 1]),
+                           pack2(v[j * 8 + 2], v[j * 8 + 3]), pack2(v[j * 8 + 4], v[j * 8 + 5]),
+                           pack2(v[j * 8 + 6], v[j * 8 + 7]));
+              st_shared_v4(srow + ((uint32_t)((j + 4) ^ (lane & 7)) << 4), pack2(v2[j * 8], v2[j * 8 + 1]),
+                           pack2(v2[j * 8 + 2], v2[j * 8 + 3]), pack2(v2[j * 8 + 4], v2[j * 8 + 5]),
+                           pack2(v2[j * 8 + 6], v2[j * 8 + 7]));
             }
-          }
-          if (p.Df) {
-            float* dst = p.Df + (size_t)row * p.ldd + col0;
-            if (full && ((reinterpret_cast<uintptr_t>(dst) & 15) == 0)) {
+          } else {
 #pragma unroll
-              for (int i = 0; i < 32; i += 4)
-                *reinterpret_cast<float4*>(dst + i) = make_float4(x[i], x[i + 1], x[i + 2], x[i + 3]);
-            } else {
-              for (int i = 0; i < 32 && col0 + i < p.N; ++i) dst[i] = x[i];
+            for (int j = 0; j < 8; ++j)
+              st_shared_v4(srow + ((uint32_t)(j ^ (lane & 7)) << 4), v[j * 4], v[j * 4 + 1], v[j * 4 + 2], v[j * 4 + 3]);
+          }
+          fence_proxy_async_smem();
+          __syncwarp();
+          if (lane == 0) {
+            tma_store_2d(&tmD, sbuf, col0, row0);
+            tma_store_commit();
+          }
+          sb ^= 1;
+        }
+      } else {
+#pragma unroll 1
+        for (int c = 0; c < BN; c += 32) {
+          uint32_t v[32];
+          tmem_ld32(t_row + c, v);
+          tmem_ld_wait();
+          const int col0 = nt * BN + c;
+          if (row < p.M && col0 < p.N) {
+            epi_apply(v, p.bias, col0, p.N, p.act);
+            const bool full = (col0 + 32 <= p.N);
+            if (p.Dh) {
+              __nv_bfloat16* dst = p.Dh + (size_t)row * p.ldd + col0;
+              if (full && ((reinterpret_cast<uintptr_t>(dst) & 15) == 0)) {
+#pragma unroll
+                for (int i = 0; i < 32; i += 8)
+                  *reinterpret_cast<uint4*>(dst + i) = make_uint4(pack2(v[i], v[i + 1]), pack2(v[i + 2], v[i + 3]),
+                                                                  pack2(v[i + 4], v[i + 5]), pack2(v[i + 6], v[i + 7]));
+              } else {
+#pragma unroll
+                for (int i = 0; i < 32; ++i)
+                  if (col0 + i < p.N) dst[i] = __float2bfloat16(__uint_as_float(v[i]));
+              }
+            }
+            if (p.Df) {
+              float* dst = p.Df + (size_t)row * p.ldd + col0;
+              if (full && ((reinterpret_cast<uintptr_t>(dst) & 15) == 0)) {
+#pragma unroll
+                for (int i = 0; i < 32; i += 4) *reinterpret_cast<uint4*>(dst + i) = make_uint4(v[i], v[i + 1], v[i + 2], v[i + 3]);
+              } else {
+#pragma unroll
+                for (int i = 0; i < 32; ++i)
+                  if (col0 + i < p.N) dst[i] = __uint_as_float(v[i]);
+              }
             }
           }
         }
@@ -199,6 +288,7 @@ tma_gemm_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__
       if (lane_id() == 0) mbar_arrive(&acc_empty[as]);
       if (++as == 2) { as = 0; aphase ^= 1; }
     }
+    if (lane_id() == 0) tma_store_wait_all();  // staging smem must outlive the bulk stores reading it
   }
   tc_fence_before_sync();
   __syncthreads();
@@ -242,24 +332,53 @@ int make_tmap_bf16_2d(CUtensorMap* out, const void* base, uint64_t rows, uint64_
   return 0;
 }
 
+// Output matrix [rows][cols] (pitch ld elements, 2- or 4-byte elements): 32-row x 128-byte boxes, 128B swizzle.
+static int make_tmap_out(CUtensorMap* out, const void* base, uint64_t rows, uint64_t cols, uint64_t ld, bool f32) {
+  EncodeTiledFn fn = get_encode_fn();
+  TFDL_REQUIRE(fn, "cuTensorMapEncodeTiled not available from the driver");
+  const uint64_t es = f32 ? 4 : 2;
+  cuuint64_t dims[2] = {cols, rows};
+  cuuint64_t strides[1] = {ld * es};
+  cuuint32_t box[2] = {(cuuint32_t)(128 / es), 32};
+  cuuint32_t estr[2] = {1, 1};
+  CUresult r = fn(out, f32 ? CU_TENSOR_MAP_DATA_TYPE_FLOAT32 : CU_TENSOR_MAP_DATA_TYPE_BFLOAT16, 2,
+                  const_cast<void*>(base), dims, strides, box, estr, CU_TENSOR_MAP_INTERLEAVE_NONE,
+                  CU_TENSOR_MAP_SWIZZLE_128B, CU_TENSOR_MAP_L2_PROMOTION_NONE, CU_TENSOR_MAP_FLOAT_OOB_FILL_NONE);
+  TFDL_REQUIRE(r == CUDA_SUCCESS, "cuTensorMapEncodeTiled (output) failed with CUresult %d", (int)r);
+  return 0;
+}
+
 template <int BN, int STAGES>
 static int launch_tma_gemm(const void* A, const void* B, TmaGemmParams p, int lda, int ldb, cudaStream_t s) {
-  CUtensorMap tmA, tmB;
+  CUtensorMap tmA, tmB, tmD;
   // K-major operand: matrix [rows][K], box (BK x tile rows). MN-major: matrix [K][rows], box (64 x BK).
   int rc = p.a_mn ? make_tmap_bf16_2d(&tmA, A, p.K, p.M, lda, BK, 64) : make_tmap_bf16_2d(&tmA, A, p.M, p.K, lda, BM, BK);
   if (rc) return rc;
   rc = p.b_mn ? make_tmap_bf16_2d(&tmB, B, p.K, p.N, ldb, BK, 64) : make_tmap_bf16_2d(&tmB, B, p.N, p.K, ldb, BN, BK);
   if (rc) return rc;
+  const void* D = p.Dh ? (const void*)p.Dh : (const void*)p.Df;
+  const size_t es = p.Dh ? 2 : 4;
+  p.tma_store = (!(p.Dh && p.Df) && ((size_t)p.ldd * es) % 16 == 0 && ((uintptr_t)D & 15) == 0) ? 1 : 0;
+  if (p.tma_store) {
+    rc = make_tmap_out(&tmD, D, p.M, p.N, p.ldd, !p.Dh);
+    if (rc) return rc;
+  } else {
+    tmD = tmA;  // unused by the kernel
+  }
   p.m_tiles = (p.M + BM - 1) / BM;
   p.n_tiles = (p.N + BN - 1) / BN;
-  constexpr size_t smem = (size_t)STAGES * (BM * BK * 2 + BN * BK * 2) + 1024;
+  constexpr size_t smem = (size_t)STAGES * (BM * BK * 2 + BN * BK * 2) + EPI_SMEM_BYTES + 1024;
   auto kern = tma_gemm_kernel<BN, STAGES>;
-  TFDL_CUDA_OK(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
-  int dev = 0, sms = 148;
-  TFDL_CUDA_OK(cudaGetDevice(&dev));
-  TFDL_CUDA_OK(cudaDeviceGetAttribute(&sms, cudaDevAttrMultiProcessorCount, dev));
+  static int sms = 0;  // per template instance: attribute + SM count are set once (all devices of a node are alike)
+  if (!sms) {
+    TFDL_CUDA_OK(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
+    int dev = 0, n = 148;
+    TFDL_CUDA_OK(cudaGetDevice(&dev));
+    TFDL_CUDA_OK(cudaDeviceGetAttribute(&n, cudaDevAttrMultiProcessorCount, dev));
+    sms = n;
+  }
   int grid = p.m_tiles * p.n_tiles < sms ? p.m_tiles * p.n_tiles : sms;
-  kern<<<grid, 192, smem, s>>>(tmA, tmB, p);
+  kern<<<grid, 192, smem, s>>>(tmA, tmB, tmD, p);
   TFDL_CUDA_OK(cudaGetLastError());
   return 0;
 }

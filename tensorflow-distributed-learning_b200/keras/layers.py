@@ -392,18 +392,36 @@ class BatchNormalization(Layer):
     def call(self, x: torch.Tensor, ctx: CallContext) -> torch.Tensor:
         g, b = ctx.param(self.gamma), ctx.param(self.beta)
         mm, mv = ctx.param(self.moving_mean), ctx.param(self.moving_variance)
+        if x.dim() == 4:
+            # NHWC activations viewed as channels_last NCHW: one fused (cuDNN) batch-norm kernel. The running
+            # statistics are updated on private copies and written back after autograd has finished, because
+            # every variable is a view of one arena and in-place writes would invalidate saved tensors.
+            xin = x.permute(0, 3, 1, 2)
+            if ctx.training:
+                rm, rv = mm.detach().clone(), mv.detach().clone()
+                y = F.batch_norm(xin, rm, rv, g, b, True, 1.0 - self.momentum, self.epsilon)
+
+                def _update(mm=mm, mv=mv, rm=rm, rv=rv) -> None:
+                    with torch.no_grad():
+                        mm.copy_(rm)
+                        mv.copy_(rv)
+
+                ctx.deferred.append(_update)
+            else:
+                y = F.batch_norm(xin, mm, mv, g, b, False, 0.0, self.epsilon)
+            return y.permute(0, 2, 3, 1)
         dims = tuple(range(x.dim() - 1))
         xf = x.float()
         if ctx.training:
             mean, var = xf.mean(dims), xf.var(dims, unbiased=False)
             m_d, v_d, mom = mean.detach(), var.detach(), self.momentum
 
-            def _update(mm=mm, mv=mv, m_d=m_d, v_d=v_d, mom=mom) -> None:
+            def _update2(mm=mm, mv=mv, m_d=m_d, v_d=v_d, mom=mom) -> None:
                 with torch.no_grad():
                     mm.mul_(mom).add_(m_d, alpha=1 - mom)
                     mv.mul_(mom).add_(v_d, alpha=1 - mom)
 
-            ctx.deferred.append(_update)
+            ctx.deferred.append(_update2)
         else:
             mean, var = mm, mv
         y = (xf - mean) * torch.rsqrt(var + self.epsilon) * g + b

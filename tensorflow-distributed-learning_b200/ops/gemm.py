@@ -79,7 +79,7 @@ class _LinearFn(torch.autograd.Function):
         ctx.act = act
         if pre_act:
             ctx.save_for_backward(x2, wb, y)
-            out = torch.relu(y) if act == "relu" else torch.nn.functional.gelu(y.float(), approximate="tanh").bfloat16()
+            out = torch.relu(y) if act == "relu" else torch.nn.functional.gelu(y, approximate="tanh")
         else:
             ctx.save_for_backward(x2, wb, None)
             out = y
@@ -93,14 +93,11 @@ class _LinearFn(torch.autograd.Function):
         if ctx.act == "relu":
             dy2 = dy2 * (pre > 0)
         elif ctx.act == "gelu":
-            p = pre.float().requires_grad_()
-            with torch.enable_grad():
-                g = torch.nn.functional.gelu(p, approximate="tanh")
-            dy2 = torch.autograd.grad(g, p, dy2.float())[0]
+            dy2 = torch.ops.aten.gelu_backward(dy2.to(pre.dtype), pre, approximate="tanh")
         dyb = dy2.bfloat16().contiguous()
         dx = gemm_tma(dyb, wb, b_mn=True)                                      # [T,out] x W[out,in] (MN-major)
         dw = gemm_tma(dyb, x2, a_mn=True, b_mn=True, out_dtype=torch.float32)  # dy^T x, both MN-major
-        db = dyb.float().sum(0) if ctx.has_bias else None
+        db = dyb.sum(0, dtype=torch.float32) if ctx.has_bias else None
         return dx.reshape(ctx.x_shape), dw.to(ctx.w_dtype), db, None
 
 
