@@ -268,7 +268,14 @@ def main() -> None:
         return
     out = run_standin(args) if args.impl == "standin" else run_ours(args)
     if out:
-        print(json.dumps(out))
+        print(json.dumps(out), flush=True)
+    try:  # leave the process group cleanly so the JSON line is the last line of output
+        import torch.distributed as dist
+
+        if dist.is_available() and dist.is_initialized():
+            dist.destroy_process_group()
+    except Exception:
+        pass
 
 
 if __name__ == "__main__":

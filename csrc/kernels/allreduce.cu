@@ -55,12 +55,31 @@ __device__ __forceinline__ bool block_barrier(const TfdlFusedArParams& p, uint32
   if (threadIdx.x == 0) ok = 1;
   __syncthreads();  // all prior global writes of this block are ordered before the release below
   if ((int)threadIdx.x < W && (int)threadIdx.x != p.rank) {
-    __threadfence_system();
-    st_release_sys(p.flags[threadIdx.x] + slot_base + p.rank, value);
+    st_release_sys(p.flags[threadIdx.x] + slot_base + p.rank, value);  // release.sys: cumulative over the bar.sync above
     if (!spin_until_ge(p.flags[p.rank] + slot_base + threadIdx.x, value, p.abort_word)) ok = 0;
   }
   __syncthreads();
   return ok != 0;
+}
+
+// Sum of element i over the W ranks' buffers. All W loads are issued before the first add, so the cost is ONE
+// NVLink round trip, not W of them (a rolled loop of volatile peer loads serialises: 7 x ~1.7 us at W = 8).
+// Summation is in rank order on every rank -> bit-identical results everywhere.
+__device__ __forceinline__ float4 gather_sum(float* const* bufs, int64_t i, int W, int rank) {
+  float4 x[TFDL_MAX_RANKS];
+#pragma unroll
+  for (int r = 0; r < TFDL_MAX_RANKS; ++r) {
+    if (r < W) {
+      const float4* src = reinterpret_cast<const float4*>(bufs[r]) + i;
+      x[r] = (r == rank) ? *src : ld_peer_f4(src);
+    }
+  }
+  float4 g = make_float4(0.f, 0.f, 0.f, 0.f);
+#pragma unroll
+  for (int r = 0; r < TFDL_MAX_RANKS; ++r) {
+    if (r < W) { g.x += x[r].x; g.y += x[r].y; g.z += x[r].z; g.w += x[r].w; }
+  }
+  return g;
 }
 
 __device__ __forceinline__ float4 sgd_update(float4 w, float4 g, float4* v, const TfdlHyper& h) {
@@ -114,13 +133,7 @@ __global__ void __launch_bounds__(512) fused_ar_oneshot_kernel(TfdlFusedArParams
   uint2* s2 = reinterpret_cast<uint2*>(p.shadow[p.rank]);
   float4* z4 = reinterpret_cast<float4*>(p.grads[par ^ 1][p.rank]);
   for (int64_t i = (int64_t)blockIdx.x * blockDim.x + threadIdx.x; i < n4; i += (int64_t)gridDim.x * blockDim.x) {
-    float4 g = make_float4(0.f, 0.f, 0.f, 0.f);
-#pragma unroll 1
-    for (int r = 0; r < W; ++r) {
-      const float4* src = reinterpret_cast<const float4*>(p.grads[par][r]) + i;
-      float4 x = (r == p.rank) ? *src : ld_peer_f4(src);
-      g.x += x.x; g.y += x.y; g.z += x.z; g.w += x.w;
-    }
+    float4 g = gather_sum(p.grads[par], i, W, p.rank);
     g.x *= h.scale; g.y *= h.scale; g.z *= h.scale; g.w *= h.scale;
     float4 w = sgd_update(w4[i], g, v4 ? v4 + i : nullptr, h);
     w4[i] = w;
@@ -154,13 +167,7 @@ __global__ void __launch_bounds__(512) fused_ar_sliced_kernel(TfdlFusedArParams 
                    : "l"(src)
                    : "memory");
     } else {
-      g = make_float4(0.f, 0.f, 0.f, 0.f);
-#pragma unroll 1
-      for (int r = 0; r < W; ++r) {
-        const float4* src = reinterpret_cast<const float4*>(p.grads[par][r]) + i;
-        float4 x = (r == p.rank) ? *src : ld_peer_f4(src);
-        g.x += x.x; g.y += x.y; g.z += x.z; g.w += x.w;
-      }
+      g = gather_sum(p.grads[par], i, W, p.rank);
     }
     g.x *= h.scale; g.y *= h.scale; g.z *= h.scale; g.w *= h.scale;
     float4 w = sgd_update(w_own[i], g, v4 ? v4 + i : nullptr, h);
@@ -220,13 +227,7 @@ __global__ void __launch_bounds__(512) allreduce_sum_kernel(TfdlFusedArParams p)
       asm volatile("multimem.st.relaxed.sys.global.v4.f32 [%0], {%1, %2, %3, %4};" ::"l"(dst), "f"(g.x), "f"(g.y),
                    "f"(g.z), "f"(g.w) : "memory");
     } else {
-      g = make_float4(0.f, 0.f, 0.f, 0.f);
-#pragma unroll 1
-      for (int r = 0; r < W; ++r) {
-        const float4* src = reinterpret_cast<const float4*>(p.grads[0][r]) + i;
-        float4 x = (r == p.rank) ? *src : ld_peer_f4(src);
-        g.x += x.x; g.y += x.y; g.z += x.z; g.w += x.w;
-      }
+      g = gather_sum(p.grads[0], i, W, p.rank);
       // slice `rank` of every arena is read by this rank alone, so it can be overwritten right away
 #pragma unroll 1
       for (int r = 0; r < W; ++r) {

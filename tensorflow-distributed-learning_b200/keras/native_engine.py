@@ -155,7 +155,8 @@ class NativeCnnEngine:
     def hyperparams_changed(self) -> None:
         opt = self.model.optimizer
         self._lr = opt.learning_rate
-        for b in getattr(self, "buckets", [self.state]):
+        # the whole-arena state is what the unbucketed program (batch sizes the fused dense block does not take) steps
+        for b in list(getattr(self, "buckets", [])) + [self.state]:
             b.set_hyper(self._lr, opt.momentum, opt.nesterov, 1.0)
 
     def weights_changed(self) -> None:

@@ -18,6 +18,10 @@ def _run(n):
     cmd = [sys.executable, "-m", "torch.distributed.run", "--nnodes=1", f"--nproc-per-node={n}", "--master-addr",
            "127.0.0.1", "--master-port", str(port), os.path.join(HERE, "mgpu_worker.py")]
     r = subprocess.run(cmd, stdout=subprocess.PIPE, stderr=subprocess.STDOUT, text=True, timeout=600)
+    out_dir = os.path.join(os.path.dirname(HERE), "gpurun_out")
+    if os.path.isdir(out_dir):  # keep the workers' output where a remote run can be read back
+        with open(os.path.join(out_dir, f"mgpu_worker_N{n}.log"), "w") as f:
+            f.write(r.stdout)
     assert r.returncode == 0, r.stdout[-6000:]
     line = [l for l in r.stdout.splitlines() if l.startswith("MGPU_REPORT ")]
     assert line, r.stdout[-3000:]

@@ -48,6 +48,23 @@ def test_native_steps_track_torch_engine(momentum):
         assert rel_l2 < 0.10 and worst < 0.30, (name, rel_l2, worst)
 
 
+@pytest.mark.parametrize("batch", [32, 256])
+def test_other_batch_sizes_track_torch_engine(batch):
+    """Batch sizes outside the fused dense block's range (B > 128) run the unbucketed program; same updates."""
+    x, y = _data(batch * 3, seed=5)
+    native, ref = _model("native", momentum=0.9), _model("torch", momentum=0.9)
+    w0 = ref.get_weights()
+    for i in range(3):
+        xb, yb = x[i * batch:(i + 1) * batch], y[i * batch:(i + 1) * batch]
+        ln, lr_ = native.train_on_batch(xb, yb, return_dict=True), ref.train_on_batch(xb, yb, return_dict=True)
+        assert abs(ln["loss"] - lr_["loss"]) < 2e-2, (i, ln, lr_)
+    assert native.engine_name == "NativeCnnEngine"
+    for name, a, b, w in zip([v.name for v in ref.weights], native.get_weights(), ref.get_weights(), w0):
+        upd_ref = (b - w).astype(np.float64)
+        rel_l2 = np.linalg.norm((a - w).astype(np.float64) - upd_ref) / (np.linalg.norm(upd_ref) + 1e-30)
+        assert np.linalg.norm(upd_ref) > 0 and rel_l2 < 0.10, (name, rel_l2)
+
+
 def test_fit_on_gpu_learns_and_uses_native_engine():
     import tfdl
     from tfdl import datasets
