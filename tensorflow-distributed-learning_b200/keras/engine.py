@@ -26,6 +26,7 @@ from ..data import Dataset
 from ..parallel import strategy as _strat
 from ..parallel.strategy import DistributedDataset, Strategy, get_strategy
 from ..parallel.values import MirroredVariable, ParamArena, PerReplica
+from ..utils.trace import nvtx_range
 from . import callbacks as _cb
 from . import losses as _losses
 from . import metrics as _metrics
@@ -527,9 +528,11 @@ class TorchEngine:
                 continue
             xt, yt = self._to_device(x, dev), self._to_device(y, dev)
             ctx = self._ctx(r, True)
-            pred = m._forward(xt, ctx)
-            per = m.loss.per_example(yt, pred)
-            (per.mean() / nrep).backward()
+            with nvtx_range("tfdl/forward"):
+                pred = m._forward(xt, ctx)
+                per = m.loss.per_example(yt, pred)
+            with nvtx_range("tfdl/backward"):
+                (per.mean() / nrep).backward()
             for fn in ctx.deferred:
                 fn()
             m.loss_tracker.add(r, per.detach().sum(), float(per.numel()))
@@ -541,11 +544,13 @@ class TorchEngine:
             if self._fused_lr != opt.learning_rate:
                 self._fused_lr = opt.learning_rate
                 self._fused.set_hyper(opt.learning_rate, opt.momentum, opt.nesterov, 1.0)
-            self._fused.step(0, self._fused.torch_algo)
+            with nvtx_range("tfdl/allreduce+sgd"):
+                self._fused.step(0, self._fused.torch_algo)
             m.optimizer.step_done()
             return
-        s.cross_device_ops.allreduce_grads([a.grads for a in m.arenas])
-        with torch.no_grad():
+        with nvtx_range("tfdl/allreduce"):
+            s.cross_device_ops.allreduce_grads([a.grads for a in m.arenas])
+        with nvtx_range("tfdl/optimizer"), torch.no_grad():
             for r, arena in enumerate(m.arenas):
                 m.optimizer.apply_flat(arena.params, arena.grads, r, None if m._all_trainable else m._masks[r])
         m.optimizer.step_done()

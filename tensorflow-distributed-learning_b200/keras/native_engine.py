@@ -21,6 +21,8 @@ from typing import Any, List, Optional, Tuple
 import numpy as np
 import torch
 
+from ..utils.trace import nvtx_range
+
 from ..ops import _lib
 from ..ops.allreduce import FusedState, P2PFusedAllReduce, SymmetricBuffer
 from ..ops.structs import AR_NAMES, CnnDims, CnnStep, FusedArParams, make_dims
@@ -254,8 +256,9 @@ class NativeCnnEngine:
             self.hyperparams_changed()
         out_ptr = host_out.data_ptr() if host_out is not None else None
         self.stream.wait_stream(torch.cuda.current_stream(self.device))
-        _lib.check(self.lib.tfdl_cnn_program_run(self._prog, records.data_ptr(), records.shape[0], n_steps, out_ptr,
-                                                 self.stream.cuda_stream), "cnn_program_run")
+        with nvtx_range(f"tfdl/native_chunk[{n_steps}]"):
+            _lib.check(self.lib.tfdl_cnn_program_run(self._prog, records.data_ptr(), records.shape[0], n_steps, out_ptr,
+                                                     self.stream.cuda_stream), "cnn_program_run")
         self.model.optimizer.iterations += n_steps
 
     def run_device(self, records: torch.Tensor, n_steps: int) -> None:

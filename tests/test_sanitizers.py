@@ -1,0 +1,29 @@
+"""ThreadSanitizer over the C++ control plane / ring all-reduce: 4 ranks as threads of one instrumented process
+(csrc/runtime_tests/tsan_driver.cc). SURVEY 5.2."""
+import os
+import shutil
+import subprocess
+
+import pytest
+
+from _mp import free_ports
+
+ROOT = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
+
+
+def test_runtime_is_clean_under_thread_sanitizer(tmp_path):
+    if shutil.which("g++") is None:
+        pytest.skip("no g++")
+    exe = str(tmp_path / "tsan_driver")
+    srcs = [os.path.join(ROOT, "csrc", "runtime", f) for f in sorted(os.listdir(os.path.join(ROOT, "csrc", "runtime")))
+            if f.endswith(".cc")] + [os.path.join(ROOT, "csrc", "runtime_tests", "tsan_driver.cc")]
+    b = subprocess.run(["g++", "-std=c++17", "-g", "-O1", "-fsanitize=thread", "-pthread", *srcs, "-o", exe],
+                       capture_output=True, text=True)
+    if b.returncode != 0 and "tsan" in (b.stderr or "").lower():
+        pytest.skip("libtsan not available")
+    assert b.returncode == 0, b.stderr[-2000:]
+    base = free_ports(1)[0]
+    env = dict(os.environ, TSAN_OPTIONS="halt_on_error=1 exitcode=66")
+    r = subprocess.run([exe, "4", str(base), "5"], capture_output=True, text=True, timeout=300, env=env)
+    assert r.returncode == 0 and "ThreadSanitizer" not in r.stderr, (r.stdout[-500:], r.stderr[-3000:])
+    assert "-> ok" in r.stdout
