@@ -223,13 +223,12 @@ static int launch_one(TfdlCnnProgram* p, cudaStream_t st) {
 
 extern "C" int tfdl_cnn_program_step(TfdlCnnProgram* p, void* stream) { return launch_one(p, (cudaStream_t)stream); }
 
-extern "C" int tfdl_cnn_program_run(TfdlCnnProgram* p, const void* host_batches, int64_t n_records, int64_t n_steps,
-                                    float* host_out, void* stream) {
-  TFDL_REQUIRE(p && host_batches && n_records > 0 && n_steps >= 0, "cnn_program_run: bad arguments");
-  cudaStream_t st = (cudaStream_t)stream;
+// Shared loop of the host-fed entry points. `src_of(i, &x_src, &y_src)` names step i's pinned host images and
+// labels; when y_src directly follows x_src and the device record is laid out the same way, one copy brings both.
+template <class SrcFn>
+static int run_host_fed(TfdlCnnProgram* p, int64_t n_steps, float* host_out, cudaStream_t st, SrcFn src_of) {
   const TfdlCnnDims& d = p->steps[0].dims;
   const size_t x_bytes = (size_t)d.B * d.H0 * d.W0 * sizeof(float), y_bytes = (size_t)d.B * sizeof(int);
-  const size_t rec = x_bytes + y_bytes;
   // both parities must be captured before the pipelined loop (capture is not allowed to interleave with
   // the event waits below)
   if (p->use_graph) {
@@ -243,12 +242,17 @@ extern "C" int tfdl_cnn_program_run(TfdlCnnProgram* p, const void* host_batches,
   TFDL_CUDA_OK(cudaEventRecord(p->ev_out[1], p->out));
   for (int64_t i = 0; i < n_steps; ++i) {
     const int par = (int)(p->steps_done & 1);
-    const char* src = static_cast<const char*>(host_batches) + (size_t)(i % n_records) * rec;
+    const char *xs = nullptr, *ys = nullptr;
+    src_of(i, &xs, &ys);
     const TfdlCnnStep& s = p->steps[par];
     // H2D of this step's batch (into the input buffers of this parity) once the step two back has consumed them
     TFDL_CUDA_OK(cudaStreamWaitEvent(p->copy, p->ev_used[par], 0));
-    TFDL_CUDA_OK(cudaMemcpyAsync(const_cast<float*>(s.x), src, x_bytes, cudaMemcpyHostToDevice, p->copy));
-    TFDL_CUDA_OK(cudaMemcpyAsync(const_cast<int*>(s.labels), src + x_bytes, y_bytes, cudaMemcpyHostToDevice, p->copy));
+    if (ys == xs + x_bytes && reinterpret_cast<const char*>(s.labels) == reinterpret_cast<const char*>(s.x) + x_bytes) {
+      TFDL_CUDA_OK(cudaMemcpyAsync(const_cast<float*>(s.x), xs, x_bytes + y_bytes, cudaMemcpyHostToDevice, p->copy));
+    } else {
+      TFDL_CUDA_OK(cudaMemcpyAsync(const_cast<float*>(s.x), xs, x_bytes, cudaMemcpyHostToDevice, p->copy));
+      TFDL_CUDA_OK(cudaMemcpyAsync(const_cast<int*>(s.labels), ys, y_bytes, cudaMemcpyHostToDevice, p->copy));
+    }
     TFDL_CUDA_OK(cudaEventRecord(p->ev_in[par], p->copy));
     TFDL_CUDA_OK(cudaStreamWaitEvent(st, p->ev_in[par], 0));
     TFDL_CUDA_OK(cudaStreamWaitEvent(st, p->ev_out[par], 0));  // step_out[par] of two steps back has been read
@@ -263,6 +267,51 @@ extern "C" int tfdl_cnn_program_run(TfdlCnnProgram* p, const void* host_batches,
   // make `st` the single stream the caller has to synchronise
   TFDL_CUDA_OK(cudaEventRecord(p->ev_out[0], p->out));
   TFDL_CUDA_OK(cudaStreamWaitEvent(st, p->ev_out[0], 0));
+  return 0;
+}
+
+extern "C" int tfdl_cnn_program_run(TfdlCnnProgram* p, const void* host_batches, int64_t n_records, int64_t n_steps,
+                                    float* host_out, void* stream) {
+  TFDL_REQUIRE(p && host_batches && n_records > 0 && n_steps >= 0, "cnn_program_run: bad arguments");
+  const TfdlCnnDims& d = p->steps[0].dims;
+  const size_t x_bytes = (size_t)d.B * d.H0 * d.W0 * sizeof(float), rec = x_bytes + (size_t)d.B * sizeof(int);
+  const char* base = static_cast<const char*>(host_batches);
+  return run_host_fed(p, n_steps, host_out, (cudaStream_t)stream, [=](int64_t i, const char** xs, const char** ys) {
+    *xs = base + (size_t)(i % n_records) * rec;
+    *ys = *xs + x_bytes;
+  });
+}
+
+// Zero-staging variant: step i reads its images from xs[i] and its int32 labels from ys[i], both in page-locked
+// host memory (cudaHostRegister'ed dataset arrays, see tfdl_host_register) - no copy into a record ring.
+extern "C" int tfdl_cnn_program_run_ptrs(TfdlCnnProgram* p, const void* const* xs, const void* const* ys,
+                                         int64_t n_steps, float* host_out, void* stream) {
+  TFDL_REQUIRE(p && xs && ys && n_steps >= 0, "cnn_program_run_ptrs: bad arguments");
+  return run_host_fed(p, n_steps, host_out, (cudaStream_t)stream, [=](int64_t i, const char** x, const char** y) {
+    *x = static_cast<const char*>(xs[i]);
+    *y = static_cast<const char*>(ys[i]);
+  });
+}
+
+// Page-lock a host range that the caller owns (a dataset array) so the executor can DMA from it directly.
+// Returns 0 also when the range is already page-locked.
+extern "C" int tfdl_host_register(void* ptr, uint64_t bytes) {
+  TFDL_REQUIRE(ptr && bytes > 0, "host_register: empty range");
+  cudaError_t e = cudaHostRegister(ptr, (size_t)bytes, cudaHostRegisterDefault);
+  if (e == cudaErrorHostMemoryAlreadyRegistered) {
+    cudaGetLastError();
+    return 0;
+  }
+  TFDL_CUDA_OK(e);
+  return 0;
+}
+extern "C" int tfdl_host_unregister(void* ptr) {
+  cudaError_t e = cudaHostUnregister(ptr);
+  if (e == cudaErrorHostMemoryNotRegistered) {
+    cudaGetLastError();
+    return 0;
+  }
+  TFDL_CUDA_OK(e);
   return 0;
 }
 
@@ -284,8 +333,12 @@ extern "C" int tfdl_cnn_program_run_device(TfdlCnnProgram* p, const void* dev_ba
     const int par = (int)(p->steps_done & 1);
     const char* src = static_cast<const char*>(dev_batches) + (size_t)(i % n_records) * rec;
     const TfdlCnnStep& s = p->steps[par];
-    TFDL_CUDA_OK(cudaMemcpyAsync(const_cast<float*>(s.x), src, x_bytes, cudaMemcpyDeviceToDevice, st));
-    TFDL_CUDA_OK(cudaMemcpyAsync(const_cast<int*>(s.labels), src + x_bytes, y_bytes, cudaMemcpyDeviceToDevice, st));
+    if (reinterpret_cast<const char*>(s.labels) == reinterpret_cast<const char*>(s.x) + x_bytes) {
+      TFDL_CUDA_OK(cudaMemcpyAsync(const_cast<float*>(s.x), src, rec, cudaMemcpyDeviceToDevice, st));
+    } else {
+      TFDL_CUDA_OK(cudaMemcpyAsync(const_cast<float*>(s.x), src, x_bytes, cudaMemcpyDeviceToDevice, st));
+      TFDL_CUDA_OK(cudaMemcpyAsync(const_cast<int*>(s.labels), src + x_bytes, y_bytes, cudaMemcpyDeviceToDevice, st));
+    }
     TFDL_RC(launch_one(p, st));
   }
   return 0;

@@ -166,3 +166,43 @@ extern "C" int tfdl_rt_gather_rows_u8_to_f32(const uint8_t* src, int64_t num_row
   });
   return 0;
 }
+
+// Packs k training batches into the executor's pinned record ring: record i = [x_i bytes | labels_i as int32].
+// xs[i] / ys[i] point at contiguous host arrays (float32 images; int32 or int64 labels). One call per chunk of
+// steps replaces 2k numpy copies on the Python side of fit() (the rebatch + staging half of SURVEY N6).
+extern "C" int tfdl_rt_pack_records(const void* const* xs, const void* const* ys, int64_t k, int64_t x_bytes,
+                                    int64_t n_labels, int label_bytes, void* ring, int64_t rec_bytes, int threads) {
+  if (!xs || !ys || !ring || k < 0 || x_bytes < 0 || n_labels < 0 || (label_bytes != 4 && label_bytes != 8) ||
+      rec_bytes < x_bytes + n_labels * 4) {
+    set_error("pack_records: bad arguments (k=%lld x_bytes=%lld labels=%lld x %d rec=%lld)", (long long)k,
+              (long long)x_bytes, (long long)n_labels, label_bytes, (long long)rec_bytes);
+    return -1;
+  }
+  auto work = [=](int64_t lo, int64_t hi) {
+    for (int64_t i = lo; i < hi; ++i) {
+      char* rec = static_cast<char*>(ring) + i * rec_bytes;
+      std::memcpy(rec, xs[i], (size_t)x_bytes);
+      int32_t* yl = reinterpret_cast<int32_t*>(rec + x_bytes);
+      if (label_bytes == 4) {
+        std::memcpy(yl, ys[i], (size_t)n_labels * 4);
+      } else {
+        const int64_t* y8 = static_cast<const int64_t*>(ys[i]);
+        for (int64_t j = 0; j < n_labels; ++j) yl[j] = (int32_t)y8[j];
+      }
+    }
+  };
+  // records are large (hundreds of KB): split across threads as soon as there is ~1 MB to move
+  const int64_t nt = std::min<int64_t>(std::min<int64_t>(threads, k), (k * x_bytes) >> 19);
+  if (nt <= 1) {
+    work(0, k);
+  } else {
+    std::vector<std::thread> ts;
+    const int64_t per = (k + nt - 1) / nt;
+    for (int64_t t = 0; t < nt; ++t) {
+      const int64_t lo = t * per, hi = std::min(k, lo + per);
+      if (lo < hi) ts.emplace_back([=] { work(lo, hi); });
+    }
+    for (auto& t : ts) t.join();
+  }
+  return 0;
+}

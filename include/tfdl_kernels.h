@@ -236,7 +236,13 @@ int tfdl_cnn_program_step(TfdlCnnProgram* p, void* stream);
  * last step has been enqueued; the caller synchronises `stream`. */
 int tfdl_cnn_program_run(TfdlCnnProgram* p, const void* host_batches, int64_t n_records, int64_t n_steps,
                          float* host_out, void* stream);
-/* As above with the records already on the device (two D2D copies + one graph launch per step). */
+/* as tfdl_cnn_program_run, but step i takes its images from xs[i] and its int32 labels from ys[i] (page-locked
+ * host memory, e.g. dataset arrays passed through tfdl_host_register): no staging copy on the host */
+int tfdl_cnn_program_run_ptrs(TfdlCnnProgram* prog, const void* const* xs, const void* const* ys, int64_t n_steps,
+                              float* host_out, void* stream);
+int tfdl_host_register(void* ptr, uint64_t bytes);   /* cudaHostRegister; ok if already page-locked */
+int tfdl_host_unregister(void* ptr);
+/* As tfdl_cnn_program_run with the records already on the device (one D2D copy + one graph launch per step). */
 int tfdl_cnn_program_run_device(TfdlCnnProgram* p, const void* dev_batches, int64_t n_records, int64_t n_steps,
                                 void* stream);
 int64_t tfdl_cnn_program_steps_done(const TfdlCnnProgram* p);

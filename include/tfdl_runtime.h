@@ -25,6 +25,10 @@ int tfdl_rt_gather_rows(const void* src, int64_t num_rows, int64_t row_bytes, co
 int tfdl_rt_gather_rows_u8_to_f32(const uint8_t* src, int64_t num_rows, int64_t row_elems, const int64_t* idx,
                                   int64_t n, float scale, float* dst, int threads);
 
+/* k records [x_i | int32 labels_i] into a (pinned) ring; labels given as int32 (label_bytes 4) or int64 (8) */
+int tfdl_rt_pack_records(const void* const* xs, const void* const* ys, int64_t k, int64_t x_bytes, int64_t n_labels,
+                         int label_bytes, void* ring, int64_t rec_bytes, int threads);
+
 /* ---- TCP control plane + RING collective (ref: README.md:21-23,65-68) -------------------- */
 /* Binds the port of addrs[rank], connects ring/control/heartbeat channels, returns once every
  * peer has joined (or NULL after timeout_ms). addrs = training tasks in rank order. */

@@ -289,7 +289,9 @@ class Model:
             while steps_per_epoch is None or step < steps_per_epoch:
                 want = 1
                 if chunked:
-                    want = engine.CHUNK if steps_per_epoch is None else min(engine.CHUNK, steps_per_epoch - step)
+                    # chunk sizes ramp 8, 16, 32, ... so the device starts after 8 batches are staged, not after CHUNK
+                    ramp = min(engine.CHUNK, 8 << min(step // 8, 16).bit_length()) if step < engine.CHUNK else engine.CHUNK
+                    want = ramp if steps_per_epoch is None else min(ramp, steps_per_epoch - step)
                 group, exhausted = [], False
                 for _ in range(want):
                     try:

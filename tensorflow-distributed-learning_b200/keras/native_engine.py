@@ -24,6 +24,7 @@ import torch
 from ..utils.trace import nvtx_range
 
 from ..ops import _lib
+from ..runtime import native as _rt
 from ..ops.allreduce import FusedState, P2PFusedAllReduce, SymmetricBuffer
 from ..ops.structs import AR_NAMES, CnnDims, CnnStep, FusedArParams, make_dims
 from ..parallel.values import PerReplica
@@ -103,6 +104,8 @@ class NativeCnnEngine:
         self._B: Optional[int] = None
         self._torch_engine: Any = None
         self._keep: List[Any] = []
+        self._pinned: dict = {}            # host ranges page-locked for the zero-staging input path
+        self._ptr_keep: List[Any] = [None, None]
         torch.cuda.set_device(self.device)
         # graphs cannot be captured on the legacy default stream: the engine owns its stream
         self.stream = torch.cuda.Stream(self.device)
@@ -182,8 +185,11 @@ class NativeCnnEngine:
                     idx2=z(B, d.F, dt=torch.uint8))
         accs = [z(B, D1, dt=torch.float32) for _ in range(2)]  # split-K accumulator, one per step parity
         sync = z(4, dt=torch.int32)
-        self.x_dev = [z(B, H0, W0, dt=torch.float32) for _ in range(2)]
-        self.y_dev = [z(B, dt=torch.int32) for _ in range(2)]
+        # one device record [x | labels] per parity, so a step's inputs arrive with ONE host-to-device copy
+        nx = B * H0 * W0 * 4
+        self.in_dev = [z(nx + B * 4, dt=torch.uint8) for _ in range(2)]
+        self.x_dev = [t[:nx].view(torch.float32).view(B, H0, W0) for t in self.in_dev]
+        self.y_dev = [t[nx:].view(torch.int32) for t in self.in_dev]
         self.step_out = [z(2, dt=torch.float32) for _ in range(2)]
         offs = self._offsets()
         steps = (CnnStep * 2)()
@@ -249,6 +255,68 @@ class NativeCnnEngine:
         rec[:nx].view(np.float32)[:] = np.asarray(x, dtype=np.float32).reshape(-1)
         rec[nx:].view(np.int32)[:] = np.asarray(y).reshape(-1).astype(np.int32, copy=False)
 
+    # ---- zero-staging input path ------------------------------------------------------------------------
+    # Batches that are contiguous views of one long-lived dataset array (from_tensor_slices(...).batch(), no
+    # shuffle) are DMA'd straight from that array: it is page-locked once with cudaHostRegister and the executor
+    # gets one pointer per step. Anything else (shuffled gathers, mapped batches, odd dtypes) is staged in the ring.
+    ZC_MAX_BYTES = int(os.environ.get("TFDL_PIN_MAX_MB", "4096")) << 20
+
+    def _owner(self, a: np.ndarray) -> Optional[np.ndarray]:
+        b = a
+        while isinstance(b.base, np.ndarray):
+            b = b.base
+        return b if b.base is None or not isinstance(b.base, np.ndarray) else None
+
+    def _pinned_range(self, a: np.ndarray) -> bool:
+        """True when `a` lies inside a host range this engine has page-locked (registering its owner on first use)."""
+        if not a.flags.c_contiguous:
+            return False
+        own = self._owner(a)
+        if own is None or own.nbytes < 8 * a.nbytes or not own.flags.c_contiguous:
+            return False  # a per-batch temporary: registering it would cost more than copying it
+        key = own.ctypes.data
+        ent = self._pinned.get(key)
+        if ent is None:
+            if own.nbytes > self.ZC_MAX_BYTES or os.environ.get("TFDL_ZERO_COPY", "1") != "1":
+                return False
+            self.lib.tfdl_host_register.argtypes = [C.c_void_p, C.c_uint64]
+            if self.lib.tfdl_host_register(C.c_void_p(key), C.c_uint64(own.nbytes)) != 0:
+                self._pinned[key] = (None, 0)  # not registrable (e.g. read-only mapping): remember, use the ring
+                return False
+            ent = self._pinned[key] = (own, own.nbytes)  # the reference keeps the memory alive while registered
+        return ent[0] is not None and key <= a.ctypes.data and a.ctypes.data + a.nbytes <= key + ent[1]
+
+    def _zero_copy_ok(self, xs: List[np.ndarray], ys: List[np.ndarray]) -> bool:
+        if not xs or xs[0].dtype != np.float32 or ys[0].dtype != np.int32:
+            return False
+        return all(self._pinned_range(a) for a in xs) and all(self._pinned_range(a) for a in ys)
+
+    def _run_ptrs(self, xs: List[np.ndarray], ys: List[np.ndarray], r: int) -> None:
+        k = len(xs)
+        px = (C.c_void_p * k)(*[a.ctypes.data for a in xs])
+        py = (C.c_void_p * k)(*[a.ctypes.data for a in ys])
+        if self.model.optimizer.learning_rate != self._lr:
+            self.hyperparams_changed()
+        self.stream.wait_stream(torch.cuda.current_stream(self.device))
+        self.lib.tfdl_cnn_program_run_ptrs.argtypes = [C.c_void_p, C.c_void_p, C.c_void_p, C.c_int64, C.c_void_p,
+                                                       C.c_void_p]
+        with nvtx_range(f"tfdl/native_chunk[{k}]"):
+            _lib.check(self.lib.tfdl_cnn_program_run_ptrs(self._prog, px, py, k, self.host_out.data_ptr(),
+                                                          self.stream.cuda_stream), "cnn_program_run_ptrs")
+        self._ptr_keep[r] = (px, py, xs, ys)  # the executor returns before the copies ran: keep the views alive
+        self.model.optimizer.iterations += k
+
+    def _pack(self, xs: List[np.ndarray], ys: List[np.ndarray]) -> None:
+        """Stage a chunk of batches in the pinned ring: one multi-threaded C++ call when the arrays are plain
+        float32 / int labels (the normal case), per-record numpy copies otherwise."""
+        fast = all(a.dtype == np.float32 and a.flags.c_contiguous for a in xs) and \
+            all(a.dtype == ys[0].dtype and a.flags.c_contiguous for a in ys) and ys[0].dtype in (np.int32, np.int64)
+        if fast and xs:
+            _rt.pack_records(xs, ys, self.ring.data_ptr(), self.rec_bytes)
+        else:
+            for k, (xb, yb) in enumerate(zip(xs, ys)):
+                self.pack_record(k, xb, yb)
+
     def run_pinned(self, records: torch.Tensor, n_steps: int, host_out: Optional[torch.Tensor] = None) -> None:
         """Drive n_steps steps from a pinned [n_records, rec_bytes] uint8 tensor (asynchronous)."""
         assert records.is_pinned() and records.shape[1] == self.rec_bytes
@@ -299,13 +367,19 @@ class NativeCnnEngine:
             self.ring, self.host_out = self.rings[r], self.host_outs[r]
             self.ring_done[r].synchronize()  # the run that last read this ring has finished (no-op if never used)
             k = 0
+            xs, ys = [], []
             while i + k < len(batches) and k < self.ring.shape[0]:
                 xb, yb = self._split(batches[i + k][0])
                 if xb.shape[0] != B:
                     break
-                self.pack_record(k, xb, yb)
+                xs.append(xb)
+                ys.append(yb)
                 k += 1
-            self.run_pinned(self.ring, k, self.host_out)
+            if self._zero_copy_ok(xs, ys):
+                self._run_ptrs(xs, ys, r)
+            else:
+                self._pack(xs, ys)
+                self.run_pinned(self.ring, k, self.host_out)
             self.ring_done[r].record(self.stream)
             self._last_k = k
             i += k
@@ -356,6 +430,10 @@ class NativeCnnEngine:
     def __del__(self) -> None:  # pragma: no cover
         try:
             if self._prog is not None:
+                torch.cuda.synchronize(self.device)
                 self.lib.tfdl_cnn_program_destroy(self._prog)
+            for key, (own, _) in list(self._pinned.items()):
+                if own is not None:
+                    self.lib.tfdl_host_unregister(C.c_void_p(key))
         except Exception:
             pass

@@ -27,6 +27,7 @@ def lib() -> C.CDLL:
         L.tfdl_rt_crc32c_mask.argtypes = [C.c_uint32]
         L.tfdl_rt_shuffle_indices.argtypes = [vp, C.c_int64, C.c_int64, C.c_uint64, vp]
         L.tfdl_rt_gather_rows.argtypes = [vp, C.c_int64, C.c_int64, vp, C.c_int64, vp, C.c_int]
+        L.tfdl_rt_pack_records.argtypes = [vp, vp, C.c_int64, C.c_int64, C.c_int64, C.c_int, vp, C.c_int64, C.c_int]
         L.tfdl_rt_gather_rows_u8_to_f32.argtypes = [vp, C.c_int64, C.c_int64, vp, C.c_int64, C.c_float, vp, C.c_int]
         L.tfdl_rt_group_create.restype = vp
         L.tfdl_rt_group_create.argtypes = [C.c_int, C.c_int, C.POINTER(C.c_char_p), C.c_int, C.c_int, C.c_int]
@@ -102,6 +103,16 @@ def gather_rows(src: np.ndarray, idx: np.ndarray, out: Optional[np.ndarray] = No
     _lib.check_rt(lib().tfdl_rt_gather_rows(_np_ptr(src), src.shape[0], row, _np_ptr(idx), idx.size, _np_ptr(out),
                                            threads), "gather_rows")
     return out
+
+
+def pack_records(xs: list, ys: list, ring_ptr: int, rec_bytes: int, threads: int = 4) -> None:
+    """Copy k (x, labels) batches into the record ring at ``ring_ptr`` ([x bytes | int32 labels] per record).
+    Every x must be C-contiguous float32 of one size, every y C-contiguous int32 or int64 of one size."""
+    k = len(xs)
+    px = (C.c_void_p * k)(*[a.ctypes.data for a in xs])
+    py = (C.c_void_p * k)(*[a.ctypes.data for a in ys])
+    _lib.check_rt(lib().tfdl_rt_pack_records(px, py, k, xs[0].nbytes, ys[0].size, ys[0].dtype.itemsize, ring_ptr,
+                                             rec_bytes, threads), "pack_records")
 
 
 def gather_rows_u8_to_f32(src: np.ndarray, idx: np.ndarray, scale: float, out_ptr: int, threads: int = 4) -> None:

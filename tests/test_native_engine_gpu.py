@@ -107,3 +107,25 @@ def test_ragged_batch_falls_back_and_resyncs():
     assert np.isfinite(logs["loss"])
     eng = m._engine
     torch.testing.assert_close(eng.state.shadow.tensor.float(), eng.state.params.tensor.bfloat16().float())
+
+
+def test_zero_staging_inputs_match_ring_path(monkeypatch):
+    """Unshuffled from_tensor_slices batches are DMA'd from the page-locked dataset array itself; same training."""
+    import tfdl
+
+    x, y = _data(64 * 12, seed=9)
+    y = y.astype(np.int32)
+    results = []
+    for zc in ("1", "0"):
+        monkeypatch.setenv("TFDL_ZERO_COPY", zc)
+        m = _model("native", lr=0.05)
+        ds = tfdl.data.Dataset.from_tensor_slices((x, y)).batch(64)
+        h = m.fit(ds, epochs=2, verbose=0)
+        used = any(own is not None for own, _ in m._engine._pinned.values())
+        assert used == (zc == "1")
+        results.append((h.history["loss"], m.get_weights()))
+        del m
+    # same data, same kernels; split-K / RED accumulation order differs run to run, so not bit-identical
+    np.testing.assert_allclose(results[0][0], results[1][0], rtol=2e-3)
+    for a, b in zip(results[0][1], results[1][1]):
+        np.testing.assert_allclose(a, b, rtol=0, atol=5e-3)

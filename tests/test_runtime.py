@@ -130,3 +130,20 @@ def test_killed_worker_is_reported_not_hung():
         assert "rank" in msg and msg != "no error", msg
         assert dt < 15
         assert failed in (1,), (r, failed, msg)
+
+
+@pytest.mark.parametrize("ydt", [np.int32, np.int64])
+def test_pack_records_matches_numpy(ydt):
+    from tfdl.runtime import native as rt
+
+    rng = np.random.default_rng(0)
+    k, B = 5, 16
+    xs = [rng.random((B, 28, 28, 1), dtype=np.float32) for _ in range(k)]
+    ys = [rng.integers(0, 10, size=B).astype(ydt) for _ in range(k)]
+    rec = B * 784 * 4 + B * 4
+    ring = np.zeros((k + 1, rec), dtype=np.uint8)
+    rt.pack_records(xs, ys, ring.ctypes.data, rec, threads=3)
+    for i in range(k):
+        np.testing.assert_array_equal(ring[i, :B * 784 * 4].view(np.float32), xs[i].reshape(-1))
+        np.testing.assert_array_equal(ring[i, B * 784 * 4:].view(np.int32), ys[i].astype(np.int32))
+    assert not ring[k].any()
