@@ -20,6 +20,7 @@
 //               direct store is kept for outputs whose pitch is not a multiple of 16 bytes.) Two TMEM
 //               accumulator stages let the epilogue of tile i overlap the MMAs of tile i+1.
 #include <cuda.h>
+#include <stdlib.h>
 #include "common.cuh"
 #include "../../include/tfdl_kernels.h"
 
@@ -92,6 +93,104 @@ __device__ __forceinline__ void epi_apply(uint32_t (&v)[32], const float* bias, 
   }
 }
 
+// Epilogue of one accumulator tile for one warp: 32 rows (TMEM lanes of this warp) x BN_T columns starting at
+// global element (row0, n0). Shared by the 1-CTA and the CTA-pair kernels.
+template <int BN_T>
+__device__ __forceinline__ void epilogue_tile(const TmaGemmParams& p, const CUtensorMap& tmD, uint32_t t_row,
+                                              uint32_t stg_base, uint32_t& sb, int row0, int n0) {
+  constexpr int BN = BN_T;
+  const int row = row0 + (int)lane_id();
+  if (p.tma_store) {
+    const int CH = p.Dh ? 64 : 32;  // output columns per 128-byte staged row
+    const uint32_t lane = lane_id();
+#pragma unroll 1
+    for (int c = 0; c < BN && row0 < p.M; c += CH) {
+      const int col0 = n0 + c;
+      if (col0 >= p.N) break;
+      uint32_t v[32], v2[32];
+      tmem_ld32(t_row + c, v);
+      if (p.Dh) tmem_ld32(t_row + c + 32, v2);
+      tmem_ld_wait();
+      epi_apply(v, p.bias, col0, p.N, p.act);
+      if (p.Dh) epi_apply(v2, p.bias, col0 + 32, p.N, p.act);
+      // the bulk store that last read this staging buffer (two chunks ago) must have drained it
+      if (lane == 0) asm volatile("cp.async.bulk.wait_group.read 1;" ::: "memory");
+      __syncwarp();
+      const uint32_t sbuf = stg_base + sb * EPI_STAGE_BYTES;
+      const uint32_t srow = sbuf + lane * 128;
+      if (p.Dh) {
+#pragma unroll
+        for (int j = 0; j < 4; ++j) {
+          st_shared_v4(srow + ((uint32_t)(j ^ (lane & 7)) << 4), pack2(v[j * 8], v[j * 8 + 1]),
+                       pack2(v[j * 8 + 2], v[j * 8 + 3]), pack2(v[j * 8 + 4], v[j * 8 + 5]),
+                       pack2(v[j * 8 + 6], v[j * 8 + 7]));
+          st_shared_v4(srow + ((uint32_t)((j + 4) ^ (lane & 7)) << 4), pack2(v2[j * 8], v2[j * 8 + 1]),
+                       pack2(v2[j * 8 + 2], v2[j * 8 + 3]), pack2(v2[j * 8 + 4], v2[j * 8 + 5]),
+                       pack2(v2[j * 8 + 6], v2[j * 8 + 7]));
+        }
+      } else {
+#pragma unroll
+        for (int j = 0; j < 8; ++j)
+          st_shared_v4(srow + ((uint32_t)(j ^ (lane & 7)) << 4), v[j * 4], v[j * 4 + 1], v[j * 4 + 2], v[j * 4 + 3]);
+      }
+      fence_proxy_async_smem();
+      __syncwarp();
+      if (lane == 0) {
+        tma_store_2d(&tmD, sbuf, col0, row0);
+        tma_store_commit();
+      }
+      sb ^= 1;
+    }
+  } else {
+#pragma unroll 1
+    for (int c = 0; c < BN; c += 32) {
+      uint32_t v[32];
+      tmem_ld32(t_row + c, v);
+      tmem_ld_wait();
+      const int col0 = n0 + c;
+      if (row < p.M && col0 < p.N) {
+        epi_apply(v, p.bias, col0, p.N, p.act);
+        const bool full = (col0 + 32 <= p.N);
+        if (p.Dh) {
+          __nv_bfloat16* dst = p.Dh + (size_t)row * p.ldd + col0;
+          if (full && ((reinterpret_cast<uintptr_t>(dst) & 15) == 0)) {
+#pragma unroll
+            for (int i = 0; i < 32; i += 8)
+              *reinterpret_cast<uint4*>(dst + i) = make_uint4(pack2(v[i], v[i + 1]), pack2(v[i + 2], v[i + 3]),
+                                                              pack2(v[i + 4], v[i + 5]), pack2(v[i + 6], v[i + 7]));
+          } else {
+#pragma unroll
+            for (int i = 0; i < 32; ++i)
+              if (col0 + i < p.N) dst[i] = __float2bfloat16(__uint_as_float(v[i]));
+          }
+        }
+        if (p.Df) {
+          float* dst = p.Df + (size_t)row * p.ldd + col0;
+          if (full && ((reinterpret_cast<uintptr_t>(dst) & 15) == 0)) {
+#pragma unroll
+            for (int i = 0; i < 32; i += 4) *reinterpret_cast<uint4*>(dst + i) = make_uint4(v[i], v[i + 1], v[i + 2], v[i + 3]);
+          } else {
+#pragma unroll
+            for (int i = 0; i < 32; ++i)
+              if (col0 + i < p.N) dst[i] = __uint_as_float(v[i]);
+          }
+        }
+      }
+    }
+  }
+}
+
+// Tile order: GROUP_M row-tiles are swept before moving to the next column-tile, so one wave of CTAs works on a
+// roughly square patch of the output and re-reads far fewer operand bytes from HBM than a column sweep would.
+__device__ __forceinline__ void tile_coords(int t, int m_tiles, int n_tiles, int group_m, int& mt, int& nt) {
+  const int group = group_m * n_tiles;
+  const int g = t / group, r = t - g * group;
+  const int first = g * group_m;
+  const int gm = min(group_m, m_tiles - first);
+  mt = first + r % gm;
+  nt = r / gm;
+}
+
 template <int BN, int STAGES>
 __global__ void __launch_bounds__(192, 1)
 tma_gemm_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ CUtensorMap tmB,
@@ -140,7 +239,8 @@ tma_gemm_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__
     if (elect_one()) {
       uint32_t stage = 0, phase = 0;
       for (int t = blockIdx.x; t < num_tiles; t += gridDim.x) {
-        const int mt = t % p.m_tiles, nt = t / p.m_tiles;
+        int mt, nt;
+        tile_coords(t, p.m_tiles, p.n_tiles, 16, mt, nt);
         for (int kb = 0; kb < k_blocks; ++kb) {
           mbar_wait(&empty_bar[stage], phase ^ 1);
           mbar_expect_tx(&full_bar[stage], STAGE_BYTES);
@@ -199,90 +299,11 @@ tma_gemm_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__
     uint32_t as = 0, aphase = 0, sb = 0;
     const uint32_t stg_base = smem_base + STAGES * STAGE_BYTES + q * 2 * EPI_STAGE_BYTES;
     for (int t = blockIdx.x; t < num_tiles; t += gridDim.x) {
-      const int mt = t % p.m_tiles, nt = t / p.m_tiles;
+      int mt, nt;
+      tile_coords(t, p.m_tiles, p.n_tiles, 16, mt, nt);
       mbar_wait(&acc_full[as], aphase);
       tc_fence_after_sync();
-      const int row = mt * BM + q * 32 + (int)lane_id();
-      const uint32_t t_row = tmem_base + as * BN + ((uint32_t)(q * 32) << 16);
-      if (p.tma_store) {
-        const int row0 = mt * BM + q * 32;
-        const int CH = p.Dh ? 64 : 32;  // output columns per 128-byte staged row
-        const uint32_t lane = lane_id();
-#pragma unroll 1
-        for (int c = 0; c < BN && row0 < p.M; c += CH) {
-          const int col0 = nt * BN + c;
-          if (col0 >= p.N) break;
-          uint32_t v[32], v2[32];
-          tmem_ld32(t_row + c, v);
-          if (p.Dh) tmem_ld32(t_row + c + 32, v2);
-          tmem_ld_wait();
-          epi_apply(v, p.bias, col0, p.N, p.act);
-          if (p.Dh) epi_apply(v2, p.bias, col0 + 32, p.N, p.act);
-          // the bulk store that last read this staging buffer (two chunks ago) must have drained it
-          if (lane == 0) asm volatile("cp.async.bulk.wait_group.read 1;" ::: "memory");
-          __syncwarp();
-          const uint32_t sbuf = stg_base + sb * EPI_STAGE_BYTES;
-          const uint32_t srow = sbuf + lane * 128;
-          if (p.Dh) {
-#pragma unroll
-            for (int j = 0; j < 4; ++j) {
-              st_shared_v4(srow + ((uint32_t)(j ^ (lane & 7)) << 4), pack2(v[j * 8], v[j * 8 + 1]),
-                           pack2(v[j * 8 + 2], v[j * 8 + 3]), pack2(v[j * 8 + 4], v[j * 8 + 5]),
-                           pack2(v[j * 8 + 6], v[j * 8 + 7]));
-              st_shared_v4(srow + ((uint32_t)((j + 4) ^ (lane & 7)) << 4), pack2(v2[j * 8], v2[j * 8 + 1]),
-                           pack2(v2[j * 8 + 2], v2[j * 8 + 3]), pack2(v2[j * 8 + 4], v2[j * 8 + 5]),
-                           pack2(v2[j * 8 + 6], v2[j * 8 + 7]));
-            }
-          } else {
-#pragma unroll
-            for (int j = 0; j < 8; ++j)
-              st_shared_v4(srow + ((uint32_t)(j ^ (lane & 7)) << 4), v[j * 4], v[j * 4 + 1], v[j * 4 + 2], v[j * 4 + 3]);
-          }
-          fence_proxy_async_smem();
-          __syncwarp();
-          if (lane == 0) {
-            tma_store_2d(&tmD, sbuf, col0, row0);
-            tma_store_commit();
-          }
-          sb ^= 1;
-        }
-      } else {
-#pragma unroll 1
-        for (int c = 0; c < BN; c += 32) {
-          uint32_t v[32];
-          tmem_ld32(t_row + c, v);
-          tmem_ld_wait();
-          const int col0 = nt * BN + c;
-          if (row < p.M && col0 < p.N) {
-            epi_apply(v, p.bias, col0, p.N, p.act);
-            const bool full = (col0 + 32 <= p.N);
-            if (p.Dh) {
-              __nv_bfloat16* dst = p.Dh + (size_t)row * p.ldd + col0;
-              if (full && ((reinterpret_cast<uintptr_t>(dst) & 15) == 0)) {
-#pragma unroll
-                for (int i = 0; i < 32; i += 8)
-                  *reinterpret_cast<uint4*>(dst + i) = make_uint4(pack2(v[i], v[i + 1]), pack2(v[i + 2], v[i + 3]),
-                                                                  pack2(v[i + 4], v[i + 5]), pack2(v[i + 6], v[i + 7]));
-              } else {
-#pragma unroll
-                for (int i = 0; i < 32; ++i)
-                  if (col0 + i < p.N) dst[i] = __float2bfloat16(__uint_as_float(v[i]));
-              }
-            }
-            if (p.Df) {
-              float* dst = p.Df + (size_t)row * p.ldd + col0;
-              if (full && ((reinterpret_cast<uintptr_t>(dst) & 15) == 0)) {
-#pragma unroll
-                for (int i = 0; i < 32; i += 4) *reinterpret_cast<uint4*>(dst + i) = make_uint4(v[i], v[i + 1], v[i + 2], v[i + 3]);
-              } else {
-#pragma unroll
-                for (int i = 0; i < 32; ++i)
-                  if (col0 + i < p.N) dst[i] = __uint_as_float(v[i]);
-              }
-            }
-          }
-        }
-      }
+      epilogue_tile<BN>(p, tmD, tmem_base + as * BN + ((uint32_t)(q * 32) << 16), stg_base, sb, mt * BM + q * 32, nt * BN);
       tc_fence_before_sync();
       __syncwarp();
       if (lane_id() == 0) mbar_arrive(&acc_empty[as]);
@@ -293,6 +314,146 @@ tma_gemm_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__
   tc_fence_before_sync();
   __syncthreads();
   if (warp == 0) tmem_dealloc(tmem_base, TMEM_COLS);
+}
+
+// ---------------------------------------------------------------------------------------
+// CTA-pair kernel (cta_group::2): a cluster of two CTAs on the two SMs of a TPC computes one 256 x 256 tile.
+// Each CTA stages its own 128 rows of A and its own 128 rows of B (halving the shared-memory operand traffic
+// per SM, which is what bounds the 1-CTA kernel), the leader CTA's elected thread issues
+// tcgen05.mma.cta_group::2 (M = 256, N = 256), each CTA keeps its 128 accumulator rows in its own TMEM and runs
+// its own epilogue. Barriers: `full` lives in the leader (both CTAs' TMA loads complete bytes on it), `empty`
+// and `acc_full` exist in both CTAs and are signalled by multicast tcgen05.commit, the leader's `acc_empty`
+// collects the eight epilogue warps of the pair.
+// ---------------------------------------------------------------------------------------
+template <int PAIR_BN, int STAGES>
+__global__ void __launch_bounds__(192, 1)
+tma_gemm_pair_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ CUtensorMap tmB,
+                     const __grid_constant__ CUtensorMap tmD, TmaGemmParams p) {
+  extern __shared__ __align__(1024) uint8_t smem_raw[];
+  uint8_t* smem = reinterpret_cast<uint8_t*>((reinterpret_cast<uintptr_t>(smem_raw) + 1023) & ~uintptr_t(1023));
+  constexpr int PAIR_HALF = PAIR_BN / 2;  // B rows staged per CTA
+  constexpr uint32_t A_BYTES = BM * BK * 2;
+  constexpr uint32_t B_BYTES = PAIR_HALF * BK * 2;
+  constexpr uint32_t STAGE_BYTES = A_BYTES + B_BYTES;
+  __shared__ uint64_t full_bar[STAGES], empty_bar[STAGES], acc_full[2], acc_empty[2];
+  __shared__ uint32_t tmem_slot;
+
+  const int warp = threadIdx.x >> 5;
+  const uint32_t rank = cluster_ctarank();
+  const bool leader = rank == 0;
+  const int pair = blockIdx.x >> 1, num_pairs = gridDim.x >> 1;
+  const int num_tiles = p.m_tiles * p.n_tiles;  // 256 x 256 tiles
+  const int k_blocks = (p.K + BK - 1) / BK;
+  constexpr uint32_t TMEM_COLS = 2 * PAIR_BN;
+
+  if (warp == 0) {
+    if (elect_one()) {
+      tma_prefetch_desc(&tmA);
+      tma_prefetch_desc(&tmB);
+      if (p.tma_store) tma_prefetch_desc(&tmD);
+    }
+    tmem_alloc_pair(&tmem_slot, TMEM_COLS);
+  }
+  if (threadIdx.x == 32) {
+    for (int i = 0; i < STAGES; ++i) {
+      mbar_init(&full_bar[i], 1);
+      mbar_init(&empty_bar[i], 1);
+    }
+    for (int i = 0; i < 2; ++i) {
+      mbar_init(&acc_full[i], 1);
+      mbar_init(&acc_empty[i], 8);  // four epilogue warps of each CTA of the pair (used in the leader only)
+    }
+    fence_mbar_init();
+  }
+  tc_fence_before_sync();
+  __syncthreads();
+  cluster_sync_all();  // the peer's barriers are initialised before anything can arrive on them
+  tc_fence_after_sync();
+  const uint32_t tmem_base = tmem_slot;
+  const uint32_t smem_base = smem_u32(smem);
+
+  if (warp == 0) {
+    // ------------------------------ TMA producer (both CTAs) ------------------------------
+    if (elect_one()) {
+      uint32_t stage = 0, phase = 0;
+      for (int t = pair; t < num_tiles; t += num_pairs) {
+        int mt, nt;
+        tile_coords(t, p.m_tiles, p.n_tiles, 8, mt, nt);
+        const int m0 = mt * 256 + (int)rank * BM, n0 = nt * PAIR_BN + (int)rank * PAIR_HALF;
+        for (int kb = 0; kb < k_blocks; ++kb) {
+          mbar_wait(&empty_bar[stage], phase ^ 1);  // own smem slot free (multicast commit from the leader)
+          const uint32_t full_leader = mapa_shared(smem_u32(&full_bar[stage]), 0);
+          if (leader) mbar_expect_tx(&full_bar[stage], 2 * STAGE_BYTES);
+          const uint32_t sa = smem_base + stage * STAGE_BYTES;
+          if (!p.a_mn) {
+            tma_load_2d_pair(sa, &tmA, kb * BK, m0, full_leader);
+          } else {
+#pragma unroll
+            for (int b = 0; b < BM / 64; ++b) tma_load_2d_pair(sa + b * 8192, &tmA, m0 + b * 64, kb * BK, full_leader);
+          }
+          if (!p.b_mn) {
+            tma_load_2d_pair(sa + A_BYTES, &tmB, kb * BK, n0, full_leader);
+          } else {
+#pragma unroll
+            for (int b = 0; b < PAIR_HALF / 64; ++b)
+              tma_load_2d_pair(sa + A_BYTES + b * 8192, &tmB, n0 + b * 64, kb * BK, full_leader);
+          }
+          if (++stage == STAGES) { stage = 0; phase ^= 1; }
+        }
+      }
+    }
+  } else if (warp == 1) {
+    // ------------------------------ MMA issuer (leader CTA only) --------------------------
+    if (leader && elect_one()) {
+      const uint32_t idesc = umma_idesc_bf16(256, PAIR_BN, p.a_mn != 0, p.b_mn != 0);
+      uint32_t stage = 0, phase = 0, as = 0, aphase = 0;
+      for (int t = pair; t < num_tiles; t += num_pairs) {
+        mbar_wait(&acc_empty[as], aphase ^ 1);
+        tc_fence_after_sync();
+        const uint32_t d_tmem = tmem_base + as * PAIR_BN;
+        for (int kb = 0; kb < k_blocks; ++kb) {
+          mbar_wait(&full_bar[stage], phase);
+          tc_fence_after_sync();
+          const uint32_t sa = smem_base + stage * STAGE_BYTES;
+          const uint32_t sb = sa + A_BYTES;
+#pragma unroll
+          for (int k = 0; k < BK / 16; ++k) {
+            uint64_t ad = p.a_mn ? umma_smem_desc(sa + k * 2048, 8192, 1024, SWZ_128B)
+                                 : umma_smem_desc(sa + k * 32, 16, 1024, SWZ_128B);
+            uint64_t bd = p.b_mn ? umma_smem_desc(sb + k * 2048, 8192, 1024, SWZ_128B)
+                                 : umma_smem_desc(sb + k * 32, 16, 1024, SWZ_128B);
+            umma_bf16_pair(d_tmem, ad, bd, idesc, (kb | k) != 0);
+          }
+          umma_commit_pair(&empty_bar[stage]);
+          if (++stage == STAGES) { stage = 0; phase ^= 1; }
+        }
+        umma_commit_pair(&acc_full[as]);
+        if (++as == 2) { as = 0; aphase ^= 1; }
+      }
+    }
+  } else {
+    // ------------------------------ epilogue (both CTAs, own 128 rows) --------------------
+    const int q = warp & 3;
+    uint32_t as = 0, aphase = 0, sb = 0;
+    const uint32_t stg_base = smem_base + STAGES * STAGE_BYTES + q * 2 * EPI_STAGE_BYTES;
+    for (int t = pair; t < num_tiles; t += num_pairs) {
+      int mt, nt;
+      tile_coords(t, p.m_tiles, p.n_tiles, 8, mt, nt);
+      mbar_wait(&acc_full[as], aphase);
+      tc_fence_after_sync();
+      epilogue_tile<PAIR_BN>(p, tmD, tmem_base + as * PAIR_BN + ((uint32_t)(q * 32) << 16), stg_base, sb,
+                             mt * 256 + (int)rank * BM + q * 32, nt * PAIR_BN);
+      tc_fence_before_sync();
+      __syncwarp();
+      if (lane_id() == 0) mbar_arrive_cluster(mapa_shared(smem_u32(&acc_empty[as]), 0));
+      if (++as == 2) { as = 0; aphase ^= 1; }
+    }
+    if (lane_id() == 0) tma_store_wait_all();
+  }
+  tc_fence_before_sync();
+  __syncthreads();
+  cluster_sync_all();  // neither CTA may retire (or free TMEM) while the pair's MMAs / remote arrives are in flight
+  if (warp == 0) tmem_dealloc_pair(tmem_base, TMEM_COLS);
 }
 
 // ---------------------------------------------------------------------------------------
@@ -383,6 +544,51 @@ static int launch_tma_gemm(const void* A, const void* B, TmaGemmParams p, int ld
   return 0;
 }
 
+template <int PAIR_BN, int STAGES>
+static int launch_tma_gemm_pair(const void* A, const void* B, TmaGemmParams p, int lda, int ldb, cudaStream_t s) {
+  CUtensorMap tmA, tmB, tmD;
+  int rc = p.a_mn ? make_tmap_bf16_2d(&tmA, A, p.K, p.M, lda, BK, 64) : make_tmap_bf16_2d(&tmA, A, p.M, p.K, lda, BM, BK);
+  if (rc) return rc;
+  rc = p.b_mn ? make_tmap_bf16_2d(&tmB, B, p.K, p.N, ldb, BK, 64) : make_tmap_bf16_2d(&tmB, B, p.N, p.K, ldb, PAIR_BN / 2, BK);
+  if (rc) return rc;
+  const void* D = p.Dh ? (const void*)p.Dh : (const void*)p.Df;
+  const size_t es = p.Dh ? 2 : 4;
+  p.tma_store = (!(p.Dh && p.Df) && ((size_t)p.ldd * es) % 16 == 0 && ((uintptr_t)D & 15) == 0) ? 1 : 0;
+  if (p.tma_store) {
+    rc = make_tmap_out(&tmD, D, p.M, p.N, p.ldd, !p.Dh);
+    if (rc) return rc;
+  } else {
+    tmD = tmA;
+  }
+  p.m_tiles = (p.M + 255) / 256;
+  p.n_tiles = (p.N + PAIR_BN - 1) / PAIR_BN;
+  constexpr size_t smem = (size_t)STAGES * (BM * BK * 2 + (PAIR_BN / 2) * BK * 2) + EPI_SMEM_BYTES + 1024;
+  auto kern = tma_gemm_pair_kernel<PAIR_BN, STAGES>;
+  static int sms = 0;
+  if (!sms) {
+    TFDL_CUDA_OK(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
+    int dev = 0, n = 148;
+    TFDL_CUDA_OK(cudaGetDevice(&dev));
+    TFDL_CUDA_OK(cudaDeviceGetAttribute(&n, cudaDevAttrMultiProcessorCount, dev));
+    sms = n;
+  }
+  int pairs = p.m_tiles * p.n_tiles < sms / 2 ? p.m_tiles * p.n_tiles : sms / 2;
+  cudaLaunchConfig_t cfg{};
+  cfg.gridDim = dim3(2 * pairs);
+  cfg.blockDim = dim3(192);
+  cfg.dynamicSmemBytes = smem;
+  cfg.stream = s;
+  cudaLaunchAttribute attr[1];
+  attr[0].id = cudaLaunchAttributeClusterDimension;
+  attr[0].val.clusterDim.x = 2;
+  attr[0].val.clusterDim.y = 1;
+  attr[0].val.clusterDim.z = 1;
+  cfg.attrs = attr;
+  cfg.numAttrs = 1;
+  TFDL_CUDA_OK(cudaLaunchKernelEx(&cfg, kern, tmA, tmB, tmD, p));
+  return 0;
+}
+
 }  // namespace tfdl
 
 extern "C" int tfdl_gemm_bf16_tma(const void* A, const void* B, float* Df, void* Dh, const float* bias, int M,
@@ -405,6 +611,19 @@ extern "C" int tfdl_gemm_bf16_tma_ex(const void* A, const void* B, float* Df, vo
   cudaStream_t s = (cudaStream_t)stream;
   // Tile choice: 128x256 when there are enough tiles to fill the chip, else 128x128 / 128x64
   long tiles256 = (long)((M + 127) / 128) * ((N + 255) / 256);
+  static int pair_mode = -1;  // TFDL_GEMM_PAIR=0 keeps every problem on the 1-CTA kernel
+  if (pair_mode < 0) {
+    const char* e = getenv("TFDL_GEMM_PAIR");
+    pair_mode = e ? atoi(e) : 1;
+  }
+  if (pair_mode && N >= 128 && M >= 256 && tiles256 >= 60) {
+    // 256 x 256 or 256 x 128 tiles per CTA pair: pick the one with the cheaper last wave (74 pairs per wave)
+    const long mt = (M + 255) / 256, pairs = 74;
+    const long c256 = ((mt * ((N + 255) / 256) + pairs - 1) / pairs) * 256;
+    const long c128 = ((mt * ((N + 127) / 128) + pairs - 1) / pairs) * 205;  // measured: a 128-wide tile costs ~0.8 of a 256-wide one
+    if (c128 < c256) return launch_tma_gemm_pair<128, 8>(A, B, p, lda, ldb, s);
+    return launch_tma_gemm_pair<256, 6>(A, B, p, lda, ldb, s);
+  }
   if (N >= 256 && tiles256 >= 120) return launch_tma_gemm<256, 4>(A, B, p, lda, ldb, s);
   if (N > 64) return launch_tma_gemm<128, 6>(A, B, p, lda, ldb, s);
   return launch_tma_gemm<64, 8>(A, B, p, lda, ldb, s);

@@ -121,3 +121,21 @@ def test_linear_autograd_all_three_gemms_on_tcgen05(act):
     torch.testing.assert_close(x.grad, xr.grad, rtol=5e-2, atol=2e-2)
     torch.testing.assert_close(w.grad, wr.grad, rtol=5e-2, atol=5e-2)
     torch.testing.assert_close(b.grad, br.grad, rtol=2e-2, atol=5e-2)
+
+
+@pytest.mark.parametrize("a_mn,b_mn", [(False, False), (False, True), (True, False), (True, True)])
+@pytest.mark.parametrize("M,N,K", [(4096, 1024, 256), (4000, 1000, 200), (8192, 768, 64)])
+def test_tma_gemm_cta_pair_kernel(M, N, K, a_mn, b_mn):
+    """Shapes with >= 120 128x256 tiles go to the cta_group::2 kernel (256 x 256 tile per CTA pair): all four
+    operand-major combinations, ragged M / N / K edges."""
+    from tfdl.ops.gemm import gemm_tma
+
+    torch.manual_seed(8)
+    a = (torch.randn((K, M) if a_mn else (M, K), device="cuda") * 0.5).bfloat16()
+    b = (torch.randn((K, N) if b_mn else (N, K), device="cuda") * 0.5).bfloat16()
+    out = gemm_tma(a, b, a_mn=a_mn, b_mn=b_mn, out_dtype=torch.float32)
+    torch.testing.assert_close(out, _ref(a, b, a_mn, b_mn), rtol=2e-3, atol=2e-2 * (K ** 0.5) / 8)
+    bias = torch.randn(N, device="cuda")
+    out16 = gemm_tma(a, b, a_mn=a_mn, b_mn=b_mn, bias=bias, act="gelu")
+    ref = torch.nn.functional.gelu(_ref(a, b, a_mn, b_mn) + bias, approximate="tanh")
+    torch.testing.assert_close(out16.float(), ref, rtol=2e-2, atol=0.15)
