@@ -148,6 +148,12 @@ __device__ __forceinline__ void tma_store_2d(const void* tmap, uint32_t src_smem
                "r"(src_smem), "r"(c0), "r"(c1)
                : "memory");
 }
+// 2-D tiled tensor reduction shared -> global: global[tile] += smem[tile] (element type from the tensor map).
+__device__ __forceinline__ void tma_reduce_add_2d(const void* tmap, uint32_t src_smem, int32_t c0, int32_t c1) {
+  asm volatile("cp.reduce.async.bulk.tensor.2d.global.shared::cta.add.tile.bulk_group [%0, {%2, %3}], [%1];" ::"l"(tmap),
+               "r"(src_smem), "r"(c0), "r"(c1)
+               : "memory");
+}
 __device__ __forceinline__ void st_shared_v4(uint32_t addr, uint32_t a, uint32_t b, uint32_t c, uint32_t d) {
   asm volatile("st.shared.v4.b32 [%0], {%1, %2, %3, %4};" ::"r"(addr), "r"(a), "r"(b), "r"(c), "r"(d) : "memory");
 }

@@ -37,6 +37,7 @@ struct TmaGemmParams {
   int act;                 // 0 none, 1 relu, 2 gelu(tanh)
   int m_tiles, n_tiles;
   int a_mn, b_mn;          // operand stored [K][rows] (MN-major) instead of [rows][K]
+  int ksplit;              // split-K factor (> 1: fp32 output accumulated with TMA reduce-add into a zeroed buffer)
   int tma_store;           // epilogue through smem + TMA store (needs a 16-byte-multiple output pitch)
 };
 
@@ -97,9 +98,10 @@ __device__ __forceinline__ void epi_apply(uint32_t (&v)[32], const float* bias, 
 // global element (row0, n0). Shared by the 1-CTA and the CTA-pair kernels.
 template <int BN_T>
 __device__ __forceinline__ void epilogue_tile(const TmaGemmParams& p, const CUtensorMap& tmD, uint32_t t_row,
-                                              uint32_t stg_base, uint32_t& sb, int row0, int n0) {
+                                              uint32_t stg_base, uint32_t& sb, int row0, int n0, bool first_split) {
   constexpr int BN = BN_T;
   const int row = row0 + (int)lane_id();
+  const float* bias = first_split ? p.bias : nullptr;  // split-K: only one split adds the bias
   if (p.tma_store) {
     const int CH = p.Dh ? 64 : 32;  // output columns per 128-byte staged row
     const uint32_t lane = lane_id();
@@ -111,8 +113,8 @@ __device__ __forceinline__ void epilogue_tile(const TmaGemmParams& p, const CUte
       tmem_ld32(t_row + c, v);
       if (p.Dh) tmem_ld32(t_row + c + 32, v2);
       tmem_ld_wait();
-      epi_apply(v, p.bias, col0, p.N, p.act);
-      if (p.Dh) epi_apply(v2, p.bias, col0 + 32, p.N, p.act);
+      epi_apply(v, bias, col0, p.N, p.act);
+      if (p.Dh) epi_apply(v2, bias, col0 + 32, p.N, p.act);
       // the bulk store that last read this staging buffer (two chunks ago) must have drained it
       if (lane == 0) asm volatile("cp.async.bulk.wait_group.read 1;" ::: "memory");
       __syncwarp();
@@ -136,7 +138,8 @@ __device__ __forceinline__ void epilogue_tile(const TmaGemmParams& p, const CUte
       fence_proxy_async_smem();
       __syncwarp();
       if (lane == 0) {
-        tma_store_2d(&tmD, sbuf, col0, row0);
+        if (p.ksplit > 1) tma_reduce_add_2d(&tmD, sbuf, col0, row0);
+        else tma_store_2d(&tmD, sbuf, col0, row0);
         tma_store_commit();
       }
       sb ^= 1;
@@ -149,7 +152,7 @@ __device__ __forceinline__ void epilogue_tile(const TmaGemmParams& p, const CUte
       tmem_ld_wait();
       const int col0 = n0 + c;
       if (row < p.M && col0 < p.N) {
-        epi_apply(v, p.bias, col0, p.N, p.act);
+        epi_apply(v, bias, col0, p.N, p.act);
         const bool full = (col0 + 32 <= p.N);
         if (p.Dh) {
           __nv_bfloat16* dst = p.Dh + (size_t)row * p.ldd + col0;
@@ -207,6 +210,7 @@ tma_gemm_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__
   const int warp = threadIdx.x >> 5;
   const int num_tiles = p.m_tiles * p.n_tiles;
   const int k_blocks = (p.K + BK - 1) / BK;
+  const int k_per = (k_blocks + p.ksplit - 1) / p.ksplit, num_units = num_tiles * p.ksplit;
   constexpr uint32_t TMEM_COLS = tmem_cols_for(2 * BN);
 
   if (warp == 0) {
@@ -238,10 +242,11 @@ tma_gemm_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__
     // ------------------------------ TMA producer ------------------------------
     if (elect_one()) {
       uint32_t stage = 0, phase = 0;
-      for (int t = blockIdx.x; t < num_tiles; t += gridDim.x) {
+      for (int u = blockIdx.x; u < num_units; u += gridDim.x) {
+        const int t = u / p.ksplit, kb0 = (u % p.ksplit) * k_per, kb1 = min(k_blocks, kb0 + k_per);
         int mt, nt;
         tile_coords(t, p.m_tiles, p.n_tiles, 16, mt, nt);
-        for (int kb = 0; kb < k_blocks; ++kb) {
+        for (int kb = kb0; kb < kb1; ++kb) {
           mbar_wait(&empty_bar[stage], phase ^ 1);
           mbar_expect_tx(&full_bar[stage], STAGE_BYTES);
           const uint32_t sa = smem_base + stage * STAGE_BYTES;
@@ -267,11 +272,12 @@ tma_gemm_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__
     if (elect_one()) {
       const uint32_t idesc = umma_idesc_bf16(BM, BN, p.a_mn != 0, p.b_mn != 0);
       uint32_t stage = 0, phase = 0, as = 0, aphase = 0;
-      for (int t = blockIdx.x; t < num_tiles; t += gridDim.x) {
+      for (int u = blockIdx.x; u < num_units; u += gridDim.x) {
+        const int t = u / p.ksplit, kb0 = (u % p.ksplit) * k_per, kb1 = min(k_blocks, kb0 + k_per);
         mbar_wait(&acc_empty[as], aphase ^ 1);
         tc_fence_after_sync();
         const uint32_t d_tmem = tmem_base + as * BN;
-        for (int kb = 0; kb < k_blocks; ++kb) {
+        for (int kb = kb0; kb < kb1; ++kb) {
           mbar_wait(&full_bar[stage], phase);
           tc_fence_after_sync();
           const uint32_t sa = smem_base + stage * STAGE_BYTES;
@@ -284,7 +290,7 @@ tma_gemm_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__
                                  : umma_smem_desc(sa + k * 32, 16, 1024, SWZ_128B);
             uint64_t bd = p.b_mn ? umma_smem_desc(sb + k * 2048, 8192, 1024, SWZ_128B)
                                  : umma_smem_desc(sb + k * 32, 16, 1024, SWZ_128B);
-            umma_bf16(d_tmem, ad, bd, idesc, (kb | k) != 0);
+            umma_bf16(d_tmem, ad, bd, idesc, (kb > kb0) || (k != 0));
           }
           umma_commit(&empty_bar[stage]);
           if (++stage == STAGES) { stage = 0; phase ^= 1; }
@@ -298,12 +304,13 @@ tma_gemm_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__
     const int q = warp & 3;  // TMEM lane quarter this warp may read
     uint32_t as = 0, aphase = 0, sb = 0;
     const uint32_t stg_base = smem_base + STAGES * STAGE_BYTES + q * 2 * EPI_STAGE_BYTES;
-    for (int t = blockIdx.x; t < num_tiles; t += gridDim.x) {
+    for (int u = blockIdx.x; u < num_units; u += gridDim.x) {
+        const int t = u / p.ksplit, kb0 = (u % p.ksplit) * k_per, kb1 = min(k_blocks, kb0 + k_per);
       int mt, nt;
       tile_coords(t, p.m_tiles, p.n_tiles, 16, mt, nt);
       mbar_wait(&acc_full[as], aphase);
       tc_fence_after_sync();
-      epilogue_tile<BN>(p, tmD, tmem_base + as * BN + ((uint32_t)(q * 32) << 16), stg_base, sb, mt * BM + q * 32, nt * BN);
+      epilogue_tile<BN>(p, tmD, tmem_base + as * BN + ((uint32_t)(q * 32) << 16), stg_base, sb, mt * BM + q * 32, nt * BN, kb0 == 0);
       tc_fence_before_sync();
       __syncwarp();
       if (lane_id() == 0) mbar_arrive(&acc_empty[as]);
@@ -344,6 +351,7 @@ tma_gemm_pair_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_const
   const int pair = blockIdx.x >> 1, num_pairs = gridDim.x >> 1;
   const int num_tiles = p.m_tiles * p.n_tiles;  // 256 x 256 tiles
   const int k_blocks = (p.K + BK - 1) / BK;
+  const int k_per = (k_blocks + p.ksplit - 1) / p.ksplit, num_units = num_tiles * p.ksplit;
   constexpr uint32_t TMEM_COLS = 2 * PAIR_BN;
 
   if (warp == 0) {
@@ -376,11 +384,12 @@ tma_gemm_pair_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_const
     // ------------------------------ TMA producer (both CTAs) ------------------------------
     if (elect_one()) {
       uint32_t stage = 0, phase = 0;
-      for (int t = pair; t < num_tiles; t += num_pairs) {
+      for (int u = pair; u < num_units; u += num_pairs) {
+        const int t = u / p.ksplit, kb0 = (u % p.ksplit) * k_per, kb1 = min(k_blocks, kb0 + k_per);
         int mt, nt;
         tile_coords(t, p.m_tiles, p.n_tiles, 8, mt, nt);
         const int m0 = mt * 256 + (int)rank * BM, n0 = nt * PAIR_BN + (int)rank * PAIR_HALF;
-        for (int kb = 0; kb < k_blocks; ++kb) {
+        for (int kb = kb0; kb < kb1; ++kb) {
           mbar_wait(&empty_bar[stage], phase ^ 1);  // own smem slot free (multicast commit from the leader)
           const uint32_t full_leader = mapa_shared(smem_u32(&full_bar[stage]), 0);
           if (leader) mbar_expect_tx(&full_bar[stage], 2 * STAGE_BYTES);
@@ -407,11 +416,12 @@ tma_gemm_pair_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_const
     if (leader && elect_one()) {
       const uint32_t idesc = umma_idesc_bf16(256, PAIR_BN, p.a_mn != 0, p.b_mn != 0);
       uint32_t stage = 0, phase = 0, as = 0, aphase = 0;
-      for (int t = pair; t < num_tiles; t += num_pairs) {
+      for (int u = pair; u < num_units; u += num_pairs) {
+        const int t = u / p.ksplit, kb0 = (u % p.ksplit) * k_per, kb1 = min(k_blocks, kb0 + k_per);
         mbar_wait(&acc_empty[as], aphase ^ 1);
         tc_fence_after_sync();
         const uint32_t d_tmem = tmem_base + as * PAIR_BN;
-        for (int kb = 0; kb < k_blocks; ++kb) {
+        for (int kb = kb0; kb < kb1; ++kb) {
           mbar_wait(&full_bar[stage], phase);
           tc_fence_after_sync();
           const uint32_t sa = smem_base + stage * STAGE_BYTES;
@@ -422,7 +432,7 @@ tma_gemm_pair_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_const
                                  : umma_smem_desc(sa + k * 32, 16, 1024, SWZ_128B);
             uint64_t bd = p.b_mn ? umma_smem_desc(sb + k * 2048, 8192, 1024, SWZ_128B)
                                  : umma_smem_desc(sb + k * 32, 16, 1024, SWZ_128B);
-            umma_bf16_pair(d_tmem, ad, bd, idesc, (kb | k) != 0);
+            umma_bf16_pair(d_tmem, ad, bd, idesc, (kb > kb0) || (k != 0));
           }
           umma_commit_pair(&empty_bar[stage]);
           if (++stage == STAGES) { stage = 0; phase ^= 1; }
@@ -436,13 +446,14 @@ tma_gemm_pair_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_const
     const int q = warp & 3;
     uint32_t as = 0, aphase = 0, sb = 0;
     const uint32_t stg_base = smem_base + STAGES * STAGE_BYTES + q * 2 * EPI_STAGE_BYTES;
-    for (int t = pair; t < num_tiles; t += num_pairs) {
+    for (int u = pair; u < num_units; u += num_pairs) {
+        const int t = u / p.ksplit, kb0 = (u % p.ksplit) * k_per, kb1 = min(k_blocks, kb0 + k_per);
       int mt, nt;
       tile_coords(t, p.m_tiles, p.n_tiles, 8, mt, nt);
       mbar_wait(&acc_full[as], aphase);
       tc_fence_after_sync();
       epilogue_tile<PAIR_BN>(p, tmD, tmem_base + as * PAIR_BN + ((uint32_t)(q * 32) << 16), stg_base, sb,
-                             mt * 256 + (int)rank * BM + q * 32, nt * PAIR_BN);
+                             mt * 256 + (int)rank * BM + q * 32, nt * PAIR_BN, kb0 == 0);
       tc_fence_before_sync();
       __syncwarp();
       if (lane_id() == 0) mbar_arrive_cluster(mapa_shared(smem_u32(&acc_empty[as]), 0));
@@ -538,7 +549,8 @@ static int launch_tma_gemm(const void* A, const void* B, TmaGemmParams p, int ld
     TFDL_CUDA_OK(cudaDeviceGetAttribute(&n, cudaDevAttrMultiProcessorCount, dev));
     sms = n;
   }
-  int grid = p.m_tiles * p.n_tiles < sms ? p.m_tiles * p.n_tiles : sms;
+  const int units = p.m_tiles * p.n_tiles * p.ksplit;
+  int grid = units < sms ? units : sms;
   kern<<<grid, 192, smem, s>>>(tmA, tmB, tmD, p);
   TFDL_CUDA_OK(cudaGetLastError());
   return 0;
@@ -572,7 +584,8 @@ static int launch_tma_gemm_pair(const void* A, const void* B, TmaGemmParams p, i
     TFDL_CUDA_OK(cudaDeviceGetAttribute(&n, cudaDevAttrMultiProcessorCount, dev));
     sms = n;
   }
-  int pairs = p.m_tiles * p.n_tiles < sms / 2 ? p.m_tiles * p.n_tiles : sms / 2;
+  const int units = p.m_tiles * p.n_tiles * p.ksplit;
+  int pairs = units < sms / 2 ? units : sms / 2;
   cudaLaunchConfig_t cfg{};
   cfg.gridDim = dim3(2 * pairs);
   cfg.blockDim = dim3(192);
@@ -599,6 +612,12 @@ extern "C" int tfdl_gemm_bf16_tma(const void* A, const void* B, float* Df, void*
 extern "C" int tfdl_gemm_bf16_tma_ex(const void* A, const void* B, float* Df, void* Dh, const float* bias, int M,
                                      int N, int K, int lda, int ldb, int ldd, int a_mn, int b_mn, int act,
                                      void* stream) {
+  return tfdl_gemm_bf16_tma_splitk(A, B, Df, Dh, bias, M, N, K, lda, ldb, ldd, a_mn, b_mn, act, 1, stream);
+}
+
+extern "C" int tfdl_gemm_bf16_tma_splitk(const void* A, const void* B, float* Df, void* Dh, const float* bias, int M,
+                                         int N, int K, int lda, int ldb, int ldd, int a_mn, int b_mn, int act,
+                                         int ksplit, void* stream) {
   using namespace tfdl;
   TFDL_REQUIRE(M > 0 && N > 0 && K > 0, "gemm_tma: empty problem");
   TFDL_REQUIRE(lda % 8 == 0 && ldb % 8 == 0, "gemm_tma: lda, ldb must be multiples of 8");
@@ -608,9 +627,19 @@ extern "C" int tfdl_gemm_bf16_tma_ex(const void* A, const void* B, float* Df, vo
   TmaGemmParams p{};
   p.Df = Df; p.Dh = (__nv_bfloat16*)Dh; p.bias = bias; p.M = M; p.N = N; p.K = K; p.ldd = ldd; p.act = act;
   p.a_mn = a_mn; p.b_mn = b_mn;
+  const int k_blocks = (K + BK - 1) / BK;
+  if (ksplit < 1) ksplit = 1;
+  if (ksplit > k_blocks) ksplit = k_blocks;
+  if (ksplit > 1) {
+    TFDL_REQUIRE(Df && !Dh && act == 0 && (ldd % 4) == 0 && ((uintptr_t)Df & 15) == 0,
+                 "gemm_tma split-K: needs a zero-initialised fp32 output with a 16-byte-multiple pitch and no activation");
+    const int k_per = (k_blocks + ksplit - 1) / ksplit;
+    ksplit = (k_blocks + k_per - 1) / k_per;  // no empty split
+  }
+  p.ksplit = ksplit;
   cudaStream_t s = (cudaStream_t)stream;
   // Tile choice: 128x256 when there are enough tiles to fill the chip, else 128x128 / 128x64
-  long tiles256 = (long)((M + 127) / 128) * ((N + 255) / 256);
+  long tiles256 = (long)((M + 127) / 128) * ((N + 255) / 256) * ksplit;
   static int pair_mode = -1;  // TFDL_GEMM_PAIR=0 keeps every problem on the 1-CTA kernel
   if (pair_mode < 0) {
     const char* e = getenv("TFDL_GEMM_PAIR");
@@ -619,8 +648,8 @@ extern "C" int tfdl_gemm_bf16_tma_ex(const void* A, const void* B, float* Df, vo
   if (pair_mode && N >= 128 && M >= 256 && tiles256 >= 60) {
     // 256 x 256 or 256 x 128 tiles per CTA pair: pick the one with the cheaper last wave (74 pairs per wave)
     const long mt = (M + 255) / 256, pairs = 74;
-    const long c256 = ((mt * ((N + 255) / 256) + pairs - 1) / pairs) * 256;
-    const long c128 = ((mt * ((N + 127) / 128) + pairs - 1) / pairs) * 205;  // measured: a 128-wide tile costs ~0.8 of a 256-wide one
+    const long c256 = ((mt * ((N + 255) / 256) * ksplit + pairs - 1) / pairs) * 256;
+    const long c128 = ((mt * ((N + 127) / 128) * ksplit + pairs - 1) / pairs) * 205;  // measured: a 128-wide tile costs ~0.8 of a 256-wide one
     if (c128 < c256) return launch_tma_gemm_pair<128, 8>(A, B, p, lda, ldb, s);
     return launch_tma_gemm_pair<256, 6>(A, B, p, lda, ldb, s);
   }

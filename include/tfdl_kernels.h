@@ -75,6 +75,10 @@ int tfdl_gemm_bf16_tma(const void* A, const void* B, float* Df, void* Dh, const 
  * 128B-swizzled column blocks: Dense dgrad (dy W) and wgrad (dy^T x) without transposing anything. */
 int tfdl_gemm_bf16_tma_ex(const void* A, const void* B, float* Df, void* Dh, const float* bias, int M, int N,
                           int K, int lda, int ldb, int ldd, int a_mn, int b_mn, int act, void* stream);
+/* same, with the reduction split `ksplit` ways across CTAs (long-K, few-tile problems such as weight gradients):
+ * fp32 output only, no activation, and the caller zero-initialises Df - splits accumulate with TMA reduce-add. */
+int tfdl_gemm_bf16_tma_splitk(const void* A, const void* B, float* Df, void* Dh, const float* bias, int M, int N, int K,
+                              int lda, int ldb, int ldd, int a_mn, int b_mn, int act, int ksplit, void* stream);
 
 
 /* ---- fused gradient all-reduce + SGD over NVLink peer memory ------------------------------

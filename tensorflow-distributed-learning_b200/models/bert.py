@@ -94,6 +94,10 @@ class BertMLM(keras.Model):
             x = b["ln2"].call(x + b["ff2"].call(b["ff1"].call(x, ctx), ctx), ctx).to(dt)
         h = self.mlm_ln.call(self.mlm_dense.call(x, ctx), ctx).to(dt)
         w = ctx.param(self.word.embeddings)  # tied decoder
+        if dt == torch.bfloat16 and h.is_cuda:
+            from ..ops.gemm import tied_decoder
+
+            return tied_decoder(h, w, ctx.param(self.mlm_bias.bias)).float()
         logits = F.linear(h, w.to(dt)) if dt != torch.float32 else F.linear(h, w)
         return self.mlm_bias.call(logits.float(), ctx)
 

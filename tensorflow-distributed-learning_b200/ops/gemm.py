@@ -42,27 +42,47 @@ def gemm_gather(a: torch.Tensor, b: torch.Tensor, *, a_mn: bool = False, b_mn: b
     return out
 
 
+def auto_ksplit(M: int, N: int, K: int) -> int:
+    """Split-K factor for problems whose output has too few tiles to fill 148 SMs but whose reduction is long
+    (weight gradients: M, N = layer widths, K = tokens). 1 = no split."""
+    tiles = -(-M // 128) * -(-N // 256)
+    kb = -(-K // 64)
+    if tiles >= 60 or kb < 16:
+        return 1
+    return max(1, min(148 // max(tiles, 1), kb // 8, 16))
+
+
 def gemm_tma(a: torch.Tensor, b: torch.Tensor, *, a_mn: bool = False, b_mn: bool = False,
              bias: torch.Tensor | None = None, act: str | None = None, out_dtype: torch.dtype = torch.bfloat16,
-             out: torch.Tensor | None = None) -> torch.Tensor:
-    """D[M,N] = act(A[M,K] @ B[N,K]^T + bias) on the persistent TMA + tcgen05 kernel.
+             out: torch.Tensor | None = None, k_split: int | None = None) -> torch.Tensor:
+    """D[M,N] = act(A[M,K] @ B[N,K]^T + bias) on the persistent TMA + tcgen05 kernels (1-CTA or CTA-pair).
 
     ``a_mn`` / ``b_mn``: the operand is stored transposed (``a`` is [K, M] / ``b`` is [K, N]) and is read as
-    an MN-major tensor-core operand - no transpose copy is made."""
+    an MN-major tensor-core operand - no transpose copy is made. ``out`` may be a column slice of a wider buffer
+    (its row stride is the output pitch). ``k_split``: None = automatic for fp32 outputs without activation
+    (the output is then zero-filled here and the splits accumulate with TMA reduce-add)."""
     assert a.dtype == torch.bfloat16 and b.dtype == torch.bfloat16 and a.is_cuda and b.is_cuda
-    a = a.contiguous()
-    b = b.contiguous()
+    if a.stride(-1) != 1 or a.stride(0) % 8:
+        a = a.contiguous()
+    if b.stride(-1) != 1 or b.stride(0) % 8:
+        b = b.contiguous()
     K, M = a.shape if a_mn else a.shape[::-1]
     Kb, N = b.shape if b_mn else b.shape[::-1]
     assert K == Kb, (a.shape, b.shape)
     if out is None:
         out = torch.empty((M, N), device=a.device, dtype=out_dtype)
+    assert out.shape == (M, N) and out.stride(1) == 1
     d32 = out if out.dtype == torch.float32 else None
     d16 = out if out.dtype == torch.bfloat16 else None
-    rc = _lib.kernels().tfdl_gemm_bf16_tma_ex(
+    ks = 1
+    if d32 is not None and act in (None, "none", "linear") and out.stride(0) % 4 == 0:
+        ks = auto_ksplit(M, N, K) if k_split is None else int(k_split)
+    if ks > 1:
+        out.zero_()
+    rc = _lib.kernels().tfdl_gemm_bf16_tma_splitk(
         _lib.ptr(a), _lib.ptr(b), _lib.ptr(d32), _lib.ptr(d16), _lib.ptr(bias),
-        M, N, K, a.stride(0), b.stride(0), out.stride(0), int(a_mn), int(b_mn), _ACT[act], _lib.cur_stream())
-    _lib.check(rc, "tfdl_gemm_bf16_tma_ex")
+        M, N, K, a.stride(0), b.stride(0), out.stride(0), int(a_mn), int(b_mn), _ACT[act], ks, _lib.cur_stream())
+    _lib.check(rc, "tfdl_gemm_bf16_tma_splitk")
     return out
 
 
@@ -105,3 +125,45 @@ def linear(x: torch.Tensor, w: torch.Tensor, bias: torch.Tensor | None = None, a
     """Dense layer on the tensor core with autograd (bf16 operands, fp32 accumulation, fp32 weight gradient).
     Needs every GEMM dimension (tokens, in, out) to be a multiple of 8."""
     return _LinearFn.apply(x, w, bias, act)
+
+
+class _TiedDecoderFn(torch.autograd.Function):
+    """logits = h W^T + b for an output width that is not a multiple of 8 (BERT's vocabulary: 30522).
+
+    Row pitches that are not 16-byte multiples push library GEMMs onto slow legacy kernels and rule out TMA. Here the
+    weight, the bias and the logits live in buffers padded to the next multiple of 8 columns: pad rows of W are zero
+    and pad bias entries are -30000, so the pad logits vanish from any softmax; the caller sees the [T, V] column
+    slice. Forward, dgrad and wgrad run on the tcgen05 CTA-pair kernel."""
+
+    @staticmethod
+    def forward(ctx, h, w, bias):
+        V, H = w.shape
+        Vp = (V + 7) // 8 * 8
+        h2 = (h if h.dtype == torch.bfloat16 else h.bfloat16()).reshape(-1, H)
+        wp = torch.zeros((Vp, H), device=w.device, dtype=torch.bfloat16)
+        wp[:V] = w
+        bp = torch.full((Vp,), -30000.0, device=w.device, dtype=torch.float32)
+        if bias is not None:
+            bp[:V] = bias
+        else:
+            bp[:V] = 0
+        out = gemm_tma(h2, wp, bias=bp)
+        ctx.save_for_backward(h2, wp)
+        ctx.meta = (V, Vp, h.shape, w.dtype, bias is not None)
+        return out[:, :V].reshape(*h.shape[:-1], V) if Vp == V else out[:, :V].unflatten(0, h.shape[:-1])
+
+    @staticmethod
+    def backward(ctx, dy):
+        h2, wp = ctx.saved_tensors
+        V, Vp, h_shape, w_dtype, has_bias = ctx.meta
+        dyp = torch.zeros((h2.shape[0], Vp), device=dy.device, dtype=torch.bfloat16)
+        dyp[:, :V] = dy.reshape(-1, V)
+        dh = gemm_tma(dyp, wp, b_mn=True)
+        dw = gemm_tma(dyp, h2, a_mn=True, b_mn=True, out_dtype=torch.float32)[:V]
+        db = dyp.sum(0, dtype=torch.float32)[:V] if has_bias else None
+        return dh.reshape(h_shape), dw.to(w_dtype), db
+
+
+def tied_decoder(h: torch.Tensor, w: torch.Tensor, bias: torch.Tensor | None = None) -> torch.Tensor:
+    """h [..., H] x w [V, H]^T + bias [V] -> [..., V] (bf16) on tcgen05; V need not be a multiple of 8."""
+    return _TiedDecoderFn.apply(h, w, bias)

@@ -139,3 +139,43 @@ def test_tma_gemm_cta_pair_kernel(M, N, K, a_mn, b_mn):
     out16 = gemm_tma(a, b, a_mn=a_mn, b_mn=b_mn, bias=bias, act="gelu")
     ref = torch.nn.functional.gelu(_ref(a, b, a_mn, b_mn) + bias, approximate="tanh")
     torch.testing.assert_close(out16.float(), ref, rtol=2e-2, atol=0.15)
+
+
+@pytest.mark.parametrize("M,N,K", [(768, 768, 8192), (768, 3072, 4096), (128, 512, 2048)])
+def test_tma_gemm_split_k_reduce_add(M, N, K):
+    """Few output tiles + long reduction (weight gradients): K is split across CTAs, partial tiles accumulate with
+    TMA reduce-add into the zero-filled fp32 output."""
+    from tfdl.ops.gemm import auto_ksplit, gemm_tma
+
+    torch.manual_seed(9)
+    a = (torch.randn(K, M, device="cuda") * 0.5).bfloat16()
+    b = (torch.randn(K, N, device="cuda") * 0.5).bfloat16()
+    assert auto_ksplit(768, 768, 8192) > 1 and auto_ksplit(8192, 8192, 8192) == 1
+    ref = _ref(a, b, True, True)
+    for ks in (None, 3, 7):
+        out = gemm_tma(a, b, a_mn=True, b_mn=True, out_dtype=torch.float32, k_split=ks)
+        torch.testing.assert_close(out, ref, rtol=2e-3, atol=2e-2 * (K ** 0.5) / 8)
+    bias = torch.randn(N, device="cuda")
+    out = gemm_tma(a, b, a_mn=True, b_mn=True, out_dtype=torch.float32, bias=bias, k_split=4)
+    torch.testing.assert_close(out, ref + bias, rtol=2e-3, atol=2e-2 * (K ** 0.5) / 8)
+
+
+def test_tied_decoder_unaligned_vocab():
+    from tfdl.ops.gemm import tied_decoder
+
+    torch.manual_seed(10)
+    V, H, T = 1003, 256, 512
+    h = (torch.randn(2, T // 2, H, device="cuda") * 0.5).bfloat16().requires_grad_()
+    w = (torch.randn(V, H, device="cuda") * 0.05).requires_grad_()
+    b = torch.randn(V, device="cuda").requires_grad_()
+    y = tied_decoder(h, w, b)
+    assert y.shape == (2, T // 2, V)
+    gy = torch.randn(2, T // 2, V, device="cuda") * 0.1
+    y.float().backward(gy)
+    hr, wr, br = h.detach().float().requires_grad_(), w.detach().bfloat16().float().requires_grad_(), b.detach().clone().requires_grad_()
+    yr = torch.nn.functional.linear(hr, wr, br)
+    yr.backward(gy.bfloat16().float())
+    torch.testing.assert_close(y.float(), yr, rtol=2e-2, atol=5e-2)
+    torch.testing.assert_close(h.grad.float(), hr.grad, rtol=5e-2, atol=2e-2)
+    torch.testing.assert_close(w.grad, wr.grad, rtol=5e-2, atol=5e-2)
+    torch.testing.assert_close(b.grad, br.grad, rtol=2e-2, atol=5e-2)

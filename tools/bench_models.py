@@ -39,6 +39,7 @@ def main():
     ap.add_argument("--steps", type=int, default=20)
     ap.add_argument("--warmup", type=int, default=5)
     ap.add_argument("--impl", default="both", choices=["tfdl", "standin", "both"])
+    ap.add_argument("--profile", action="store_true", help="after timing: torch.profiler kernel table of 2 steps (diagnosis only)")
     a = ap.parse_args()
     world, rank, lrank = int(os.environ.get("WORLD_SIZE", 1)), int(os.environ.get("RANK", 0)), int(os.environ.get("LOCAL_RANK", 0))
     dev = torch.device("cuda", lrank)
@@ -72,6 +73,13 @@ def main():
         out["tfdl"] = {"ms_per_step": ms, "value": a.batch * world / ms * 1e3, "unit": unit, "engine": type(eng).__name__,
                        "fused_allreduce_sgd": eng._fused is not None,
                        "allreduce": getattr(getattr(eng, "_fused", None), "torch_algo", None), "params": model.count_params()}
+        if a.profile and rank == 0:
+            from torch.profiler import ProfilerActivity, profile
+            with profile(activities=[ProfilerActivity.CUDA, ProfilerActivity.CPU]) as prof:
+                for _ in range(2):
+                    eng.train_step(batch)
+                torch.cuda.synchronize()
+            print(prof.key_averages().table(sort_by="cuda_time_total", row_limit=32, max_name_column_width=70))
         del model, eng
         torch.cuda.empty_cache()
     if a.impl in ("standin", "both"):
