@@ -178,7 +178,7 @@ def run_ours(args) -> dict:
         "config": {"model": MODEL, "global_batch": global_batch, "per_gpu_batch": B, "image": "28x28x1",
                    "parallelism": f"dp{world}", "allreduce": engine.algo_name,
                    "l2_policy": f"inputs larger than L2: {n_pool} distinct device-resident batches "
-                                f"({n_pool * rec >> 20} MiB) rotated, one D2D copy per step",
+                                f"({n_pool * rec >> 20} MiB) rotated, one D2D copy per step on the copy stream (overlaps the previous step, like the H2D copy of the e2e path)",
                    "optimizer_step_in_timed_region": True},
         "clocks": clocks,
         "e2e": {"value": round(global_batch * args.steps / (e2e_ms / 1e3), 1), "unit": "images/sec",
