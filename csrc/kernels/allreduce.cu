@@ -122,6 +122,7 @@ __device__ __forceinline__ void finish_step(const TfdlFusedArParams& p, uint32_t
 // one-shot
 // -------------------------------------------------------------------------------------------
 __global__ void __launch_bounds__(512) fused_ar_oneshot_kernel(TfdlFusedArParams p) {
+  pdl_wait();  // launched as a programmatic dependent of the last backward kernel: its gradients are final from here
   const uint32_t e = *p.epoch + 1;
   const int par = p.parity >= 0 ? p.parity : (int)((e - 1) & 1);
   const TfdlHyper h = *p.hyper;
@@ -275,7 +276,7 @@ extern "C" int tfdl_fused_allreduce_sgd(const TfdlFusedArParams* p, int algo, vo
   const int64_t n4 = p->n / 4;
   if (algo == TFDL_AR_ONESHOT || p->world == 1) {
     int grid = pick_grid(p, n4, threads);
-    fused_ar_oneshot_kernel<<<grid, threads, 0, s>>>(*p);
+    TFDL_CUDA_OK(launch_kernel_pdl(4, fused_ar_oneshot_kernel, dim3(grid), dim3(threads), 0, s, *p));
   } else if (algo == TFDL_AR_TWOSHOT) {
     int grid = pick_grid(p, (n4 + p->world - 1) / p->world, threads);
     fused_ar_sliced_kernel<false><<<grid, threads, 0, s>>>(*p);

@@ -151,6 +151,8 @@ conv2_dgrad_tma_kernel(const __grid_constant__ CUtensorMap tmDY, const __grid_co
   __syncthreads();
   tc_fence_after_sync();
   const uint32_t tmem = slot;
+  pdl_launch_dependents();
+  pdl_wait();  // dy2 (dense block) is complete from here on; everything above overlapped its tail
   if (threadIdx.x == 0) {
     mbar_expect_tx(&bar_tma, GW * GW * 128 + 9 * C2 * C1 * 2);
     tma_load_4d_(p_smem, &tmDY, 0, -2, -2, n, &bar_tma);
@@ -320,6 +322,7 @@ conv12_fwd_tma_kernel(const float* __restrict__ x, const float* __restrict__ w1,
   const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31, n = blockIdx.x;
   const uint32_t x_smem = smem_u32(smem), w_smem = x_smem + XROWS * 64;
   float* xs = reinterpret_cast<float*>(smem + XROWS * 64 + 9 * 128 * 64);  // the input image, fp32
+  pdl_launch_dependents();  // the dense block may start its prologue (TMEM alloc, barrier init) now
   if (clear2 && n == 0 && threadIdx.x < 2) clear2[threadIdx.x] = 0.f;
   if (warp == 0) tmem_alloc(&slot, 256);
   if (threadIdx.x == 32) {
@@ -456,6 +459,8 @@ conv21_bwd_tma_kernel(const __grid_constant__ CUtensorMap tmDY, const __grid_con
   __syncthreads();
   tc_fence_after_sync();
   const uint32_t tmem = slot;
+  pdl_launch_dependents();
+  pdl_wait();  // dy2 (dense block) is complete from here on; everything above overlapped its tail
   if (threadIdx.x == 0) {
     mbar_expect_tx(&bar_tma, GW * GW * 128 + 9 * C2 * C1 * 2);
     tma_load_4d_(p_smem, &tmDY, 0, -2, -2, n, &bar_tma);
@@ -672,8 +677,7 @@ extern "C" int tfdl_cnn_conv21_bwd_tma(const void* dy2, const void* w2h, const v
   const size_t smem = 288 * 128 + 9 * 64 * 64 + (size_t)d->H0 * d->W0 * 4 + (size_t)32 * ld * 5 + 16 + 1024;
   auto kern = conv21_bwd_tma_kernel<13>;
   if (int rc = set_smem_tma(kern, smem)) return rc;
-  kern<<<d->B, TT, smem, (cudaStream_t)stream>>>(tmDY, tmW, (const __nv_bfloat16*)a1, idx1, x, g_w1c, g_b1c,
-                                                (__nv_bfloat16*)g1_out, *d);
-  TFDL_CUDA_OK(cudaGetLastError());
+  TFDL_CUDA_OK(launch_kernel_pdl(2, kern, dim3(d->B), dim3(TT), smem, (cudaStream_t)stream, tmDY, tmW,
+                                 (const __nv_bfloat16*)a1, idx1, x, g_w1c, g_b1c, (__nv_bfloat16*)g1_out, *d));
   return 0;
 }

@@ -56,6 +56,34 @@ __device__ __forceinline__ bool elect_one() {
 #define TFDL_SPIN_LIMIT (1u << 28)
 
 // ----------------------------------------------------------------------------------------
+// Programmatic dependent launch (PDL): a kernel launched with the attribute below may start
+// while its stream predecessor is still running; it runs its on-chip prologue (TMEM
+// allocation, mbarrier init, descriptor prefetch) and then blocks in pdl_wait() until the
+// predecessor has completed and its writes are visible. The predecessor lets dependents go
+// early with pdl_launch_dependents(). Both are no-ops for kernels launched the normal way.
+// ----------------------------------------------------------------------------------------
+__device__ __forceinline__ void pdl_wait() { asm volatile("griddepcontrol.wait;" ::: "memory"); }
+__device__ __forceinline__ void pdl_launch_dependents() { asm volatile("griddepcontrol.launch_dependents;" ::: "memory"); }
+
+int pdl_mask();  // TFDL_PDL bit mask (errors.cu): 1 dense block, 2 conv backward, 4 all-reduce launched as programmatic dependents
+
+template <class... P, class... A>
+inline cudaError_t launch_kernel_pdl(int which, void (*kern)(P...), dim3 grid, dim3 block, size_t smem, cudaStream_t s,
+                                     A... args) {
+  cudaLaunchConfig_t cfg{};
+  cfg.gridDim = grid;
+  cfg.blockDim = block;
+  cfg.dynamicSmemBytes = smem;
+  cfg.stream = s;
+  cudaLaunchAttribute at[1];
+  at[0].id = cudaLaunchAttributeProgrammaticStreamSerialization;
+  at[0].val.programmaticStreamSerializationAllowed = 1;
+  cfg.attrs = at;
+  cfg.numAttrs = (pdl_mask() & which) ? 1 : 0;
+  return cudaLaunchKernelEx(&cfg, kern, args...);
+}
+
+// ----------------------------------------------------------------------------------------
 // mbarrier
 // ----------------------------------------------------------------------------------------
 __device__ __forceinline__ void mbar_init(uint64_t* bar, uint32_t count) {

@@ -130,6 +130,8 @@ dense_block_kernel(const __grid_constant__ CUtensorMap tmW1, const __grid_consta
   for (int j = 0; j < 16; ++j) my_b2[j] = (half == 0 && j < NC) ? __ldg(a.b2 + j) : 0.f;
 
   DBPHASE(1);
+  pdl_launch_dependents();
+  pdl_wait();  // a2 / idx2 (conv forward) are complete; the prologue above overlapped the previous kernel's tail
   // ---------------- phase 1: forward split-K chunk -> RED into acc -------------------------------------
   if (tid == 0) {
     mbar_expect_tx(&bar_tma, 16384 + 16384 + 2 * 2048);
@@ -479,7 +481,8 @@ extern "C" int tfdl_cnn_dense_block(const void* a2, const uint8_t* idx2, const v
   a.g_w2 = g_w2; a.g_b2 = g_b2; a.metrics = metrics; a.step_out = step_out; a.dh_out = (__nv_bfloat16*)dh_out; a.d = *d;
   const size_t smem = DB_SMEM + 1024;
   TFDL_CUDA_OK(cudaFuncSetAttribute(dense_block_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
-  dense_block_kernel<<<d->P2h * d->P2w, DB_THREADS, smem, (cudaStream_t)stream>>>(tmW1, tmA2, tmW2, tmDY, a);
+  TFDL_CUDA_OK(launch_kernel_pdl(1, dense_block_kernel, dim3(d->P2h * d->P2w), dim3(DB_THREADS), smem, (cudaStream_t)stream,
+                                 tmW1, tmA2, tmW2, tmDY, a));
   TFDL_CUDA_OK(cudaGetLastError());
   return 0;
 }

@@ -1,6 +1,7 @@
 // Thread-local last-error string behind the C ABI (see include/tfdl_kernels.h).
 #include <cstdarg>
 #include <cstdio>
+#include <cstdlib>
 #include "common.cuh"
 #include "../../include/tfdl_kernels.h"
 
@@ -11,6 +12,16 @@ void set_last_error(const char* fmt, ...) {
   va_start(ap, fmt);
   vsnprintf(g_err, sizeof(g_err), fmt, ap);
   va_end(ap);
+}
+int pdl_mask() {
+  static int m = -1;
+  if (m < 0) {
+    const char* e = getenv("TFDL_PDL");
+    // measured on B200 (bench.py, us/step): 0 -> 41.7, 1 -> 41.0, 4 -> 41.0, 5 -> 40.2, 2 -> 48.6 (conv backward CTAs land on
+    // SMs whose TMEM the dense block still holds), so the default is dense block + all-reduce
+    m = e ? atoi(e) : 5;
+  }
+  return m;
 }
 }  // namespace tfdl
 
