@@ -80,6 +80,16 @@ int tfdl_gemm_bf16_tma_ex(const void* A, const void* B, float* Df, void* Dh, con
 int tfdl_gemm_bf16_tma_splitk(const void* A, const void* B, float* Df, void* Dh, const float* bias, int M, int N, int K,
                               int lda, int ldb, int ldd, int a_mn, int b_mn, int act, int ksplit, void* stream);
 
+/* ---- LayerNorm (tf.keras.layers.LayerNormalization of the transformer config) -------------------------------------
+ * bf16 rows of H = 256, 512, 768 or 1024 elements, fp32 gamma/beta/statistics. forward: z = x (+ residual, optional;
+ * z_out receives the bf16 sum), y = LN(z); mean/rstd [T] are saved for the backward pass. backward: dgamma/dbeta are
+ * ACCUMULATED (zero them first). */
+int tfdl_layernorm_supported(int H);
+int tfdl_layernorm_fwd(const void* x, const void* residual, const float* gamma, const float* beta, void* y, void* z_out,
+                       float* mean, float* rstd, int T, int H, float eps, void* stream);
+int tfdl_layernorm_bwd(const void* dy, const void* z, const float* mean, const float* rstd, const float* gamma, void* dz,
+                       float* dgamma, float* dbeta, int T, int H, void* stream);
+
 
 /* ---- fused gradient all-reduce + SGD over NVLink peer memory ------------------------------
  * ref: README.md:17,21,23,67 (NcclAllReduce / CollectiveOps after every batch) and

@@ -437,7 +437,15 @@ class LayerNormalization(Layer):
         self.gamma = self.add_weight("gamma", (input_shape[-1],), "ones")
         self.beta = self.add_weight("beta", (input_shape[-1],), "zeros")
 
-    def call(self, x: torch.Tensor, ctx: CallContext) -> torch.Tensor:
+    def call(self, x: torch.Tensor, ctx: CallContext, residual: Optional[torch.Tensor] = None) -> torch.Tensor:
+        """LayerNorm(x + residual) over the last axis. bf16 CUDA activations run on the native streaming kernel
+        (ops/layernorm.py: residual add fused, fp32 statistics); everything else goes through torch in fp32."""
+        from ..ops import layernorm as _ln
+
+        if _ln.supported(x) and (residual is None or (residual.dtype == x.dtype and residual.shape == x.shape)):
+            return _ln.layer_norm(x, ctx.param(self.gamma), ctx.param(self.beta), self.epsilon, residual)
+        if residual is not None:
+            x = x + residual
         return F.layer_norm(x.float(), (x.shape[-1],), ctx.param(self.gamma), ctx.param(self.beta),
                             self.epsilon).to(x.dtype)
 

@@ -90,8 +90,8 @@ class BertMLM(keras.Model):
             k = b["k"].call(x, ctx).view(B, S, nh, hd).transpose(1, 2)
             v = b["v"].call(x, ctx).view(B, S, nh, hd).transpose(1, 2)
             a = F.scaled_dot_product_attention(q, k, v).transpose(1, 2).reshape(B, S, self.hidden)
-            x = b["ln1"].call(x + b["o"].call(a, ctx), ctx).to(dt)
-            x = b["ln2"].call(x + b["ff2"].call(b["ff1"].call(x, ctx), ctx), ctx).to(dt)
+            x = b["ln1"].call(b["o"].call(a, ctx), ctx, residual=x).to(dt)
+            x = b["ln2"].call(b["ff2"].call(b["ff1"].call(x, ctx), ctx), ctx, residual=x).to(dt)
         h = self.mlm_ln.call(self.mlm_dense.call(x, ctx), ctx).to(dt)
         w = ctx.param(self.word.embeddings)  # tied decoder
         if dt == torch.bfloat16 and h.is_cuda:

@@ -179,3 +179,33 @@ def test_tied_decoder_unaligned_vocab():
     torch.testing.assert_close(h.grad.float(), hr.grad, rtol=5e-2, atol=2e-2)
     torch.testing.assert_close(w.grad, wr.grad, rtol=5e-2, atol=5e-2)
     torch.testing.assert_close(b.grad, br.grad, rtol=2e-2, atol=5e-2)
+
+
+@pytest.mark.parametrize("H", [256, 768, 1024])
+@pytest.mark.parametrize("with_res", [False, True])
+def test_native_layernorm_fwd_bwd(H, with_res):
+    from tfdl.ops.layernorm import layer_norm, supported
+
+    torch.manual_seed(12)
+    T = 1000
+    x = (torch.randn(4, T // 4, H, device="cuda") * 2 + 0.5).bfloat16().requires_grad_()
+    r = (torch.randn(4, T // 4, H, device="cuda")).bfloat16().requires_grad_() if with_res else None
+    base = torch.randn(2 * H + 1, device="cuda")
+    g = (base[1:H + 1] * 0.1 + 1).requires_grad_()      # deliberately only 4-byte aligned, like an arena view
+    b = base[H + 1:].clone().requires_grad_()
+    assert supported(x)
+    y = layer_norm(x, g, b, 1e-5, r)
+    gy = torch.randn_like(y.float()) * 0.1
+    y.float().backward(gy)
+    xr = x.detach().float().requires_grad_()
+    rr = r.detach().float().requires_grad_() if with_res else None
+    gr, br = g.detach().clone().requires_grad_(), b.detach().clone().requires_grad_()
+    z = (xr + rr).bfloat16().float() if with_res else xr
+    yr = torch.nn.functional.layer_norm(z, (H,), gr, br, 1e-5)
+    yr.backward(gy.bfloat16().float())
+    torch.testing.assert_close(y.float(), yr, rtol=2e-2, atol=3e-2)
+    torch.testing.assert_close(x.grad.float(), xr.grad, rtol=3e-2, atol=3e-3)
+    if with_res:
+        torch.testing.assert_close(r.grad.float(), rr.grad, rtol=3e-2, atol=3e-3)
+    torch.testing.assert_close(g.grad, gr.grad, rtol=2e-2, atol=5e-2)
+    torch.testing.assert_close(b.grad, br.grad, rtol=2e-2, atol=5e-2)
