@@ -24,9 +24,19 @@ extern "C" int tfdl_cnn_step_launch(const TfdlCnnStep* s, void* stream, void* si
   return tfdl_cnn_step_launch_overlap(s, nullptr, 0, stream, side, nullptr, ev_fork, ev_join, nullptr, nullptr);
 }
 
+static int step_launch_impl(const TfdlCnnStep* s, const TfdlFusedArParams* early, int early_algo, void* stream, void* side,
+                            void* ar_stream, void* ev_fork, void* ev_join, void* ev_ar_fork, void* ev_ar_join, bool join_ar);
+
 extern "C" int tfdl_cnn_step_launch_overlap(const TfdlCnnStep* s, const TfdlFusedArParams* early, int early_algo,
                                             void* stream, void* side, void* ar_stream, void* ev_fork, void* ev_join,
                                             void* ev_ar_fork, void* ev_ar_join) {
+  return step_launch_impl(s, early, early_algo, stream, side, ar_stream, ev_fork, ev_join, ev_ar_fork, ev_ar_join, true);
+}
+
+// join_ar = false leaves the early bucket's all-reduce un-joined: the caller enqueues the last bucket's all-reduce
+// first (the two are independent and run side by side) and then waits on ev_ar_join itself.
+static int step_launch_impl(const TfdlCnnStep* s, const TfdlFusedArParams* early, int early_algo, void* stream, void* side,
+                            void* ar_stream, void* ev_fork, void* ev_join, void* ev_ar_fork, void* ev_ar_join, bool join_ar) {
   const TfdlCnnDims* d = &s->dims;
   cudaStream_t st = (cudaStream_t)stream, sd = (cudaStream_t)side;
   cudaEvent_t ef = (cudaEvent_t)ev_fork, ej = (cudaEvent_t)ev_join;
@@ -96,7 +106,7 @@ extern "C" int tfdl_cnn_step_launch_overlap(const TfdlCnnStep* s, const TfdlFuse
     TFDL_CUDA_OK(cudaEventRecord(ej, sd));
     TFDL_CUDA_OK(cudaStreamWaitEvent(st, ej, 0));
   }
-  if (overlap) TFDL_CUDA_OK(cudaStreamWaitEvent(st, (cudaEvent_t)ev_ar_join, 0));
+  if (overlap && join_ar) TFDL_CUDA_OK(cudaStreamWaitEvent(st, (cudaEvent_t)ev_ar_join, 0));
   return 0;
 }
 
@@ -120,9 +130,11 @@ struct TfdlCnnProgram {
 };
 
 static int enqueue_step(TfdlCnnProgram* p, int par, cudaStream_t st) {
-  TFDL_RC(tfdl_cnn_step_launch_overlap(&p->steps[par], p->has_early ? &p->ar_early[par] : nullptr, p->algo_early, st,
-                                       p->side, p->ar_stream, p->ev_fork, p->ev_join, p->ev_ar_fork, p->ev_ar_join));
+  TFDL_RC(step_launch_impl(&p->steps[par], p->has_early ? &p->ar_early[par] : nullptr, p->algo_early, st, p->side,
+                           p->ar_stream, p->ev_fork, p->ev_join, p->ev_ar_fork, p->ev_ar_join, false));
   TFDL_RC(tfdl_fused_allreduce_sgd(&p->ar[par], p->algo, st));
+  // the dense bucket's all-reduce (own stream, own flags) may still be running next to the conv bucket's: join now
+  if (p->has_early && p->steps[par].use_dense_block) TFDL_CUDA_OK(cudaStreamWaitEvent(st, p->ev_ar_join, 0));
   return 0;
 }
 
