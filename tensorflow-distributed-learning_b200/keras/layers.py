@@ -389,9 +389,27 @@ class BatchNormalization(Layer):
         self.moving_mean = self.add_weight("moving_mean", (c,), "zeros", trainable=False)
         self.moving_variance = self.add_weight("moving_variance", (c,), "ones", trainable=False)
 
-    def call(self, x: torch.Tensor, ctx: CallContext) -> torch.Tensor:
+    def call(self, x: torch.Tensor, ctx: CallContext, relu: bool = False,
+             residual: Optional[torch.Tensor] = None) -> torch.Tensor:
+        """y = BN(x); with ``relu`` / ``residual`` the bottleneck tail relu(BN(x) + residual) in the same pass.
+        NHWC bf16 CUDA activations run on the native streaming kernels (ops/batchnorm.py)."""
+        from ..ops import batchnorm as _bn
+
         g, b = ctx.param(self.gamma), ctx.param(self.beta)
         mm, mv = ctx.param(self.moving_mean), ctx.param(self.moving_variance)
+        if _bn.supported(x) and (residual is None or (residual.dtype == x.dtype and residual.shape == x.shape)):
+            if ctx.training:
+                # the kernel writes the running statistics through their arena pointers (no autograd version bump)
+                return _bn.batch_norm_train(x, g, b, mm.detach(), mv.detach(), 1.0 - self.momentum, self.epsilon, relu,
+                                            residual)
+            return _bn.batch_norm_infer(x, g, b, mm, mv, self.epsilon, relu, residual)
+        y = self._call_torch(x, ctx, g, b, mm, mv)
+        if residual is not None:
+            y = y + residual
+        return torch.relu(y) if relu else y
+
+    def _call_torch(self, x: torch.Tensor, ctx: CallContext, g: torch.Tensor, b: torch.Tensor, mm: torch.Tensor,
+                    mv: torch.Tensor) -> torch.Tensor:
         if x.dim() == 4:
             # NHWC activations viewed as channels_last NCHW: one fused (cuDNN) batch-norm kernel. The running
             # statistics are updated on private copies and written back after autograd has finished, because

@@ -2,11 +2,10 @@
 batch 256/GPU"). Same topology, layer names and parameter count as tf.keras.applications.ResNet50
 (25,636,712 parameters, 53,120 of them non-trainable BatchNorm statistics), NHWC.
 
-Execution: this model runs on the TorchEngine (convs / BatchNorm through torch ops in channels_last);
-what is native here is the part the reference's README is about - the per-step gradient
-all-reduce + SGD/momentum update over the ~102 MB arena is ONE fused NVLink kernel (ops/allreduce.py),
-and the classifier Dense layer uses the tcgen05 GEMM under the mixed_bfloat16 policy. Native conv /
-BatchNorm kernels for this topology are not written yet (tracked in DESIGN.md).
+Execution: this model runs on the TorchEngine. Convolutions go through cuDNN (channels_last); BatchNorm, ReLU and
+the residual add are the native streaming kernels of ops/batchnorm.py (half of the eager step time was BatchNorm),
+the classifier Dense layer uses the tcgen05 GEMM under the mixed_bfloat16 policy, and the per-step gradient
+all-reduce + SGD/momentum update over the ~102 MB arena is ONE fused NVLink kernel (ops/allreduce.py).
 """
 from __future__ import annotations
 
@@ -80,16 +79,16 @@ class ResNet50(keras.Model):
     def _forward(self, x: torch.Tensor, ctx: CallContext) -> torch.Tensor:
         if ctx.compute_dtype != torch.float32:
             x = x.to(ctx.compute_dtype)
-        x = self.stem[1].call(self.stem[0].call(x, ctx), ctx)
-        x = self.pool1.call(torch.relu(x), ctx)
+        # BatchNorm + ReLU (+ the bottleneck's residual add) are one fused pass (keras/layers.py:BatchNormalization)
+        x = self.stem[1].call(self.stem[0].call(x, ctx), ctx, relu=True)
+        x = self.pool1.call(x, ctx)
         for _, main, shortcut in self._blocks:
             sc = x
             if shortcut is not None:
                 sc = shortcut[1].call(shortcut[0].call(x, ctx), ctx)
-            y = torch.relu(main[1].call(main[0].call(x, ctx), ctx))
-            y = torch.relu(main[3].call(main[2].call(y, ctx), ctx))
-            y = main[5].call(main[4].call(y, ctx), ctx)
-            x = torch.relu(y + sc)
+            y = main[1].call(main[0].call(x, ctx), ctx, relu=True)
+            y = main[3].call(main[2].call(y, ctx), ctx, relu=True)
+            x = main[5].call(main[4].call(y, ctx), ctx, relu=True, residual=sc)
         return self.fc.call(self.avg.call(x, ctx), ctx).float()
 
 

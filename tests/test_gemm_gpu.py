@@ -209,3 +209,45 @@ def test_native_layernorm_fwd_bwd(H, with_res):
         torch.testing.assert_close(r.grad.float(), rr.grad, rtol=3e-2, atol=3e-3)
     torch.testing.assert_close(g.grad, gr.grad, rtol=2e-2, atol=5e-2)
     torch.testing.assert_close(b.grad, br.grad, rtol=2e-2, atol=5e-2)
+
+
+@pytest.mark.parametrize("C,relu,with_res", [(64, True, False), (256, True, True), (2048, False, False), (8, True, True)])
+def test_native_batchnorm_fwd_bwd(C, relu, with_res):
+    from tfdl.ops.batchnorm import batch_norm_infer, batch_norm_train, supported
+
+    torch.manual_seed(13)
+    x = (torch.randn(6, 7, 9, C, device="cuda") * 1.5 + 0.3).bfloat16().requires_grad_()
+    r = torch.randn(6, 7, 9, C, device="cuda").bfloat16().requires_grad_() if with_res else None
+    g = (torch.randn(C, device="cuda") * 0.2 + 1).requires_grad_()
+    b = (torch.randn(C, device="cuda") * 0.2).requires_grad_()
+    rm, rv = torch.zeros(C, device="cuda"), torch.ones(C, device="cuda")
+    assert supported(x)
+    y = batch_norm_train(x, g, b, rm, rv, 0.01, 1e-3, relu, r)
+    gy = torch.randn_like(y.float()) * 0.1
+    y.float().backward(gy)
+    xr = x.detach().float().requires_grad_()
+    rr = r.detach().float().requires_grad_() if with_res else None
+    gr, br = g.detach().clone().requires_grad_(), b.detach().clone().requires_grad_()
+    rm2, rv2 = torch.zeros(C, device="cuda"), torch.ones(C, device="cuda")
+    yr = torch.nn.functional.batch_norm(xr.permute(0, 3, 1, 2), rm2, rv2, gr, br, True, 0.01, 1e-3).permute(0, 2, 3, 1)
+    if with_res:
+        yr = yr + rr
+    if relu:
+        yr = torch.relu(yr)
+    yr.backward(gy.bfloat16().float())
+    torch.testing.assert_close(y.float(), yr, rtol=2e-2, atol=3e-2)
+    torch.testing.assert_close(rm, rm2, rtol=1e-3, atol=1e-4)
+    torch.testing.assert_close(rv, rv2, rtol=1e-3, atol=1e-4)
+    torch.testing.assert_close(x.grad.float(), xr.grad, rtol=5e-2, atol=5e-3)
+    if with_res:
+        torch.testing.assert_close(r.grad.float(), rr.grad, rtol=5e-2, atol=5e-3)
+    torch.testing.assert_close(g.grad, gr.grad, rtol=3e-2, atol=5e-2)
+    torch.testing.assert_close(b.grad, br.grad, rtol=3e-2, atol=5e-2)
+    yi = batch_norm_infer(x.detach(), g.detach(), b.detach(), rm, rv, 1e-3, relu, r.detach() if with_res else None)
+    yir = torch.nn.functional.batch_norm(x.detach().float().permute(0, 3, 1, 2), rm, rv, g.detach(), b.detach(), False, 0.0,
+                                         1e-3).permute(0, 2, 3, 1)
+    if with_res:
+        yir = yir + r.detach().float()
+    if relu:
+        yir = torch.relu(yir)
+    torch.testing.assert_close(yi.float(), yir, rtol=2e-2, atol=3e-2)
