@@ -84,18 +84,22 @@ bn_stats_kernel(const __nv_bfloat16* __restrict__ x, float* __restrict__ sums, l
 template <bool TRAIN>
 __global__ void __launch_bounds__(BN_THREADS)
 bn_apply_kernel(const __nv_bfloat16* __restrict__ x, const __nv_bfloat16* __restrict__ res, const float* __restrict__ sums,
-                const float* __restrict__ gamma, const float* __restrict__ beta, float* __restrict__ running_mean,
+                const float* __restrict__ in_bias, const float* __restrict__ gamma, const float* __restrict__ beta,
+                float* __restrict__ running_mean,
                 float* __restrict__ running_var, float* __restrict__ mean_out, float* __restrict__ rstd_out,
                 __nv_bfloat16* __restrict__ y, long long M, int C, float eps, float momentum, int relu) {
   __shared__ float sc[BN_MAX_C], sf[BN_MAX_C];
   const float inv_m = 1.f / (float)M;
   for (int c = threadIdx.x; c < C; c += BN_THREADS) {
     float mean, var;
+    // in_bias: a per-channel bias the producer (a convolution) left out. Batch statistics absorb it exactly
+    // (BN(x + b) == BN(x)), so in training it only shifts the running mean; in inference it shifts the input.
+    const float ib = in_bias ? in_bias[c] : 0.f;
     if (TRAIN) {
       mean = sums[c] * inv_m;
       var = fmaxf(sums[C + c] * inv_m - mean * mean, 0.f);
     } else {
-      mean = running_mean[c];
+      mean = running_mean[c] - ib;
       var = running_var[c];
     }
     const float rstd = rsqrtf(var + eps);
@@ -107,7 +111,7 @@ bn_apply_kernel(const __nv_bfloat16* __restrict__ x, const __nv_bfloat16* __rest
       rstd_out[c] = rstd;
       if (running_mean) {
         const float unbiased = M > 1 ? var * ((float)M / (float)(M - 1)) : var;
-        running_mean[c] = (1.f - momentum) * running_mean[c] + momentum * mean;
+        running_mean[c] = (1.f - momentum) * running_mean[c] + momentum * (mean + ib);
         running_var[c] = (1.f - momentum) * running_var[c] + momentum * unbiased;
       }
     }
@@ -260,7 +264,8 @@ static int bn_grid_vec(long long M, int C) {
 }
 
 // sums: 2*C floats of scratch (any contents; cleared here). mean_out / rstd_out [C] are what the backward pass needs.
-extern "C" int tfdl_batchnorm_fwd(const void* x, const void* residual, const float* gamma, const float* beta,
+extern "C" int tfdl_batchnorm_fwd(const void* x, const void* residual, const float* in_bias, const float* gamma,
+                                  const float* beta,
                                   float* running_mean, float* running_var, float* sums, float* mean_out, float* rstd_out,
                                   void* y, long long M, int C, float eps, float momentum, int relu, int training,
                                   void* stream) {
@@ -272,12 +277,12 @@ extern "C" int tfdl_batchnorm_fwd(const void* x, const void* residual, const flo
     TFDL_CUDA_OK(cudaMemsetAsync(sums, 0, sizeof(float) * 2 * C, s));
     bn_stats_kernel<<<bn_grid_rows(M, C), BN_THREADS, 0, s>>>((const __nv_bfloat16*)x, sums, M, C);
     bn_apply_kernel<true><<<bn_grid_vec(M, C), BN_THREADS, 0, s>>>(
-        (const __nv_bfloat16*)x, (const __nv_bfloat16*)residual, sums, gamma, beta, running_mean, running_var, mean_out,
+        (const __nv_bfloat16*)x, (const __nv_bfloat16*)residual, sums, in_bias, gamma, beta, running_mean, running_var, mean_out,
         rstd_out, (__nv_bfloat16*)y, M, C, eps, momentum, relu);
   } else {
     TFDL_REQUIRE(running_mean && running_var, "batchnorm_fwd: inference needs the running statistics");
     bn_apply_kernel<false><<<bn_grid_vec(M, C), BN_THREADS, 0, s>>>(
-        (const __nv_bfloat16*)x, (const __nv_bfloat16*)residual, nullptr, gamma, beta, running_mean, running_var, nullptr,
+        (const __nv_bfloat16*)x, (const __nv_bfloat16*)residual, nullptr, in_bias, gamma, beta, running_mean, running_var, nullptr,
         nullptr, (__nv_bfloat16*)y, M, C, eps, momentum, relu);
   }
   TFDL_CUDA_OK(cudaGetLastError());

@@ -94,10 +94,12 @@ int tfdl_layernorm_bwd(const void* dy, const void* z, const float* mean, const f
  * ResNet-50 config), with the bottleneck's ReLU and residual add fused: y = relu(BN(x) + residual).
  * C/8 must be a power of two, C <= 2048. `sums` is 2*C floats of scratch. Training: batch statistics, mean/rstd [C]
  * saved for the backward pass, running statistics updated in place (momentum = weight of the NEW value, running_var
- * gets the unbiased variance); inference: running statistics. backward: y is read only for the ReLU mask. */
+ * gets the unbiased variance); inference: running statistics. backward: y is read only for the ReLU mask.
+ * in_bias (optional, [C]): a bias the producing convolution skipped - BN(x + b) == BN(x) under batch statistics, so it
+ * only shifts the running mean (training) or the input (inference); its gradient is exactly zero. */
 int tfdl_batchnorm_supported(int C);
-int tfdl_batchnorm_fwd(const void* x, const void* residual, const float* gamma, const float* beta, float* running_mean,
-                       float* running_var, float* sums, float* mean_out, float* rstd_out, void* y, long long M, int C,
+int tfdl_batchnorm_fwd(const void* x, const void* residual, const float* in_bias, const float* gamma, const float* beta,
+                       float* running_mean, float* running_var, float* sums, float* mean_out, float* rstd_out, void* y, long long M, int C,
                        float eps, float momentum, int relu, int training, void* stream);
 int tfdl_batchnorm_bwd(const void* dy, const void* x, const void* y, const float* mean, const float* rstd,
                        const float* gamma, float* sums, void* dx, void* dres, float* dgamma, float* dbeta, long long M,

@@ -240,20 +240,25 @@ class Conv2D(Layer):
             return ((h - kh) // sh + 1, (w - kw) // sw + 1, self.filters)
         return (-(-h // sh), -(-w // sw), self.filters)
 
-    def call(self, x: torch.Tensor, ctx: CallContext) -> torch.Tensor:
+    def call(self, x: torch.Tensor, ctx: CallContext, add_bias: bool = True) -> torch.Tensor:
+        """``add_bias=False``: leave the bias to a following BatchNormalization(in_bias=...), which absorbs it for
+        free (no extra pass over the activations, no bias-gradient reduction)."""
         assert self.kernel is not None
         w = ctx.param(self.kernel).permute(0, 3, 1, 2)  # OHWI storage viewed as OIHW (channels_last strides)
-        b = ctx.param(self.bias) if self.bias is not None else None
+        b = ctx.param(self.bias) if (self.bias is not None and add_bias) else None
         xin = x.permute(0, 3, 1, 2)
+        pad = (0, 0)
         if self.padding == "same":
             pt, pb = self._pads(x.shape[1], self.kernel_size[0], self.strides[0])
             pl, pr = self._pads(x.shape[2], self.kernel_size[1], self.strides[1])
+            pad = (min(pt, pb), min(pl, pr))  # the symmetric part is the convolution's own padding: no copy
+            pt, pb, pl, pr = pt - pad[0], pb - pad[0], pl - pad[1], pr - pad[1]
             if pt or pb or pl or pr:
                 xin = F.pad(xin, (pl, pr, pt, pb))
         if ctx.compute_dtype != torch.float32:
             xin, w = xin.to(ctx.compute_dtype), w.to(ctx.compute_dtype)
             b = b.to(ctx.compute_dtype) if b is not None else None
-        y = F.conv2d(xin, w, b, stride=self.strides).permute(0, 2, 3, 1)
+        y = F.conv2d(xin, w, b, stride=self.strides, padding=pad).permute(0, 2, 3, 1)
         act = _ACTS[self.activation]
         return act(y) if act else y
 
@@ -389,9 +394,10 @@ class BatchNormalization(Layer):
         self.moving_mean = self.add_weight("moving_mean", (c,), "zeros", trainable=False)
         self.moving_variance = self.add_weight("moving_variance", (c,), "ones", trainable=False)
 
-    def call(self, x: torch.Tensor, ctx: CallContext, relu: bool = False,
-             residual: Optional[torch.Tensor] = None) -> torch.Tensor:
-        """y = BN(x); with ``relu`` / ``residual`` the bottleneck tail relu(BN(x) + residual) in the same pass.
+    def call(self, x: torch.Tensor, ctx: CallContext, relu: bool = False, residual: Optional[torch.Tensor] = None,
+             in_bias: Optional[torch.Tensor] = None) -> torch.Tensor:
+        """y = BN(x + in_bias); with ``relu`` / ``residual`` the bottleneck tail relu(BN(x) + residual) in the same
+        pass. ``in_bias``: the bias of the producing Conv2D when it was called with add_bias=False.
         NHWC bf16 CUDA activations run on the native streaming kernels (ops/batchnorm.py)."""
         from ..ops import batchnorm as _bn
 
@@ -401,8 +407,10 @@ class BatchNormalization(Layer):
             if ctx.training:
                 # the kernel writes the running statistics through their arena pointers (no autograd version bump)
                 return _bn.batch_norm_train(x, g, b, mm.detach(), mv.detach(), 1.0 - self.momentum, self.epsilon, relu,
-                                            residual)
-            return _bn.batch_norm_infer(x, g, b, mm, mv, self.epsilon, relu, residual)
+                                            residual, in_bias)
+            return _bn.batch_norm_infer(x, g, b, mm, mv, self.epsilon, relu, residual, in_bias)
+        if in_bias is not None:
+            x = x + in_bias.to(x.dtype)
         y = self._call_torch(x, ctx, g, b, mm, mv)
         if residual is not None:
             y = y + residual

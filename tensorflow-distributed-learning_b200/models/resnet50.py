@@ -79,16 +79,19 @@ class ResNet50(keras.Model):
     def _forward(self, x: torch.Tensor, ctx: CallContext) -> torch.Tensor:
         if ctx.compute_dtype != torch.float32:
             x = x.to(ctx.compute_dtype)
-        # BatchNorm + ReLU (+ the bottleneck's residual add) are one fused pass (keras/layers.py:BatchNormalization)
-        x = self.stem[1].call(self.stem[0].call(x, ctx), ctx, relu=True)
+        # Conv bias, BatchNorm, ReLU and the bottleneck's residual add are ONE fused pass over the activations: the
+        # convolution leaves its bias out and the BatchNorm kernel absorbs it (keras/layers.py:BatchNormalization)
+        def cbn(conv: Layer, bn: Layer, t: torch.Tensor, relu: bool, residual: Optional[torch.Tensor] = None) -> torch.Tensor:
+            bias = ctx.param(conv.bias) if conv.bias is not None else None
+            return bn.call(conv.call(t, ctx, add_bias=False), ctx, relu=relu, residual=residual, in_bias=bias)
+
+        x = cbn(self.stem[0], self.stem[1], x, True)
         x = self.pool1.call(x, ctx)
         for _, main, shortcut in self._blocks:
-            sc = x
-            if shortcut is not None:
-                sc = shortcut[1].call(shortcut[0].call(x, ctx), ctx)
-            y = main[1].call(main[0].call(x, ctx), ctx, relu=True)
-            y = main[3].call(main[2].call(y, ctx), ctx, relu=True)
-            x = main[5].call(main[4].call(y, ctx), ctx, relu=True, residual=sc)
+            sc = x if shortcut is None else cbn(shortcut[0], shortcut[1], x, False)
+            y = cbn(main[0], main[1], x, True)
+            y = cbn(main[2], main[3], y, True)
+            x = cbn(main[4], main[5], y, True, sc)
         return self.fc.call(self.avg.call(x, ctx), ctx).float()
 
 

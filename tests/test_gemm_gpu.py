@@ -222,7 +222,8 @@ def test_native_batchnorm_fwd_bwd(C, relu, with_res):
     b = (torch.randn(C, device="cuda") * 0.2).requires_grad_()
     rm, rv = torch.zeros(C, device="cuda"), torch.ones(C, device="cuda")
     assert supported(x)
-    y = batch_norm_train(x, g, b, rm, rv, 0.01, 1e-3, relu, r)
+    in_bias = torch.randn(C, device="cuda")  # a skipped conv bias: no effect on y, shifts the running mean
+    y = batch_norm_train(x, g, b, rm, rv, 0.01, 1e-3, relu, r, in_bias)
     gy = torch.randn_like(y.float()) * 0.1
     y.float().backward(gy)
     xr = x.detach().float().requires_grad_()
@@ -236,7 +237,8 @@ def test_native_batchnorm_fwd_bwd(C, relu, with_res):
         yr = torch.relu(yr)
     yr.backward(gy.bfloat16().float())
     torch.testing.assert_close(y.float(), yr, rtol=2e-2, atol=3e-2)
-    torch.testing.assert_close(rm, rm2, rtol=1e-3, atol=1e-4)
+    torch.testing.assert_close(rm, rm2 + 0.01 * in_bias, rtol=1e-3, atol=1e-4)
+    rm -= 0.01 * in_bias
     torch.testing.assert_close(rv, rv2, rtol=1e-3, atol=1e-4)
     torch.testing.assert_close(x.grad.float(), xr.grad, rtol=5e-2, atol=5e-3)
     if with_res:
