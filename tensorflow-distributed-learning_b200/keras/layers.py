@@ -13,6 +13,7 @@ native kernel yet). On a B200 the supported stacks are executed by the native st
 from __future__ import annotations
 
 import math
+import os
 from typing import Any, Callable, Dict, List, Optional, Sequence, Tuple, Union
 
 import numpy as np
@@ -244,8 +245,19 @@ class Conv2D(Layer):
         """``add_bias=False``: leave the bias to a following BatchNormalization(in_bias=...), which absorbs it for
         free (no extra pass over the activations, no bias-gradient reduction)."""
         assert self.kernel is not None
-        w = ctx.param(self.kernel).permute(0, 3, 1, 2)  # OHWI storage viewed as OIHW (channels_last strides)
         b = ctx.param(self.bias) if (self.bias is not None and add_bias) else None
+        if (self.kernel_size == (1, 1) and self.strides == (1, 1) and x.is_cuda and ctx.compute_dtype == torch.bfloat16
+                and x.shape[-1] % 8 == 0 and self.filters % 8 == 0 and os.environ.get("TFDL_CONV1X1", "gemm") == "gemm"):
+            # a 1x1 stride-1 convolution over NHWC activations IS a GEMM over [N*H*W, Cin]: forward, dgrad and wgrad
+            # run on the TMA + tcgen05 kernels (OHWI storage of a 1x1 kernel is the [out][in] matrix itself)
+            from ..ops.gemm import linear
+
+            w2 = ctx.param(self.kernel).reshape(self.filters, x.shape[-1])
+            y = linear(x, w2, b, self.activation if self.activation in (None, "relu", "gelu") else None)
+            if self.activation not in (None, "relu", "gelu"):
+                y = _ACTS[self.activation](y)
+            return y
+        w = ctx.param(self.kernel).permute(0, 3, 1, 2)  # OHWI storage viewed as OIHW (channels_last strides)
         xin = x.permute(0, 3, 1, 2)
         pad = (0, 0)
         if self.padding == "same":
