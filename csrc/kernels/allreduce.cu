@@ -241,6 +241,44 @@ __global__ void __launch_bounds__(512) allreduce_sum_kernel(TfdlFusedArParams p)
   finish_step(p, e);
 }
 
+// Broadcast of a symmetric fp32 buffer from `root` (the chief's initial variable values, SURVEY K15 - TF sends them
+// with CollectiveBcastSend/Recv): after a start barrier every other rank copies the root's buffer over NVLink with
+// 16-byte peer loads; the end barrier keeps the root from touching its copy before everyone has read it.
+// Buffers are p.grads[0][*], as for allreduce_sum_kernel.
+__global__ void __launch_bounds__(512) broadcast_kernel(TfdlFusedArParams p, int root) {
+  const uint32_t e = *p.epoch + 1;
+  if (!block_barrier(p, 0, e)) return;
+  if (p.rank != root) {
+    const int64_t n4 = p.n >> 2;
+    const float4* src = reinterpret_cast<const float4*>(p.grads[0][root]);
+    float4* dst = reinterpret_cast<float4*>(p.grads[0][p.rank]);
+    for (int64_t i = (int64_t)blockIdx.x * blockDim.x + threadIdx.x; i < n4; i += (int64_t)gridDim.x * blockDim.x)
+      dst[i] = ld_peer_f4(src + i);
+  }
+  if (!block_barrier(p, p.pad_stride, e)) return;
+  finish_step(p, e);
+}
+
+// Sum of up to 256 doubles across ranks (metric totals, SURVEY K16: sync-on-read variables are SUM-aggregated when
+// read). Each rank's values sit in its own symmetric slot [parity][n]; every rank adds the W slots in rank order, so
+// all ranks get bit-identical totals. Slots alternate by call parity, which makes a second barrier unnecessary.
+__global__ void __launch_bounds__(256) allreduce_f64_kernel(TfdlFusedArParams p, double* __restrict__ out, int n) {
+  const uint32_t e = *p.epoch + 1;
+  const int par = (int)((e - 1) & 1);
+  if (!block_barrier(p, 0, e)) return;
+  for (int i = threadIdx.x; i < n; i += blockDim.x) {
+    double t = 0.0;
+    for (int r = 0; r < p.world; ++r) {
+      const double* slot = reinterpret_cast<const double*>(p.grads[0][r]) + (size_t)par * 256 + i;
+      unsigned long long bits;
+      asm volatile("ld.relaxed.sys.global.u64 %0, [%1];" : "=l"(bits) : "l"(slot) : "memory");
+      t += __longlong_as_double((long long)bits);
+    }
+    out[i] = t;
+  }
+  finish_step(p, e);
+}
+
 // fp32 -> bf16 shadow refresh (after set_weights / checkpoint load) and buffer clear
 __global__ void cast_shadow_kernel(const float* __restrict__ src, __nv_bfloat16* __restrict__ dst, int64_t n) {
   int64_t i = ((int64_t)blockIdx.x * blockDim.x + threadIdx.x) * 4;
@@ -328,5 +366,26 @@ extern "C" int tfdl_enable_peer_access(int device, int peer) {
   if (e == cudaErrorPeerAccessAlreadyEnabled) { cudaGetLastError(); e = cudaSuccess; }
   cudaSetDevice(cur);
   TFDL_CUDA_OK(e);
+  return 0;
+}
+
+extern "C" int tfdl_broadcast_f32(const TfdlFusedArParams* p, int root, void* stream) {
+  TFDL_REQUIRE(p && p->world >= 2 && p->world <= TFDL_MAX_RANKS && root >= 0 && root < p->world,
+               "broadcast_f32: bad world / root");
+  TFDL_REQUIRE(p->n > 0 && p->n % 4 == 0, "broadcast_f32: n must be a positive multiple of 4");
+  const int threads = 512;
+  int grid = pick_grid(p, p->n / 4, threads);
+  broadcast_kernel<<<grid, threads, 0, (cudaStream_t)stream>>>(*p, root);
+  TFDL_CUDA_OK(cudaGetLastError());
+  return 0;
+}
+
+// p->grads[0][r] = rank r's slot buffer of 2 x 256 doubles (the caller writes its n values into slot [*p->epoch & 1]
+// of its own buffer, stream-ordered before this call); out = n doubles of device memory.
+extern "C" int tfdl_allreduce_small_f64(const TfdlFusedArParams* p, double* out, int n, void* stream) {
+  TFDL_REQUIRE(p && p->world >= 2 && p->world <= TFDL_MAX_RANKS && out && n > 0 && n <= 256,
+               "allreduce_small_f64: bad arguments (n = %d, at most 256 values)", n);
+  allreduce_f64_kernel<<<1, 256, 0, (cudaStream_t)stream>>>(*p, out, n);
+  TFDL_CUDA_OK(cudaGetLastError());
   return 0;
 }

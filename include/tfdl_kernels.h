@@ -141,6 +141,11 @@ typedef struct {
 int tfdl_fused_allreduce_sgd(const TfdlFusedArParams* p, int algo, void* stream);
 /* In-place sum of grads[0][*] over ranks (no update); the bandwidth-sweep primitive. */
 int tfdl_allreduce_sum(const TfdlFusedArParams* p, int algo, void* stream);
+/* Copy grads[0][root] into every other rank's grads[0][rank] over NVLink (initial variable broadcast from the chief). */
+int tfdl_broadcast_f32(const TfdlFusedArParams* p, int root, void* stream);
+/* Sum n <= 256 doubles across ranks (metric totals): grads[0][r] = rank r's slot buffer of 2 x 256 doubles, the caller
+ * puts its values into slot [epoch & 1] of its own buffer before the call; every rank receives the same totals. */
+int tfdl_allreduce_small_f64(const TfdlFusedArParams* p, double* out, int n, void* stream);
 int tfdl_cast_f32_to_bf16(const float* src, void* dst_bf16, int64_t n, void* stream);
 int tfdl_enable_peer_access(int device, int peer);
 

@@ -105,7 +105,8 @@ class P2PFusedAllReduce(CrossDeviceOps):
         _lib.kernels()  # fail loudly on a GPU box without the native library
         self._arenas: List[SymmetricBuffer] = []
         self._states: Dict[int, "FusedState"] = {}
-        self._plain: Dict[int, "FusedState"] = {}
+        self._plain: Dict[Any, "FusedState"] = {}
+        self._scalars: Optional[list] = None
 
     # ---- arena allocation hook used by parallel.values.ParamArena -----------------------------
     def alloc_arena(self, numel: int, device: torch.device) -> torch.Tensor:
@@ -138,16 +139,44 @@ class P2PFusedAllReduce(CrossDeviceOps):
         self._plain[key].allreduce_sum()
 
     def allreduce_scalars(self, vals: np.ndarray) -> np.ndarray:
+        """Metric totals (sync-on-read SUM, README.md:67): a one-CTA NVLink kernel adds the ranks' float64 slots in rank
+        order, so every rank reads bit-identical totals. No NCCL call."""
         if self.world == 1:
             return vals
-        t = torch.from_numpy(np.ascontiguousarray(vals, dtype=np.float64).copy()).to(self.device)
-        self.dist.all_reduce(t)  # a few scalars at epoch end, not the gradient path
-        return t.cpu().numpy()
+        v = np.ascontiguousarray(vals, dtype=np.float64).reshape(-1)
+        if v.size > 256:  # not a metric read any more: generic path
+            t = torch.from_numpy(v.copy()).to(self.device)
+            self.dist.all_reduce(t)
+            return t.cpu().numpy().reshape(np.shape(vals))
+        if self._scalars is None:
+            buf = SymmetricBuffer(512, torch.float64, self.device, self.world, self.rank)
+            st = FusedState(self, None, buf, False, plain=True)
+            self._scalars = [buf, st, torch.zeros(256, dtype=torch.float64, device=self.device), 0]
+        buf, st, out, calls = self._scalars
+        par = calls & 1  # == the kernel's epoch parity: this state is used by nothing else
+        self._scalars[3] = calls + 1
+        buf.tensor[par * 256:par * 256 + v.size].copy_(torch.from_numpy(v))
+        _lib.check(_lib.kernels().tfdl_allreduce_small_f64(C.byref(st.struct(0)), _lib.ptr(out), int(v.size),
+                                                           _lib.cur_stream()), "allreduce_small_f64")
+        return out[:v.size].cpu().numpy().reshape(np.shape(vals))
 
     def broadcast_params(self, params: Sequence[torch.Tensor]) -> None:
-        if self.world > 1:
-            self.dist.broadcast(params[0], src=0)
-            torch.cuda.synchronize(self.device)
+        """Initial values from the chief (tf_dist_example.py:56-57): every other rank copies rank 0's arena over NVLink
+        with peer loads (csrc/kernels/allreduce.cu:broadcast_kernel)."""
+        if self.world == 1:
+            return
+        for t in params:
+            try:
+                sym = self._find(t)
+            except RuntimeError:  # not a symmetric arena: library fallback
+                self.dist.broadcast(t, src=0)
+                continue
+            key = ("bcast", t.data_ptr())
+            if key not in self._plain:
+                self._plain[key] = FusedState(self, None, sym, False, plain=True)
+            _lib.check(_lib.kernels().tfdl_broadcast_f32(C.byref(self._plain[key].struct(0)), 0, _lib.cur_stream()),
+                       "broadcast_f32")
+        torch.cuda.synchronize(self.device)
 
     def barrier(self) -> None:
         if self.world > 1:

@@ -83,6 +83,23 @@ def main() -> None:
         torch.testing.assert_close(buf, torch.arange(n, device=dev, dtype=torch.float32) * tot * world, rtol=1e-6, atol=0)
     report["plain_sum"] = "ok"
 
+    # ---- metric totals (float64, bit-identical on every rank) and the chief's broadcast, both on the NVLink kernels ----
+    for rep in range(3):  # three calls: both slot parities
+        vals = np.array([rank + 1.0, 0.1 * (rank + 1) + rep, 1e15 + rank], dtype=np.float64)
+        tot = ops.allreduce_scalars(vals)
+        exp = np.array([sum(r + 1.0 for r in range(world)), sum(0.1 * (r + 1) + rep for r in range(world)),
+                        sum(1e15 + r for r in range(world))])
+        np.testing.assert_allclose(tot, exp, rtol=1e-15)
+        allv = [torch.empty(3, dtype=torch.float64, device=dev) for _ in range(world)]
+        dist.all_gather(allv, torch.from_numpy(tot).to(dev))
+        assert all(torch.equal(allv[0], a) for a in allv)
+    bc = ops.alloc_arena(4096 + 4, dev)
+    bc.copy_(torch.arange(4100, device=dev, dtype=torch.float32) * (rank + 3))
+    torch.cuda.synchronize(dev)
+    ops.broadcast_params([bc])
+    torch.testing.assert_close(bc, torch.arange(4100, device=dev, dtype=torch.float32) * 3, rtol=0, atol=0)
+    report["scalars_and_broadcast"] = "ok"
+
     # ---- training: N GPUs at global batch 64*N == one GPU fed the same global batches -----------------------
     from tfdl.models import build_and_compile_cnn_model
 

@@ -32,7 +32,7 @@ def test_all_visible_gpus():
     n = torch.cuda.device_count()
     rep = _run(n)
     assert rep["world"] == n and rep["train_identical"] == "ok" and rep["train_matches_single_gpu"] == "ok"
-    assert rep["plain_sum"] == "ok"
+    assert rep["plain_sum"] == "ok" and rep.get("scalars_and_broadcast", "ok" if n == 1 else None) == "ok"
     assert all(v == "ok" for k, v in rep.items() if k.startswith("fused_"))
 
 
