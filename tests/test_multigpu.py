@@ -40,3 +40,29 @@ def test_two_gpus_when_more_are_visible():
     if torch.cuda.device_count() <= 2:
         pytest.skip("covered by test_all_visible_gpus")
     assert _run(2)["train_matches_single_gpu"] == "ok"
+
+
+def test_tf_config_workers_one_gpu_each():
+    """The reference's launch form: one process per cluster task with its own TF_CONFIG (README.md:156-162)."""
+    n = min(torch.cuda.device_count(), 2)
+    if n < 2:
+        pytest.skip("needs 2 GPUs")
+    ports = free_ports(2)
+    cluster = {"worker": [f"127.0.0.1:{p}" for p in ports]}
+    procs = []
+    for i in range(n):
+        env = dict(os.environ, TF_CONFIG=json.dumps({"cluster": cluster, "task": {"type": "worker", "index": i}}))
+        for k in ("RANK", "WORLD_SIZE", "LOCAL_RANK", "MASTER_ADDR", "MASTER_PORT"):
+            env.pop(k, None)
+        procs.append(subprocess.Popen([sys.executable, os.path.join(HERE, "tfconfig_gpu_worker.py")], env=env,
+                                      stdout=subprocess.PIPE, stderr=subprocess.STDOUT, text=True))
+    outs = [p.communicate(timeout=600)[0] for p in procs]
+    reps = []
+    for p, o in zip(procs, outs):
+        assert p.returncode == 0, o[-4000:]
+        line = [l for l in o.splitlines() if l.startswith("TFCFG_REPORT ")]
+        assert line, o[-2000:]
+        reps.append(json.loads(line[-1][len("TFCFG_REPORT "):]))
+    assert all(r["replicas"] == n and r["engine"] == "NativeCnnEngine" and r["ops"] == "P2PFusedAllReduce" for r in reps), reps
+    assert reps[0]["wsum"] == reps[1]["wsum"] and reps[0]["wabs"] == reps[1]["wabs"]  # mirrored variables stay identical
+    assert reps[0]["loss"] == reps[1]["loss"]
