@@ -218,3 +218,80 @@ extern "C" int tfdl_layernorm_bwd(const void* dy, const void* z, const float* me
   TFDL_CUDA_OK(cudaGetLastError());
   return 0;
 }
+
+// ---------------------------------------------------------------------------------------------------------
+// Column sums of a bf16 matrix [T, N] into fp32 [N] (bias gradients of Dense layers: db = sum over tokens of dy).
+// One pass at streaming speed: a CTA owns a slab of rows, each thread 8 consecutive columns (16-byte loads, several
+// rows in flight), partial sums stay in registers, one atomic per column per CTA at the end. `out` must be zeroed.
+// ---------------------------------------------------------------------------------------------------------
+namespace tfdl {
+constexpr int CS_THREADS = 256;
+constexpr int CS_MAX_GROUPS = 4;  // column groups of 8 per thread -> N <= 8 * 256 * 4 = 8192
+
+constexpr int CS_UNROLL = 4;
+
+__global__ void __launch_bounds__(CS_THREADS)
+colsum_bf16_kernel(const __nv_bfloat16* __restrict__ x, float* __restrict__ out, long long T, int N, int ld) {
+  extern __shared__ float sh[];  // [N]
+  const int groups = N >> 3;
+  const int gpt = (groups + CS_THREADS - 1) / CS_THREADS;  // column groups per thread (<= CS_MAX_GROUPS)
+  const int tpr = (groups + gpt - 1) / gpt;                // threads per row
+  const int rpb = CS_THREADS / tpr;                        // rows per CTA iteration
+  const int ci = threadIdx.x % tpr, rl = threadIdx.x / tpr;
+  for (int i = threadIdx.x; i < N; i += CS_THREADS) sh[i] = 0.f;
+  __syncthreads();
+  float acc[CS_MAX_GROUPS][8];
+#pragma unroll
+  for (int g = 0; g < CS_MAX_GROUPS; ++g)
+#pragma unroll
+    for (int e = 0; e < 8; ++e) acc[g][e] = 0.f;
+  if (rl < rpb) {
+    const long long stride = (long long)gridDim.x * rpb;
+    for (long long r = (long long)blockIdx.x * rpb + rl; r < T; r += CS_UNROLL * stride) {
+      uint4 v[CS_UNROLL][CS_MAX_GROUPS];
+#pragma unroll
+      for (int u = 0; u < CS_UNROLL; ++u) {
+        const long long rr = r + u * stride;
+#pragma unroll
+        for (int g = 0; g < CS_MAX_GROUPS; ++g) {
+          const int cg = ci + g * tpr;
+          v[u][g] = (rr < T && g < gpt && cg < groups) ? __ldg(reinterpret_cast<const uint4*>(x + rr * ld) + cg)
+                                                       : make_uint4(0, 0, 0, 0);
+        }
+      }
+#pragma unroll
+      for (int u = 0; u < CS_UNROLL; ++u)
+#pragma unroll
+        for (int g = 0; g < CS_MAX_GROUPS; ++g) {
+          float f[8];
+          unpack8(v[u][g], f);
+#pragma unroll
+          for (int e = 0; e < 8; ++e) acc[g][e] += f[e];
+        }
+    }
+#pragma unroll
+    for (int g = 0; g < CS_MAX_GROUPS; ++g) {
+      const int cg = ci + g * tpr;
+      if (g < gpt && cg < groups) {
+#pragma unroll
+        for (int e = 0; e < 8; ++e) atomicAdd(&sh[cg * 8 + e], acc[g][e]);
+      }
+    }
+  }
+  __syncthreads();
+  for (int i = threadIdx.x; i < N; i += CS_THREADS) atomicAdd(out + i, sh[i]);
+}
+}  // namespace tfdl
+
+// out[n] += sum_t x[t][n]; x bf16 [T, N] with row pitch ld (elements, multiple of 8), N % 8 == 0, N <= 8192.
+extern "C" int tfdl_colsum_bf16(const void* x, float* out, long long T, int N, int ld, void* stream) {
+  TFDL_REQUIRE(T > 0 && N > 0 && N % 8 == 0 && N <= 8 * CS_THREADS * CS_MAX_GROUPS && ld % 8 == 0 && ld >= N,
+               "colsum_bf16: unsupported shape [%lld, %d] (pitch %d)", T, N, ld);
+  TFDL_REQUIRE(((uintptr_t)x & 15) == 0, "colsum_bf16: x must be 16-byte aligned");
+  long long blocks = (T + 31) / 32;  // at least a few rows per row-lane, so the atomics stay a small fraction of the work
+  if (blocks > 148 * 2) blocks = 148 * 2;
+  colsum_bf16_kernel<<<(unsigned)blocks, CS_THREADS, (size_t)N * sizeof(float), (cudaStream_t)stream>>>(
+      (const __nv_bfloat16*)x, out, T, N, ld);
+  TFDL_CUDA_OK(cudaGetLastError());
+  return 0;
+}

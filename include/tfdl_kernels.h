@@ -89,6 +89,9 @@ int tfdl_layernorm_fwd(const void* x, const void* residual, const float* gamma, 
                        float* mean, float* rstd, int T, int H, float eps, void* stream);
 int tfdl_layernorm_bwd(const void* dy, const void* z, const float* mean, const float* rstd, const float* gamma, void* dz,
                        float* dgamma, float* dbeta, int T, int H, void* stream);
+/* out[n] += sum_t x[t][n]: bias gradient of a Dense layer. x bf16 [T, N], row pitch ld; N % 8 == 0, N <= 8192; `out`
+ * (fp32 [N]) is accumulated into - zero it first. */
+int tfdl_colsum_bf16(const void* x, float* out, long long T, int N, int ld, void* stream);
 
 /* ---- BatchNorm for NHWC bf16 activations [M = N*H*W rows][C channels] (tf.keras.layers.BatchNormalization of the
  * ResNet-50 config), with the bottleneck's ReLU and residual add fused: y = relu(BN(x) + residual).

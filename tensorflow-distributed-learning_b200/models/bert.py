@@ -85,10 +85,20 @@ class BertMLM(keras.Model):
         x = self.word.call(ids, ctx) + self.pos.call(pos, ctx)[None] + ctx.param(self.typ.embeddings)[0]
         x = self.emb_ln.call(x, ctx).to(dt)
         nh, hd = self.heads, self.hidden // self.heads
+        fuse_qkv = bool(x.is_cuda and dt == torch.bfloat16 and self.hidden % 8 == 0 and (B * S) % 8 == 0)
+        if fuse_qkv:
+            from ..ops.gemm import linear as _tc_linear
         for b in self.blocks:
-            q = b["q"].call(x, ctx).view(B, S, nh, hd).transpose(1, 2)
-            k = b["k"].call(x, ctx).view(B, S, nh, hd).transpose(1, 2)
-            v = b["v"].call(x, ctx).view(B, S, nh, hd).transpose(1, 2)
+            if fuse_qkv:
+                # query / key / value stay three Keras variables (names, checkpoints); for the tensor core they are one
+                # [3H, H] operand: a single N = 3H GEMM fills the machine where three N = H ones leave 1.3 waves each
+                w = torch.cat([ctx.param(b[n].kernel) for n in ("q", "k", "v")], 0)
+                bias = torch.cat([ctx.param(b[n].bias) for n in ("q", "k", "v")], 0)
+                q, k, v = (t.view(B, S, nh, hd).transpose(1, 2) for t in _tc_linear(x, w, bias, None).split(self.hidden, -1))
+            else:
+                q = b["q"].call(x, ctx).view(B, S, nh, hd).transpose(1, 2)
+                k = b["k"].call(x, ctx).view(B, S, nh, hd).transpose(1, 2)
+                v = b["v"].call(x, ctx).view(B, S, nh, hd).transpose(1, 2)
             a = F.scaled_dot_product_attention(q, k, v).transpose(1, 2).reshape(B, S, self.hidden)
             x = b["ln1"].call(b["o"].call(a, ctx), ctx, residual=x).to(dt)
             x = b["ln2"].call(b["ff2"].call(b["ff1"].call(x, ctx), ctx), ctx, residual=x).to(dt)

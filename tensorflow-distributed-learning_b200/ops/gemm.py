@@ -86,6 +86,19 @@ def gemm_tma(a: torch.Tensor, b: torch.Tensor, *, a_mn: bool = False, b_mn: bool
     return out
 
 
+def colsum(x: torch.Tensor) -> torch.Tensor:
+    """fp32 column sums of a bf16 [T, N] matrix (a Dense layer's bias gradient) on the native streaming kernel;
+    falls back to torch for shapes it does not take."""
+    T, N = x.shape
+    if x.is_cuda and x.dtype == torch.bfloat16 and N % 8 == 0 and N <= 8192 and x.stride(1) == 1 and x.stride(0) % 8 == 0 \
+            and x.data_ptr() % 16 == 0:
+        out = torch.zeros(N, device=x.device, dtype=torch.float32)
+        _lib.check(_lib.kernels().tfdl_colsum_bf16(_lib.ptr(x), _lib.ptr(out), ctypes.c_longlong(T), N, x.stride(0),
+                                                   _lib.cur_stream()), "tfdl_colsum_bf16")
+        return out
+    return x.sum(0, dtype=torch.float32)
+
+
 class _LinearFn(torch.autograd.Function):
     """y = act(x W^T + b) with forward, input-gradient and weight-gradient GEMMs all on tcgen05."""
 
@@ -117,7 +130,7 @@ class _LinearFn(torch.autograd.Function):
         dyb = dy2.bfloat16().contiguous()
         dx = gemm_tma(dyb, wb, b_mn=True)                                      # [T,out] x W[out,in] (MN-major)
         dw = gemm_tma(dyb, x2, a_mn=True, b_mn=True, out_dtype=torch.float32)  # dy^T x, both MN-major
-        db = dyb.sum(0, dtype=torch.float32) if ctx.has_bias else None
+        db = colsum(dyb) if ctx.has_bias else None
         return dx.reshape(ctx.x_shape), dw.to(ctx.w_dtype), db, None
 
 
@@ -160,7 +173,7 @@ class _TiedDecoderFn(torch.autograd.Function):
         dyp[:, :V] = dy.reshape(-1, V)
         dh = gemm_tma(dyp, wp, b_mn=True)
         dw = gemm_tma(dyp, h2, a_mn=True, b_mn=True, out_dtype=torch.float32)[:V]
-        db = dyp.sum(0, dtype=torch.float32)[:V] if has_bias else None
+        db = colsum(dyp)[:V] if has_bias else None
         return dh.reshape(h_shape), dw.to(w_dtype), db
 
 

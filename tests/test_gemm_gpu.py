@@ -284,3 +284,14 @@ def test_conv1x1_on_tcgen05_gemm_matches_cudnn_path(monkeypatch):
     for a, b in zip(outs["gemm"], outs["cudnn"]):
         torch.testing.assert_close(a, b, rtol=3e-2, atol=3e-2)
     assert float(outs["gemm"][2].abs().sum()) > 0
+
+
+@pytest.mark.parametrize("T,N", [(8192, 768), (1000, 3072), (77, 8), (4096, 30528)])
+def test_colsum_bias_gradient_kernel(T, N):
+    from tfdl.ops.gemm import colsum
+
+    torch.manual_seed(14)
+    x = (torch.randn(T, N, device="cuda") * 0.5).bfloat16()
+    torch.testing.assert_close(colsum(x), x.float().sum(0), rtol=1e-3, atol=1e-2)
+    if N >= 16:  # a column slice of a wider buffer (row pitch > N)
+        torch.testing.assert_close(colsum(x[:, :N - 8]), x[:, :N - 8].float().sum(0), rtol=1e-3, atol=1e-2)
