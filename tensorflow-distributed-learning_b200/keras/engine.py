@@ -478,6 +478,9 @@ class TorchEngine:
         self.leaves: List[Dict[int, torch.Tensor]] = []
         self._fused = None
         self._fused_lr = None
+        self._graphs: Dict[Any, Any] = {}
+        self._graph_seen: Dict[Any, int] = {}
+        self._graph_off = False
         ops = self.strategy.cross_device_ops
         if (type(ops).__name__ == "P2PFusedAllReduce" and isinstance(model.optimizer, _optimizers.SGD)
                 and len(self.devices) == 1 and os.environ.get("TFDL_TORCH_FUSED_AR", "1") == "1"):
@@ -518,17 +521,86 @@ class TorchEngine:
         return batch, None
 
     def train_step(self, batches: PerReplica) -> None:
-        m, s = self.model, self.strategy
+        m = self.model
         assert m.loss is not None and m.optimizer is not None
-        nrep = s.num_replicas_in_sync
+        if self._graph_eligible():
+            x, y = self._split(batches[0])
+            n = int(np.asarray(x).shape[0]) if not isinstance(x, torch.Tensor) else x.shape[0]
+            if n > 0 and y is not None:
+                dev = self.devices[0]
+                self._train_step_graphed(self._to_device(x, dev), self._to_device(y, dev))
+                return
+        self._sync_hyper()
+        items: List[Optional[Tuple[torch.Tensor, torch.Tensor]]] = []
         for r, dev in enumerate(self.devices):
+            x, y = self._split(batches[r])
+            n = x.shape[0] if isinstance(x, torch.Tensor) else int(np.asarray(x).shape[0])
+            items.append((self._to_device(x, dev), self._to_device(y, dev)) if n else None)
+        self._step_body(items)
+        m.optimizer.step_done()
+
+    # ---- whole-step CUDA graph -------------------------------------------------------------------------------
+    # The eager step of a transformer is several hundred small launches and the host, not the GPU, sets the step
+    # time. For one-replica-per-process CUDA training with SGD the whole step (zero gradients, forward, backward,
+    # metric counters, fused all-reduce + update) is captured once per (shapes, learning rate) and replayed; inputs
+    # are copied into static buffers. The reference gets the same effect from tf.function tracing (README.md:67).
+    def _graph_eligible(self) -> bool:
+        if self._graph_off or len(self.devices) != 1 or self.devices[0].type != "cuda":
+            return False
+        if not isinstance(self.model.optimizer, _optimizers.SGD) or callable(getattr(self.model.optimizer, "_lr", None)):
+            return False
+        return os.environ.get("TFDL_TORCH_GRAPH", "1") == "1"
+
+    def _sync_hyper(self) -> None:
+        if self._fused is not None:
+            opt = self.model.optimizer
+            if self._fused_lr != opt.learning_rate:
+                self._fused_lr = opt.learning_rate
+                self._fused.set_hyper(opt.learning_rate, opt.momentum, opt.nesterov, 1.0)
+
+    def _train_step_graphed(self, xt: torch.Tensor, yt: torch.Tensor) -> None:
+        opt = self.model.optimizer
+        key = (tuple(xt.shape), xt.dtype, tuple(yt.shape), yt.dtype, float(opt.learning_rate), opt.momentum, opt.nesterov)
+        self._sync_hyper()
+        ent = self._graphs.get(key)
+        if ent is None:
+            seen = self._graph_seen.get(key, 0)
+            self._graph_seen[key] = seen + 1
+            if seen < 3:  # warm-up (library handles, autotuning, allocator pools) before anything is captured
+                self._step_body([(xt, yt)])
+                opt.step_done()
+                return
+            try:
+                sx, sy = xt.clone(), yt.clone()
+                torch.cuda.synchronize(self.devices[0])
+                graph = torch.cuda.CUDAGraph()
+                with torch.cuda.graph(graph):
+                    self._step_body([(sx, sy)])
+                ent = self._graphs[key] = (graph, sx, sy)
+            except Exception as e:  # an op that cannot be captured: stay eager for this engine
+                self._graph_off = True
+                torch.cuda.synchronize(self.devices[0])
+                if os.environ.get("TFDL_TORCH_GRAPH_DEBUG"):
+                    print(f"[tfdl] step graph capture failed, running eagerly: {e!r}", file=sys.stderr)
+                self._step_body([(xt, yt)])
+                opt.step_done()
+                return
+        graph, sx, sy = ent
+        sx.copy_(xt, non_blocking=True)
+        sy.copy_(yt, non_blocking=True)
+        graph.replay()
+        opt.step_done()
+
+    def _step_body(self, per_replica: List[Optional[Tuple[torch.Tensor, torch.Tensor]]]) -> None:
+        """Device work of one step: forward / backward per local replica, gradient collective, update."""
+        m, s = self.model, self.strategy
+        nrep = s.num_replicas_in_sync
+        for r, item in enumerate(per_replica):
             arena = m.arenas[r]
             arena.grads.zero_()
-            x, y = self._split(batches[r])
-            n = int(np.asarray(x).shape[0]) if not isinstance(x, torch.Tensor) else x.shape[0]
-            if n == 0:
+            if item is None:
                 continue
-            xt, yt = self._to_device(x, dev), self._to_device(y, dev)
+            xt, yt = item
             ctx = self._ctx(r, True)
             with nvtx_range("tfdl/forward"):
                 pred = m._forward(xt, ctx)
@@ -542,20 +614,14 @@ class TorchEngine:
                 for met in m.compiled_metrics:
                     met.update_state(yt, pred.detach(), r)
         if self._fused is not None:
-            opt = m.optimizer
-            if self._fused_lr != opt.learning_rate:
-                self._fused_lr = opt.learning_rate
-                self._fused.set_hyper(opt.learning_rate, opt.momentum, opt.nesterov, 1.0)
             with nvtx_range("tfdl/allreduce+sgd"):
                 self._fused.step(0, self._fused.torch_algo)
-            m.optimizer.step_done()
             return
         with nvtx_range("tfdl/allreduce"):
             s.cross_device_ops.allreduce_grads([a.grads for a in m.arenas])
         with nvtx_range("tfdl/optimizer"), torch.no_grad():
             for r, arena in enumerate(m.arenas):
                 m.optimizer.apply_flat(arena.params, arena.grads, r, None if m._all_trainable else m._masks[r])
-        m.optimizer.step_done()
 
     def test_step(self, batches: PerReplica) -> None:
         m = self.model
