@@ -93,6 +93,14 @@ int tfdl_layernorm_bwd(const void* dy, const void* z, const float* mean, const f
  * (fp32 [N]) is accumulated into - zero it first. */
 int tfdl_colsum_bf16(const void* x, float* out, long long T, int N, int ld, void* stream);
 
+/* ---- Fused self-attention, S = 128 tokens, head dim 64 (BERT-base at sequence length 128) ----------------------------
+ * qkv: bf16 [B*S][3H] = the fused query|key|value projection (H = heads*64); out: bf16 [B*S][H]; lse2: fp32 [B*heads][S]
+ * saved for the backward pass. backward: dout bf16 [B*S][H] -> dqkv bf16 [B*S][3H]. No mask, softmax scale 1/8. */
+int tfdl_attention_supported(int S, int H, int heads);
+int tfdl_attention_fwd(const void* qkv, void* out, float* lse2, int B, int S, int H, int heads, void* stream);
+int tfdl_attention_bwd(const void* qkv, const void* dout, const float* lse2, void* dqkv, int B, int S, int H, int heads,
+                       void* stream);
+
 /* ---- BatchNorm for NHWC bf16 activations [M = N*H*W rows][C channels] (tf.keras.layers.BatchNormalization of the
  * ResNet-50 config), with the bottleneck's ReLU and residual add fused: y = relu(BN(x) + residual).
  * C/8 must be a power of two, C <= 2048. `sums` is 2*C floats of scratch. Training: batch statistics, mean/rstd [C]

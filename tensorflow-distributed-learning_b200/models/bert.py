@@ -4,14 +4,15 @@ buckets, fused all-reduce + update)"): 12 layers, hidden 768, 12 heads, FFN 3072
 
 Execution: TorchEngine. Every Dense projection (QKV, attention output, FFN, MLM transform - 73 of the
 ~110 M parameters... and all of the GEMM FLOPs except the tied decoder) runs forward, dgrad and wgrad on
-the persistent TMA + tcgen05 GEMM under the mixed_bfloat16 policy (ops/gemm.py:linear); attention itself
-is torch's scaled_dot_product_attention (library flash kernel; at S = 128 a whole sequence fits one tile,
-so no sequence parallelism is needed - SURVEY 5.7); the ~440 MB fp32 gradient arena is reduced by the
+the persistent TMA + tcgen05 GEMM under the mixed_bfloat16 policy (ops/gemm.py:linear); attention is the fused
+tcgen05 kernel of ops/attention.py (at S = 128 a whole sequence fits one tile, so no sequence parallelism is
+needed - SURVEY 5.7; other sequence lengths fall back to torch's scaled_dot_product_attention); the ~440 MB fp32 gradient arena is reduced by the
 fused NVLink kernels. input = token ids [B, S] int, labels = token ids with -100 on unmasked positions.
 """
 from __future__ import annotations
 
 import math
+import os
 from typing import List, Sequence
 
 import torch
@@ -86,15 +87,26 @@ class BertMLM(keras.Model):
         x = self.emb_ln.call(x, ctx).to(dt)
         nh, hd = self.heads, self.hidden // self.heads
         fuse_qkv = bool(x.is_cuda and dt == torch.bfloat16 and self.hidden % 8 == 0 and (B * S) % 8 == 0)
+        native_attn = False
         if fuse_qkv:
+            from ..ops.attention import attention as _attention
             from ..ops.gemm import linear as _tc_linear
+
+            native_attn = S == 128 and hd == 64 and os.environ.get("TFDL_ATTENTION", "native") == "native"
         for b in self.blocks:
             if fuse_qkv:
                 # query / key / value stay three Keras variables (names, checkpoints); for the tensor core they are one
                 # [3H, H] operand: a single N = 3H GEMM fills the machine where three N = H ones leave 1.3 waves each
                 w = torch.cat([ctx.param(b[n].kernel) for n in ("q", "k", "v")], 0)
                 bias = torch.cat([ctx.param(b[n].bias) for n in ("q", "k", "v")], 0)
-                q, k, v = (t.view(B, S, nh, hd).transpose(1, 2) for t in _tc_linear(x, w, bias, None).split(self.hidden, -1))
+                qkv = _tc_linear(x, w, bias, None)
+                if native_attn:
+                    # per-head Q / K / V tiles are cut out of the fused projection by TMA inside the kernel
+                    a = _attention(qkv, nh)
+                    x = b["ln1"].call(b["o"].call(a, ctx), ctx, residual=x).to(dt)
+                    x = b["ln2"].call(b["ff2"].call(b["ff1"].call(x, ctx), ctx), ctx, residual=x).to(dt)
+                    continue
+                q, k, v = (t.view(B, S, nh, hd).transpose(1, 2) for t in qkv.split(self.hidden, -1))
             else:
                 q = b["q"].call(x, ctx).view(B, S, nh, hd).transpose(1, 2)
                 k = b["k"].call(x, ctx).view(B, S, nh, hd).transpose(1, 2)

@@ -295,3 +295,22 @@ def test_colsum_bias_gradient_kernel(T, N):
     torch.testing.assert_close(colsum(x), x.float().sum(0), rtol=1e-3, atol=1e-2)
     if N >= 16:  # a column slice of a wider buffer (row pitch > N)
         torch.testing.assert_close(colsum(x[:, :N - 8]), x[:, :N - 8].float().sum(0), rtol=1e-3, atol=1e-2)
+
+
+@pytest.mark.parametrize("B,heads", [(3, 12), (2, 2)])
+def test_fused_attention_fwd_bwd(B, heads):
+    from tfdl.ops.attention import attention, supported
+
+    torch.manual_seed(15)
+    H = heads * 64
+    qkv = (torch.randn(B, 128, 3 * H, device="cuda") * 0.8).bfloat16().requires_grad_()
+    assert supported(qkv, heads)
+    y = attention(qkv, heads)
+    gy = torch.randn(B, 128, H, device="cuda") * 0.1
+    y.float().backward(gy)
+    ref_in = qkv.detach().float().requires_grad_()
+    q, k, v = (t.view(B, 128, heads, 64).transpose(1, 2) for t in ref_in.split(H, -1))
+    yr = torch.nn.functional.scaled_dot_product_attention(q, k, v).transpose(1, 2).reshape(B, 128, H)
+    yr.backward(gy.bfloat16().float())
+    torch.testing.assert_close(y.float(), yr, rtol=3e-2, atol=2e-2)
+    torch.testing.assert_close(qkv.grad.float(), ref_in.grad, rtol=5e-2, atol=5e-3)
