@@ -101,6 +101,15 @@ int tfdl_attention_fwd(const void* qkv, void* out, float* lse2, int B, int S, in
 int tfdl_attention_bwd(const void* qkv, const void* dout, const float* lse2, void* dqkv, int B, int S, int H, int heads,
                        void* stream);
 
+/* ---- Sparse softmax cross-entropy on bf16 logits [T][ld] (first V columns valid; ld % 8 == 0, ld <= 100 K) --------------
+ * forward: loss fp32 [T] (0 where label == ignore_index) and the softmax probabilities bf16 [T][ld] (pad columns 0);
+ * backward: probs -> dlogits = (p - onehot) * gloss[t], in place. labels are int64. */
+int tfdl_softmax_xent_supported(int V, int ld);
+int tfdl_softmax_xent_fwd(const void* logits, const long long* labels, float* loss, void* probs, long long T, int V, int ld,
+                          long long ignore_index, void* stream);
+int tfdl_softmax_xent_bwd(void* probs_inout, const long long* labels, const float* gloss, long long T, int V, int ld,
+                          long long ignore_index, void* stream);
+
 /* ---- BatchNorm for NHWC bf16 activations [M = N*H*W rows][C channels] (tf.keras.layers.BatchNormalization of the
  * ResNet-50 config), with the bottleneck's ReLU and residual add fused: y = relu(BN(x) + residual).
  * C/8 must be a power of two, C <= 2048. `sums` is 2*C floats of scratch. Training: batch statistics, mean/rstd [C]

@@ -27,6 +27,13 @@ class SparseCategoricalCrossentropy(Loss):
         self.ignore_class = ignore_class
 
     def per_example(self, y_true: torch.Tensor, y_pred: torch.Tensor) -> torch.Tensor:
+        if self.from_logits and y_pred.is_cuda and y_pred.dtype == torch.bfloat16:
+            # bf16 logits on a GPU (wide vocabularies): one fused forward and one in-place backward kernel
+            from ..ops import xent as _xent
+
+            if _xent.supported(y_pred):
+                ig = self.ignore_class if self.ignore_class is not None else -(1 << 62)
+                return _xent.sparse_softmax_xent(y_pred, y_true, ig)
         yp = y_pred.float()
         if yp.dim() > 2:
             yp = yp.reshape(-1, yp.shape[-1])

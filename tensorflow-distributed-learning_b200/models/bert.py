@@ -119,7 +119,8 @@ class BertMLM(keras.Model):
         if dt == torch.bfloat16 and h.is_cuda:
             from ..ops.gemm import tied_decoder
 
-            return tied_decoder(h, w, ctx.param(self.mlm_bias.bias)).float()
+            # bf16 logits (a column slice of the padded GEMM output): the loss kernel reads them as they are
+            return tied_decoder(h, w, ctx.param(self.mlm_bias.bias))
         logits = F.linear(h, w.to(dt)) if dt != torch.float32 else F.linear(h, w)
         return self.mlm_bias.call(logits.float(), ctx)
 

@@ -169,8 +169,16 @@ class _TiedDecoderFn(torch.autograd.Function):
     def backward(ctx, dy):
         h2, wp = ctx.saved_tensors
         V, Vp, h_shape, w_dtype, has_bias = ctx.meta
-        dyp = torch.zeros((h2.shape[0], Vp), device=dy.device, dtype=torch.bfloat16)
-        dyp[:, :V] = dy.reshape(-1, V)
+        T = h2.shape[0]
+        d2 = dy.view(T, V) if dy.dim() == 2 or dy.stride(-1) == 1 and dy.stride(-2) == Vp else None
+        if (Vp != V and d2 is not None and d2.dtype == torch.bfloat16 and d2.stride() == (Vp, 1)
+                and d2.data_ptr() % 16 == 0 and getattr(d2, "_base", None) is not None
+                and d2._base.numel() == T * Vp):
+            # the gradient already IS a column slice of a padded bf16 buffer with zero pad columns (ops/xent.py): use it
+            dyp = torch.as_strided(d2, (T, Vp), (Vp, 1))
+        else:
+            dyp = torch.zeros((T, Vp), device=dy.device, dtype=torch.bfloat16)
+            dyp[:, :V] = dy.reshape(-1, V)
         dh = gemm_tma(dyp, wp, b_mn=True)
         dw = gemm_tma(dyp, h2, a_mn=True, b_mn=True, out_dtype=torch.float32)[:V]
         db = colsum(dyp)[:V] if has_bias else None

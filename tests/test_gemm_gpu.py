@@ -314,3 +314,25 @@ def test_fused_attention_fwd_bwd(B, heads):
     yr.backward(gy.bfloat16().float())
     torch.testing.assert_close(y.float(), yr, rtol=3e-2, atol=2e-2)
     torch.testing.assert_close(qkv.grad.float(), ref_in.grad, rtol=5e-2, atol=5e-3)
+
+
+@pytest.mark.parametrize("T,V,pad", [(300, 1003, True), (64, 512, False), (128, 30522, True)])
+def test_fused_softmax_xent_fwd_bwd(T, V, pad):
+    from tfdl.ops.xent import sparse_softmax_xent, supported
+
+    torch.manual_seed(16)
+    Vp = (V + 7) // 8 * 8 if pad else V
+    buf = torch.full((T, Vp), -30000.0, device="cuda").bfloat16()
+    buf[:, :V] = (torch.randn(T, V, device="cuda") * 3).bfloat16()
+    logits = buf[:, :V].view(2, T // 2, V).detach().requires_grad_()
+    y = torch.randint(0, V, (2, T // 2), device="cuda")
+    y[0, :5] = -100
+    assert supported(logits)
+    loss = sparse_softmax_xent(logits, y, -100)
+    g = torch.rand(T, device="cuda")
+    loss.backward(g)
+    ref_in = buf[:, :V].float().detach().requires_grad_()
+    lr = torch.nn.functional.cross_entropy(ref_in, y.reshape(-1), reduction="none", ignore_index=-100)
+    lr.backward(g)
+    torch.testing.assert_close(loss, lr, rtol=1e-3, atol=1e-3)
+    torch.testing.assert_close(logits.grad.float().reshape(T, V), ref_in.grad, rtol=2e-2, atol=2e-3)
