@@ -228,7 +228,7 @@ namespace tfdl {
 constexpr int CS_THREADS = 256;
 constexpr int CS_MAX_GROUPS = 4;  // column groups of 8 per thread -> N <= 8 * 256 * 4 = 8192
 
-constexpr int CS_UNROLL = 4;
+constexpr int CS_UNROLL = 8;  // rows in flight per row-lane: a CTA keeps 8-16 KB of loads outstanding
 
 __global__ void __launch_bounds__(CS_THREADS)
 colsum_bf16_kernel(const __nv_bfloat16* __restrict__ x, float* __restrict__ out, long long T, int N, int ld) {
@@ -288,8 +288,8 @@ extern "C" int tfdl_colsum_bf16(const void* x, float* out, long long T, int N, i
   TFDL_REQUIRE(T > 0 && N > 0 && N % 8 == 0 && N <= 8 * CS_THREADS * CS_MAX_GROUPS && ld % 8 == 0 && ld >= N,
                "colsum_bf16: unsupported shape [%lld, %d] (pitch %d)", T, N, ld);
   TFDL_REQUIRE(((uintptr_t)x & 15) == 0, "colsum_bf16: x must be 16-byte aligned");
-  long long blocks = (T + 31) / 32;  // at least a few rows per row-lane, so the atomics stay a small fraction of the work
-  if (blocks > 148 * 2) blocks = 148 * 2;
+  long long blocks = (T + 15) / 16;  // at least a few rows per row-lane, so the atomics stay a small fraction of the work
+  if (blocks > 148 * 4) blocks = 148 * 4;
   colsum_bf16_kernel<<<(unsigned)blocks, CS_THREADS, (size_t)N * sizeof(float), (cudaStream_t)stream>>>(
       (const __nv_bfloat16*)x, out, T, N, ld);
   TFDL_CUDA_OK(cudaGetLastError());
