@@ -119,24 +119,32 @@ bn_apply_kernel(const __nv_bfloat16* __restrict__ x, const __nv_bfloat16* __rest
   __syncthreads();
   const int tpr = C >> 3;
   const long long nvec = M * tpr;
-  for (long long i = (long long)blockIdx.x * BN_THREADS + threadIdx.x; i < nvec; i += (long long)gridDim.x * BN_THREADS) {
-    const int cg = (int)(i % tpr);
-    float f[8];
-    bn_unpack8(ld_stream(reinterpret_cast<const uint4*>(x) + i), f);
-    if (res) {
-      float r[8];
-      bn_unpack8(ld_stream(reinterpret_cast<const uint4*>(res) + i), r);
+  // two vectors per thread per trip, all loads issued before the arithmetic; C/8 is a power of two, so the channel
+  // group is a mask, not a 64-bit division
+  const long long stride = (long long)gridDim.x * BN_THREADS;
+  const uint4 zero4 = make_uint4(0, 0, 0, 0);
+  for (long long i = (long long)blockIdx.x * BN_THREADS + threadIdx.x; i < nvec; i += 2 * stride) {
+    const long long i1 = i + stride;
+    const bool two = i1 < nvec;
+    const uint4 x0 = ld_stream(reinterpret_cast<const uint4*>(x) + i);
+    const uint4 x1 = two ? ld_stream(reinterpret_cast<const uint4*>(x) + i1) : zero4;
+    const uint4 r0 = res ? ld_stream(reinterpret_cast<const uint4*>(res) + i) : zero4;
+    const uint4 r1 = (res && two) ? ld_stream(reinterpret_cast<const uint4*>(res) + i1) : zero4;
 #pragma unroll
-      for (int e = 0; e < 8; ++e) f[e] = fmaf(f[e], sc[cg * 8 + e], sf[cg * 8 + e]) + r[e];
-    } else {
+    for (int h = 0; h < 2; ++h) {
+      if (h == 1 && !two) break;
+      const long long ii = h ? i1 : i;
+      const int cg = (int)(ii & (tpr - 1));
+      float f[8], r[8];
+      bn_unpack8(h ? x1 : x0, f);
+      bn_unpack8(h ? r1 : r0, r);
 #pragma unroll
-      for (int e = 0; e < 8; ++e) f[e] = fmaf(f[e], sc[cg * 8 + e], sf[cg * 8 + e]);
+      for (int e = 0; e < 8; ++e) {
+        f[e] = fmaf(f[e], sc[cg * 8 + e], sf[cg * 8 + e]) + r[e];
+        if (relu) f[e] = fmaxf(f[e], 0.f);
+      }
+      reinterpret_cast<uint4*>(y)[ii] = bn_pack8(f);
     }
-    if (relu) {
-#pragma unroll
-      for (int e = 0; e < 8; ++e) f[e] = fmaxf(f[e], 0.f);
-    }
-    reinterpret_cast<uint4*>(y)[i] = bn_pack8(f);
   }
 }
 
@@ -221,22 +229,35 @@ bn_bwd_apply_kernel(const __nv_bfloat16* __restrict__ dy, const __nv_bfloat16* _
   __syncthreads();
   const int tpr = C >> 3;
   const long long nvec = M * tpr;
-  for (long long i = (long long)blockIdx.x * BN_THREADS + threadIdx.x; i < nvec; i += (long long)gridDim.x * BN_THREADS) {
-    const int cg = (int)(i % tpr);
-    float fd[8], fx[8];
-    bn_unpack8(ld_stream(reinterpret_cast<const uint4*>(dy) + i), fd);
-    bn_unpack8(ld_stream(reinterpret_cast<const uint4*>(x) + i), fx);
-    if (relu) {
-      float fy[8];
-      bn_unpack8(ld_stream(reinterpret_cast<const uint4*>(y) + i), fy);
+  const long long stride = (long long)gridDim.x * BN_THREADS;
+  const uint4 zero4 = make_uint4(0, 0, 0, 0);
+  for (long long i = (long long)blockIdx.x * BN_THREADS + threadIdx.x; i < nvec; i += 2 * stride) {
+    const long long i1 = i + stride;
+    const bool two = i1 < nvec;
+    const uint4 d0 = ld_stream(reinterpret_cast<const uint4*>(dy) + i), x0 = ld_stream(reinterpret_cast<const uint4*>(x) + i);
+    const uint4 d1 = two ? ld_stream(reinterpret_cast<const uint4*>(dy) + i1) : zero4;
+    const uint4 x1 = two ? ld_stream(reinterpret_cast<const uint4*>(x) + i1) : zero4;
+    const uint4 y0 = relu ? ld_stream(reinterpret_cast<const uint4*>(y) + i) : zero4;
+    const uint4 y1 = (relu && two) ? ld_stream(reinterpret_cast<const uint4*>(y) + i1) : zero4;
 #pragma unroll
-      for (int e = 0; e < 8; ++e) fd[e] = fy[e] > 0.f ? fd[e] : 0.f;
+    for (int h = 0; h < 2; ++h) {
+      if (h == 1 && !two) break;
+      const long long ii = h ? i1 : i;
+      const int cg = (int)(ii & (tpr - 1));
+      float fd[8], fx[8], fy[8];
+      bn_unpack8(h ? d1 : d0, fd);
+      bn_unpack8(h ? x1 : x0, fx);
+      bn_unpack8(h ? y1 : y0, fy);
+      if (relu) {
+#pragma unroll
+        for (int e = 0; e < 8; ++e) fd[e] = fy[e] > 0.f ? fd[e] : 0.f;
+      }
+      if (dres) reinterpret_cast<uint4*>(dres)[ii] = bn_pack8(fd);
+      float o[8];
+#pragma unroll
+      for (int e = 0; e < 8; ++e) o[e] = fmaf(a[cg * 8 + e], fd[e], fmaf(b[cg * 8 + e], fx[e], c0[cg * 8 + e]));
+      reinterpret_cast<uint4*>(dx)[ii] = bn_pack8(o);
     }
-    if (dres) reinterpret_cast<uint4*>(dres)[i] = bn_pack8(fd);
-    float o[8];
-#pragma unroll
-    for (int e = 0; e < 8; ++e) o[e] = fmaf(a[cg * 8 + e], fd[e], fmaf(b[cg * 8 + e], fx[e], c0[cg * 8 + e]));
-    reinterpret_cast<uint4*>(dx)[i] = bn_pack8(o);
   }
 }
 
