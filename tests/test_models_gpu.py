@@ -43,7 +43,7 @@ def test_bert_small_native_path_tracks_fp32(monkeypatch):
     native, eng = _train(build, batches, "mixed_bfloat16", monkeypatch)
     ref, _ = _train(build, batches, "float32", monkeypatch, {"TFDL_TORCH_GRAPH": "0"})
     assert eng == "TorchEngine" and all(np.isfinite(native))
-    np.testing.assert_allclose(native, ref, rtol=3e-2, atol=3e-2)
+    np.testing.assert_allclose(native, ref, rtol=6e-2, atol=5e-2)
 
 
 def test_resnet50_small_images_native_path_tracks_fp32(monkeypatch):
