@@ -3,7 +3,8 @@
 // reference (tf_dist_example.py:50) in the shape the driver's transformer config needs.
 //
 // The eager formulation costs ~9 passes over a 1 GB fp32 logits tensor (cast, log-softmax, gather, their backward).
-// Here the logits stay bf16: the forward reads a row once into shared memory, reduces max and sum in the CTA, writes
+// Here the logits stay bf16: the forward reads a row once into shared memory, reduces max and sum in the CTA (one exp
+// per logit), writes
 // the loss and the softmax probabilities (bf16, in the same padded layout as the logits); the backward turns the
 // probabilities into dlogits = (p - onehot) * dloss in place. Two read+write passes over 0.5 GB in total.
 #include "common.cuh"
@@ -50,19 +51,8 @@ softmax_xent_fwd_kernel(const __nv_bfloat16* __restrict__ logits, const long lon
   }
   mx = xe_block_reduce(mx, true, red);
   const float L2E = 1.4426950408889634f;
+  // exp once per logit: the unnormalised exponentials replace the logits in shared memory (bf16), the sum is fp32
   float sum = 0.f;
-  for (int i = threadIdx.x; i < nvec; i += XE_THREADS) {
-    const uint4 v = row_s[i];
-    const uint32_t w[4] = {v.x, v.y, v.z, v.w};
-#pragma unroll
-    for (int e = 0; e < 8; ++e) {
-      const float f = __uint_as_float((e & 1) ? (w[e >> 1] & 0xFFFF0000u) : (w[e >> 1] << 16));
-      if (i * 8 + e < V) sum += exp2f((f - mx) * L2E);
-    }
-  }
-  sum = xe_block_reduce(sum, false, red);
-  const float inv = 1.f / sum;
-  uint4* dst = reinterpret_cast<uint4*>(probs + t * ld);
   for (int i = threadIdx.x; i < nvec; i += XE_THREADS) {
     const uint4 v = row_s[i];
     const uint32_t w[4] = {v.x, v.y, v.z, v.w};
@@ -70,15 +60,27 @@ softmax_xent_fwd_kernel(const __nv_bfloat16* __restrict__ logits, const long lon
 #pragma unroll
     for (int e = 0; e < 8; ++e) {
       const float f = __uint_as_float((e & 1) ? (w[e >> 1] & 0xFFFF0000u) : (w[e >> 1] << 16));
-      p[e] = (i * 8 + e < V) ? exp2f((f - mx) * L2E) * inv : 0.f;
+      p[e] = (i * 8 + e < V) ? exp2f((f - mx) * L2E) : 0.f;
+      sum += p[e];
     }
+    row_s[i] = make_uint4(pack_bf16x2(p[0], p[1]), pack_bf16x2(p[2], p[3]), pack_bf16x2(p[4], p[5]), pack_bf16x2(p[6], p[7]));
+  }
+  sum = xe_block_reduce(sum, false, red);
+  const float inv = 1.f / sum;
+  uint4* dst = reinterpret_cast<uint4*>(probs + t * ld);
+  for (int i = threadIdx.x; i < nvec; i += XE_THREADS) {  // each thread re-reads only what it wrote itself
+    const uint4 v = row_s[i];
+    const uint32_t w[4] = {v.x, v.y, v.z, v.w};
+    float p[8];
+#pragma unroll
+    for (int e = 0; e < 8; ++e) p[e] = __uint_as_float((e & 1) ? (w[e >> 1] & 0xFFFF0000u) : (w[e >> 1] << 16)) * inv;
     dst[i] = make_uint4(pack_bf16x2(p[0], p[1]), pack_bf16x2(p[2], p[3]), pack_bf16x2(p[4], p[5]), pack_bf16x2(p[6], p[7]));
   }
   if (threadIdx.x == 0) {
     const long long y = labels[t];
     float l = 0.f;
     if (y != ignore && y >= 0 && y < V) {
-      const float xy = __bfloat162float(reinterpret_cast<const __nv_bfloat16*>(row_s)[y]);
+      const float xy = __bfloat162float(logits[t * ld + y]);  // shared memory holds exponentials by now
       l = (mx - xy) + logf(sum);
     }
     loss[t] = l;
