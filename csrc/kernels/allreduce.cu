@@ -16,6 +16,11 @@
 //              into every rank's arena (reduce-scatter + all-gather by peer stores) (bandwidth-optimal)
 //   multimem   as two-shot, but the slice is reduced inside the NVSwitch with
 //              multimem.ld_reduce and broadcast with multimem.st                    (NVLS)
+//   push       every rank WRITES its gradients into every peer's inbox as 16-byte packets
+//              {value, epoch, value, epoch}; the receiver polls its own memory and the arrival of
+//              the data is the signal - no flag barrier, no peer load: one NVLink one-way trip   (lowest latency)
+//   push2      the same packets in two hops: gradient slices to their owner, updated weight
+//              slices from the owner to everyone (reduce-scatter + all-gather, no barrier)      (mid sizes)
 //
 // Synchronisation protocol (all variants):
 //   * `epoch` is a device-local step counter. Step e (1-based) uses gradient buffer parity
@@ -38,7 +43,7 @@ namespace tfdl {
 
 __device__ __forceinline__ bool spin_until_ge(const uint32_t* flag, uint32_t want, const uint32_t* abort_word) {
   uint32_t spins = 0;
-  while (ld_acquire_sys(flag) < want) {
+  while ((int32_t)(ld_acquire_sys(flag) - want) < 0) {  // wrap-safe: epochs of the ranks of a group differ by at most 1
     if ((++spins & 0x3FF) == 0) {
       if (abort_word && ld_relaxed_sys(abort_word) != 0) return false;
       if (spins > TFDL_SPIN_LIMIT) __trap();
@@ -100,6 +105,21 @@ __device__ __forceinline__ float4 sgd_update(float4 w, float4 g, float4* v, cons
   return w;
 }
 
+// Scalar tail for element counts that are not a multiple of 4 (the vector loops cover [0, n & ~3)).
+__device__ __forceinline__ float ld_peer_f1(const float* p) {
+  float v;
+  asm volatile("ld.relaxed.sys.global.f32 %0, [%1];" : "=f"(v) : "l"(p) : "memory");
+  return v;
+}
+__device__ __forceinline__ void st_peer_f1(float* p, float v) {
+  asm volatile("st.relaxed.sys.global.f32 [%0], %1;" ::"l"(p), "f"(v) : "memory");
+}
+__device__ __forceinline__ float gather_sum1(float* const* bufs, int64_t i, int W, int rank) {
+  float g = 0.f;
+  for (int r = 0; r < W; ++r) g += (r == rank) ? bufs[r][i] : ld_peer_f1(bufs[r] + i);
+  return g;
+}
+
 __device__ __forceinline__ uint2 to_bf16x4(float4 w) {
   return make_uint2(pack_bf16x2(w.x, w.y), pack_bf16x2(w.z, w.w));
 }
@@ -141,13 +161,40 @@ __global__ void __launch_bounds__(512) fused_ar_oneshot_kernel(TfdlFusedArParams
     if (s2) s2[i] = to_bf16x4(w);
     if (z4) z4[i] = make_float4(0.f, 0.f, 0.f, 0.f);
   }
+  if ((p.n & 3) && blockIdx.x == 0 && threadIdx.x == 0) {  // scalar tail (n not a multiple of 4)
+    for (int64_t i = n4 * 4; i < p.n; ++i) {
+      float4 g = make_float4(gather_sum1(p.grads[par], i, W, p.rank) * h.scale, 0.f, 0.f, 0.f);
+      float4 m = p.mom ? make_float4(p.mom[i], 0.f, 0.f, 0.f) : g;
+      float4 w = sgd_update(make_float4(p.params[p.rank][i], 0.f, 0.f, 0.f), g, p.mom ? &m : nullptr, h);
+      if (p.mom) p.mom[i] = m.x;
+      p.params[p.rank][i] = w.x;
+      if (p.shadow[p.rank]) reinterpret_cast<__nv_bfloat16*>(p.shadow[p.rank])[i] = __float2bfloat16(w.x);
+      if (p.grads[par ^ 1][p.rank]) p.grads[par ^ 1][p.rank][i] = 0.f;
+    }
+  }
   finish_step(p, e);
 }
 
 // -------------------------------------------------------------------------------------------
 // two-shot (MC = false) and multimem / NVLS (MC = true)
 // -------------------------------------------------------------------------------------------
-template <bool MC>
+__device__ __forceinline__ float4 mc_ld_reduce_f4(const float4* src) {
+  float4 g;
+  asm volatile("multimem.ld_reduce.relaxed.sys.global.add.v4.f32 {%0, %1, %2, %3}, [%4];"
+               : "=f"(g.x), "=f"(g.y), "=f"(g.z), "=f"(g.w)
+               : "l"(src)
+               : "memory");
+  return g;
+}
+__device__ __forceinline__ void mc_st_f4(float4* dst, float4 w) {
+  asm volatile("multimem.st.relaxed.sys.global.v4.f32 [%0], {%1, %2, %3, %4};" ::"l"(dst), "f"(w.x), "f"(w.y), "f"(w.z),
+               "f"(w.w)
+               : "memory");
+}
+
+// U float4 per thread per trip: the loop is bound by the NVLink round trip, so the bytes in flight per SM set the
+// bandwidth (one float4 per thread was 296 GB/s at W = 2 by Little's law).
+template <bool MC, int U>
 __global__ void __launch_bounds__(512) fused_ar_sliced_kernel(TfdlFusedArParams p) {
   const uint32_t e = *p.epoch + 1;
   const int par = p.parity >= 0 ? p.parity : (int)((e - 1) & 1);
@@ -157,53 +204,224 @@ __global__ void __launch_bounds__(512) fused_ar_sliced_kernel(TfdlFusedArParams 
   const int64_t n4 = p.n >> 2;
   const int64_t per = (n4 + W - 1) / W;
   const int64_t lo = per * p.rank, hi = min(n4, lo + per);
+  const int64_t tid = (int64_t)blockIdx.x * blockDim.x + threadIdx.x, nth = (int64_t)gridDim.x * blockDim.x;
   float4* v4 = reinterpret_cast<float4*>(p.mom);
   const float4* w_own = reinterpret_cast<const float4*>(p.params[p.rank]);
-  for (int64_t i = lo + (int64_t)blockIdx.x * blockDim.x + threadIdx.x; i < hi; i += (int64_t)gridDim.x * blockDim.x) {
-    float4 g;
-    if (MC) {
-      const float4* src = reinterpret_cast<const float4*>(p.mc_grads[par]) + i;
-      asm volatile("multimem.ld_reduce.relaxed.sys.global.add.v4.f32 {%0, %1, %2, %3}, [%4];"
-                   : "=f"(g.x), "=f"(g.y), "=f"(g.z), "=f"(g.w)
-                   : "l"(src)
-                   : "memory");
-    } else {
-      g = gather_sum(p.grads[par], i, W, p.rank);
+  for (int64_t i0 = lo + tid; i0 < hi; i0 += nth * U) {
+    float4 g[U];
+#pragma unroll
+    for (int u = 0; u < U; ++u) {
+      const int64_t i = i0 + u * nth;
+      if (i < hi) g[u] = MC ? mc_ld_reduce_f4(reinterpret_cast<const float4*>(p.mc_grads[par]) + i)
+                            : gather_sum(p.grads[par], i, W, p.rank);
     }
-    g.x *= h.scale; g.y *= h.scale; g.z *= h.scale; g.w *= h.scale;
-    float4 w = sgd_update(w_own[i], g, v4 ? v4 + i : nullptr, h);
-    uint2 s = to_bf16x4(w);
-    if (MC) {
-      float4* dst = reinterpret_cast<float4*>(p.mc_params) + i;
-      asm volatile("multimem.st.relaxed.sys.global.v4.f32 [%0], {%1, %2, %3, %4};" ::"l"(dst), "f"(w.x), "f"(w.y),
-                   "f"(w.z), "f"(w.w)
-                   : "memory");
-      if (p.mc_shadow) {
-        uint2* sd = reinterpret_cast<uint2*>(p.mc_shadow) + i;
-        asm volatile("multimem.st.relaxed.sys.global.v2.f32 [%0], {%1, %2};" ::"l"(sd), "f"(__uint_as_float(s.x)),
-                     "f"(__uint_as_float(s.y))
-                     : "memory");
-      }
-    } else {
-#pragma unroll 1
-      for (int r = 0; r < W; ++r) {
-        float4* dst = reinterpret_cast<float4*>(p.params[r]) + i;
-        if (r == p.rank) *dst = w; else st_peer_f4(dst, w);
-        if (p.shadow[r]) {
-          uint2* sd = reinterpret_cast<uint2*>(p.shadow[r]) + i;
-          if (r == p.rank) *sd = s;
-          else asm volatile("st.relaxed.sys.global.v2.u32 [%0], {%1, %2};" ::"l"(sd), "r"(s.x), "r"(s.y) : "memory");
-        }
+#pragma unroll
+    for (int u = 0; u < U; ++u) {
+      const int64_t i = i0 + u * nth;
+      if (i >= hi) continue;
+      float4 gg = g[u];
+      gg.x *= h.scale; gg.y *= h.scale; gg.z *= h.scale; gg.w *= h.scale;
+      const float4 w = sgd_update(w_own[i], gg, v4 ? v4 + i : nullptr, h);
+      if (MC) {
+        mc_st_f4(reinterpret_cast<float4*>(p.mc_params) + i, w);
+      } else {
+#pragma unroll
+        for (int r = 0; r < TFDL_MAX_RANKS; ++r)
+          if (r < W) {
+            float4* dst = reinterpret_cast<float4*>(p.params[r]) + i;
+            if (r == p.rank) *dst = w; else st_peer_f4(dst, w);
+          }
       }
     }
   }
   // clear the other-parity gradient buffer (whole local arena)
   float4* z4 = reinterpret_cast<float4*>(p.grads[par ^ 1][p.rank]);
   if (z4)
-    for (int64_t i = (int64_t)blockIdx.x * blockDim.x + threadIdx.x; i < n4; i += (int64_t)gridDim.x * blockDim.x)
-      z4[i] = make_float4(0.f, 0.f, 0.f, 0.f);
-  // end barrier: every peer's slice has been written into my arena before this kernel retires
+    for (int64_t i = tid; i < n4; i += nth) z4[i] = make_float4(0.f, 0.f, 0.f, 0.f);
+  // end barrier: block b of every peer has stored its part of every slice into my arena
   if (!block_barrier(p, p.pad_stride, e)) return;
+  // bf16 shadow of the WHOLE arena, cast locally (the weights travel over NVLink once, as fp32; the shadow never
+  // does). Block b converts exactly the elements that the peers' blocks b wrote - the ones its barrier covers.
+  uint2* s2 = reinterpret_cast<uint2*>(p.shadow[p.rank]);
+  if (s2) {
+    for (int r = 0; r < W; ++r) {
+      const int64_t rlo = per * r, rhi = min(n4, rlo + per);
+      for (int64_t i = rlo + tid; i < rhi; i += nth) s2[i] = to_bf16x4(ld_peer_f4(w_own + i));
+    }
+  }
+  finish_step(p, e);
+}
+
+// -------------------------------------------------------------------------------------------
+// push / push2: flag-in-data packets (the data IS the signal)
+// -------------------------------------------------------------------------------------------
+// A packet is 16 bytes {v0, e, v1, e}: two fp32 values, each next to a copy of the step's epoch. NVLink
+// delivers aligned 8-byte units whole, so a receiver that sees `e` in both flag words holds both values of
+// step e; nothing orders packets against each other and nothing has to. A float4 is two packets. Inboxes are
+// double-buffered by epoch parity: a sender can reach step e+2 (same slot) only after its step e+1 completed,
+// which needed this rank's step e+1 packets, which this rank sent after it finished reading step e.
+// Every rank adds the W contributions in rank order (its own from the local arena), so all replicas compute
+// bit-identical weights. Peers' gradient arenas are never read, so the parity double buffer of the gradient
+// arena is not needed for correctness here (it is kept: backward accumulates into a pre-cleared buffer).
+#define TFDL_PUSH_SPIN_LIMIT (1u << 25)
+
+__device__ __forceinline__ void st_packet(uint4* dst, float a, float b, uint32_t e) {
+  asm volatile("st.relaxed.sys.global.v4.u32 [%0], {%1, %2, %3, %4};" ::"l"(dst), "r"(__float_as_uint(a)), "r"(e),
+               "r"(__float_as_uint(b)), "r"(e)
+               : "memory");
+}
+__device__ __forceinline__ uint4 ld_packet(const uint4* src) {
+  uint4 v;
+  asm volatile("ld.relaxed.sys.global.v4.u32 {%0, %1, %2, %3}, [%4];"
+               : "=r"(v.x), "=r"(v.y), "=r"(v.z), "=r"(v.w)
+               : "l"(src)
+               : "memory");
+  return v;
+}
+__device__ __forceinline__ void push_f4(uint4* dst, float4 g, uint32_t e) {
+  st_packet(dst, g.x, g.y, e);
+  st_packet(dst + 1, g.z, g.w, e);
+}
+
+// Sum over ranks of float4 #slot: peers' values from this rank's inbox regions (region r at base + r*stride),
+// this rank's own value `own` in its rank-order position. All 2(W-1) packet loads are in flight together.
+__device__ __forceinline__ bool poll_sum(const uint4* base, int64_t stride, int64_t slot, int W, int rank, uint32_t e,
+                                         float4 own, const uint32_t* abort_word, float4& out) {
+  uint4 a[TFDL_MAX_RANKS], b[TFDL_MAX_RANKS];
+  uint32_t spins = 0;
+  for (;;) {
+#pragma unroll
+    for (int r = 0; r < TFDL_MAX_RANKS; ++r)
+      if (r < W && r != rank) {
+        a[r] = ld_packet(base + r * stride + slot * 2);
+        b[r] = ld_packet(base + r * stride + slot * 2 + 1);
+      }
+    bool ready = true;
+#pragma unroll
+    for (int r = 0; r < TFDL_MAX_RANKS; ++r)
+      if (r < W && r != rank) ready = ready && a[r].y == e && a[r].w == e && b[r].y == e && b[r].w == e;
+    if (ready) break;
+    if ((++spins & 0x3FF) == 0) {
+      if (abort_word && ld_relaxed_sys(abort_word) != 0) return false;
+      if (spins > TFDL_PUSH_SPIN_LIMIT) __trap();
+    }
+  }
+  float4 g = make_float4(0.f, 0.f, 0.f, 0.f);
+#pragma unroll
+  for (int r = 0; r < TFDL_MAX_RANKS; ++r)
+    if (r < W) {
+      if (r == rank) { g.x += own.x; g.y += own.y; g.z += own.z; g.w += own.w; }
+      else {
+        g.x += __uint_as_float(a[r].x); g.y += __uint_as_float(a[r].z);
+        g.z += __uint_as_float(b[r].x); g.w += __uint_as_float(b[r].z);
+      }
+    }
+  out = g;
+  return true;
+}
+__device__ __forceinline__ bool poll_one(const uint4* src, uint32_t e, const uint32_t* abort_word, float4& out) {
+  uint32_t spins = 0;
+  for (;;) {
+    uint4 a = ld_packet(src), b = ld_packet(src + 1);
+    if (a.y == e && a.w == e && b.y == e && b.w == e) {
+      out = make_float4(__uint_as_float(a.x), __uint_as_float(a.z), __uint_as_float(b.x), __uint_as_float(b.z));
+      return true;
+    }
+    if ((++spins & 0x3FF) == 0) {
+      if (abort_word && ld_relaxed_sys(abort_word) != 0) return false;
+      if (spins > TFDL_PUSH_SPIN_LIMIT) __trap();
+    }
+  }
+}
+
+__global__ void __launch_bounds__(256) fused_ar_push_kernel(TfdlFusedArParams p) {
+  pdl_wait();
+  const uint32_t e = *p.epoch + 1;
+  const int par = p.parity >= 0 ? p.parity : (int)((e - 1) & 1);
+  const int ipar = (int)((e - 1) & 1);  // inbox parity always follows the epoch (the gradient parity may be fixed)
+  const TfdlHyper h = *p.hyper;
+  const int W = p.world, rank = p.rank;
+  const int64_t n4 = p.n >> 2;
+  const int64_t region = n4 * 2;  // packets per (parity, source)
+  const float4* g4 = reinterpret_cast<const float4*>(p.grads[par][rank]);
+  const int64_t tid = (int64_t)blockIdx.x * blockDim.x + threadIdx.x, nth = (int64_t)gridDim.x * blockDim.x;
+  // ---- out: my gradients into every peer's inbox ----
+  for (int64_t i = tid; i < n4; i += nth) {
+    const float4 g = g4[i];
+#pragma unroll
+    for (int r = 0; r < TFDL_MAX_RANKS; ++r)
+      if (r < W && r != rank)
+        push_f4(reinterpret_cast<uint4*>(p.inbox[r]) + ((int64_t)ipar * W + rank) * region + i * 2, g, e);
+  }
+  // ---- in: sum in rank order, update ----
+  const uint4* mine = reinterpret_cast<const uint4*>(p.inbox[rank]) + (int64_t)ipar * W * region;
+  float4* w4 = reinterpret_cast<float4*>(p.params[rank]);
+  float4* v4 = reinterpret_cast<float4*>(p.mom);
+  uint2* s2 = reinterpret_cast<uint2*>(p.shadow[rank]);
+  float4* z4 = reinterpret_cast<float4*>(p.grads[par ^ 1][rank]);
+  for (int64_t i = tid; i < n4; i += nth) {
+    float4 g;
+    if (!poll_sum(mine, region, i, W, rank, e, g4[i], p.abort_word, g)) return;
+    g.x *= h.scale; g.y *= h.scale; g.z *= h.scale; g.w *= h.scale;
+    float4 w = sgd_update(w4[i], g, v4 ? v4 + i : nullptr, h);
+    w4[i] = w;
+    if (s2) s2[i] = to_bf16x4(w);
+    if (z4) z4[i] = make_float4(0.f, 0.f, 0.f, 0.f);
+  }
+  finish_step(p, e);
+}
+
+// Two hops. Inbox layout per parity: [hop 0: W source regions][hop 1: W owner regions], each `per` float4 slots.
+__global__ void __launch_bounds__(256) fused_ar_push2_kernel(TfdlFusedArParams p) {
+  pdl_wait();
+  const uint32_t e = *p.epoch + 1;
+  const int par = p.parity >= 0 ? p.parity : (int)((e - 1) & 1);
+  const int ipar = (int)((e - 1) & 1);
+  const TfdlHyper h = *p.hyper;
+  const int W = p.world, rank = p.rank;
+  const int64_t n4 = p.n >> 2;
+  const int64_t per = (n4 + W - 1) / W, region = per * 2;
+  const int64_t lo = per * rank, hi = min(n4, lo + per);
+  const float4* g4 = reinterpret_cast<const float4*>(p.grads[par][rank]);
+  float4* w4 = reinterpret_cast<float4*>(p.params[rank]);
+  float4* v4 = reinterpret_cast<float4*>(p.mom);
+  uint2* s2 = reinterpret_cast<uint2*>(p.shadow[rank]);
+  const int64_t tid = (int64_t)blockIdx.x * blockDim.x + threadIdx.x, nth = (int64_t)gridDim.x * blockDim.x;
+  const int64_t hop0 = ((int64_t)ipar * 2 + 0) * W * region, hop1 = ((int64_t)ipar * 2 + 1) * W * region;
+  // ---- hop 0 out: slice j of my gradients to rank j ----
+  for (int64_t i = tid; i < n4; i += nth) {
+    const int owner = (int)(i / per);
+    if (owner == rank) continue;
+    push_f4(reinterpret_cast<uint4*>(p.inbox[owner]) + hop0 + (int64_t)rank * region + (i - owner * per) * 2, g4[i], e);
+  }
+  // ---- my slice: sum, update, hop 1 out (the new weights) ----
+  const uint4* in0 = reinterpret_cast<const uint4*>(p.inbox[rank]) + hop0;
+  for (int64_t i = lo + tid; i < hi; i += nth) {
+    float4 g;
+    if (!poll_sum(in0, region, i - lo, W, rank, e, g4[i], p.abort_word, g)) return;
+    g.x *= h.scale; g.y *= h.scale; g.z *= h.scale; g.w *= h.scale;
+    float4 w = sgd_update(w4[i], g, v4 ? v4 + i : nullptr, h);
+    w4[i] = w;
+    if (s2) s2[i] = to_bf16x4(w);
+#pragma unroll
+    for (int r = 0; r < TFDL_MAX_RANKS; ++r)
+      if (r < W && r != rank)
+        push_f4(reinterpret_cast<uint4*>(p.inbox[r]) + hop1 + (int64_t)rank * region + (i - lo) * 2, w, e);
+  }
+  // ---- clear the other-parity gradients while the owners work ----
+  float4* z4 = reinterpret_cast<float4*>(p.grads[par ^ 1][rank]);
+  if (z4)
+    for (int64_t i = tid; i < n4; i += nth) z4[i] = make_float4(0.f, 0.f, 0.f, 0.f);
+  // ---- hop 1 in: everybody else's slices ----
+  const uint4* in1 = reinterpret_cast<const uint4*>(p.inbox[rank]) + hop1;
+  for (int64_t i = tid; i < n4; i += nth) {
+    const int owner = (int)(i / per);
+    if (owner == rank) continue;
+    float4 w;
+    if (!poll_one(in1 + (int64_t)owner * region + (i - owner * per) * 2, e, p.abort_word, w)) return;
+    w4[i] = w;
+    if (s2) s2[i] = to_bf16x4(w);
+  }
   finish_step(p, e);
 }
 
@@ -218,23 +436,38 @@ __global__ void __launch_bounds__(512) allreduce_sum_kernel(TfdlFusedArParams p)
   const int64_t n4 = p.n >> 2;
   const int64_t per = (n4 + W - 1) / W;
   const int64_t lo = per * p.rank, hi = min(n4, lo + per);
-  for (int64_t i = lo + (int64_t)blockIdx.x * blockDim.x + threadIdx.x; i < hi; i += (int64_t)gridDim.x * blockDim.x) {
-    float4 g;
-    if (MC) {
-      const float4* src = reinterpret_cast<const float4*>(p.mc_grads[0]) + i;
-      asm volatile("multimem.ld_reduce.relaxed.sys.global.add.v4.f32 {%0, %1, %2, %3}, [%4];"
-                   : "=f"(g.x), "=f"(g.y), "=f"(g.z), "=f"(g.w) : "l"(src) : "memory");
-      float4* dst = reinterpret_cast<float4*>(p.mc_grads[0]) + i;
-      asm volatile("multimem.st.relaxed.sys.global.v4.f32 [%0], {%1, %2, %3, %4};" ::"l"(dst), "f"(g.x), "f"(g.y),
-                   "f"(g.z), "f"(g.w) : "memory");
-    } else {
-      g = gather_sum(p.grads[0], i, W, p.rank);
-      // slice `rank` of every arena is read by this rank alone, so it can be overwritten right away
-#pragma unroll 1
-      for (int r = 0; r < W; ++r) {
-        float4* dst = reinterpret_cast<float4*>(p.grads[0][r]) + i;
-        if (r == p.rank) *dst = g; else st_peer_f4(dst, g);
+  const int64_t tid = (int64_t)blockIdx.x * blockDim.x + threadIdx.x, nth = (int64_t)gridDim.x * blockDim.x;
+  constexpr int U = MC ? 4 : 2;
+  for (int64_t i0 = lo + tid; i0 < hi; i0 += nth * U) {
+    float4 g[U];
+#pragma unroll
+    for (int u = 0; u < U; ++u) {
+      const int64_t i = i0 + u * nth;
+      if (i < hi) g[u] = MC ? mc_ld_reduce_f4(reinterpret_cast<const float4*>(p.mc_grads[0]) + i)
+                            : gather_sum(p.grads[0], i, W, p.rank);
+    }
+#pragma unroll
+    for (int u = 0; u < U; ++u) {
+      const int64_t i = i0 + u * nth;
+      if (i >= hi) continue;
+      if (MC) {
+        mc_st_f4(reinterpret_cast<float4*>(p.mc_grads[0]) + i, g[u]);
+      } else {
+        // slice `rank` of every arena is read by this rank alone, so it can be overwritten right away
+#pragma unroll
+        for (int r = 0; r < TFDL_MAX_RANKS; ++r)
+          if (r < W) {
+            float4* dst = reinterpret_cast<float4*>(p.grads[0][r]) + i;
+            if (r == p.rank) *dst = g[u]; else st_peer_f4(dst, g[u]);
+          }
       }
+    }
+  }
+  if ((p.n & 3) && p.rank == 0 && blockIdx.x == 0 && threadIdx.x == 0) {  // scalar tail, owned by rank 0
+    for (int64_t i = n4 * 4; i < p.n; ++i) {
+      const float g = gather_sum1(p.grads[0], i, W, 0);
+      for (int r = 0; r < W; ++r)
+        if (r == 0) p.grads[0][0][i] = g; else st_peer_f1(p.grads[0][r] + i, g);
     }
   }
   if (!block_barrier(p, p.pad_stride, e)) return;
@@ -254,6 +487,8 @@ __global__ void __launch_bounds__(512) broadcast_kernel(TfdlFusedArParams p, int
     float4* dst = reinterpret_cast<float4*>(p.grads[0][p.rank]);
     for (int64_t i = (int64_t)blockIdx.x * blockDim.x + threadIdx.x; i < n4; i += (int64_t)gridDim.x * blockDim.x)
       dst[i] = ld_peer_f4(src + i);
+    if ((p.n & 3) && blockIdx.x == 0 && threadIdx.x == 0)
+      for (int64_t i = n4 * 4; i < p.n; ++i) p.grads[0][p.rank][i] = ld_peer_f1(p.grads[0][root] + i);
   }
   if (!block_barrier(p, p.pad_stride, e)) return;
   finish_step(p, e);
@@ -302,26 +537,47 @@ static int pick_grid(const TfdlFusedArParams* p, int64_t work4, int threads) {
   return (int)blocks;
 }
 
+// Bytes of inbox every rank must provide for the push paths (peer-mapped, zero-initialised once).
+extern "C" int64_t tfdl_fused_ar_inbox_bytes(int algo, int world, int64_t n) {
+  const int64_t n4 = (n + 3) / 4;
+  if (algo == TFDL_AR_PUSH) return 2 * (int64_t)world * n4 * 32;                                // [parity][source][float4 -> 2 packets]
+  if (algo == TFDL_AR_PUSH2) return 2 * 2 * (int64_t)world * ((n4 + world - 1) / world) * 32;   // [parity][hop][rank][slice]
+  return 0;
+}
+
 extern "C" int tfdl_fused_allreduce_sgd(const TfdlFusedArParams* p, int algo, void* stream) {
   TFDL_REQUIRE(p && p->world >= 1 && p->world <= TFDL_MAX_RANKS, "fused_allreduce_sgd: world %d out of range",
                p ? p->world : -1);
-  TFDL_REQUIRE(p->n > 0 && p->n % 4 == 0, "fused_allreduce_sgd: n=%lld must be a positive multiple of 4",
-               (long long)p->n);
+  TFDL_REQUIRE(p->n > 0, "fused_allreduce_sgd: n=%lld must be positive", (long long)p->n);
+  TFDL_REQUIRE(p->n % 4 == 0 || algo == TFDL_AR_ONESHOT || p->world == 1,
+               "fused_allreduce_sgd: n=%lld is not a multiple of 4: only the one-shot path takes a ragged tail "
+               "(parameter arenas are padded to 16 bytes)", (long long)p->n);
   TFDL_REQUIRE(p->epoch && p->done && p->hyper, "fused_allreduce_sgd: epoch/done/hyper pointers are required");
   TFDL_REQUIRE(p->world == 1 || p->flags[p->rank], "fused_allreduce_sgd: flag pads missing");
   cudaStream_t s = (cudaStream_t)stream;
   const int threads = 256;
-  const int64_t n4 = p->n / 4;
+  const int64_t n4 = (p->n + 3) / 4;
   if (algo == TFDL_AR_ONESHOT || p->world == 1) {
     int grid = pick_grid(p, n4, threads);
     TFDL_CUDA_OK(launch_kernel_pdl(4, fused_ar_oneshot_kernel, dim3(grid), dim3(threads), 0, s, *p));
   } else if (algo == TFDL_AR_TWOSHOT) {
-    int grid = pick_grid(p, (n4 + p->world - 1) / p->world, threads);
-    fused_ar_sliced_kernel<false><<<grid, threads, 0, s>>>(*p);
+    int grid = pick_grid(p, (n4 + p->world - 1) / p->world, 512);
+    fused_ar_sliced_kernel<false, 2><<<grid, 512, 0, s>>>(*p);
   } else if (algo == TFDL_AR_MULTIMEM) {
     TFDL_REQUIRE(p->mc_params && p->mc_grads[0] && p->mc_grads[1], "fused_allreduce_sgd: multicast pointers missing");
-    int grid = pick_grid(p, (n4 + p->world - 1) / p->world, threads);
-    fused_ar_sliced_kernel<true><<<grid, threads, 0, s>>>(*p);
+    int grid = pick_grid(p, (n4 + p->world - 1) / p->world, 512);
+    fused_ar_sliced_kernel<true, 4><<<grid, 512, 0, s>>>(*p);
+  } else if (algo == TFDL_AR_PUSH || algo == TFDL_AR_PUSH2) {
+    TFDL_REQUIRE(p->inbox[p->rank] && p->inbox_bytes >= tfdl_fused_ar_inbox_bytes(algo, p->world, p->n),
+                 "fused_allreduce_sgd: push needs an inbox of %lld bytes per rank (tfdl_fused_ar_inbox_bytes), got %lld",
+                 (long long)tfdl_fused_ar_inbox_bytes(algo, p->world, p->n), (long long)p->inbox_bytes);
+    if (algo == TFDL_AR_PUSH) {
+      int grid = pick_grid(p, n4, threads);
+      TFDL_CUDA_OK(launch_kernel_pdl(4, fused_ar_push_kernel, dim3(grid), dim3(threads), 0, s, *p));
+    } else {
+      int grid = pick_grid(p, n4, threads);  // hop 0 / hop 1-in walk the whole arena
+      TFDL_CUDA_OK(launch_kernel_pdl(4, fused_ar_push2_kernel, dim3(grid), dim3(threads), 0, s, *p));
+    }
   } else {
     TFDL_REQUIRE(false, "fused_allreduce_sgd: unknown algorithm %d", algo);
   }
@@ -332,10 +588,10 @@ extern "C" int tfdl_fused_allreduce_sgd(const TfdlFusedArParams* p, int algo, vo
 extern "C" int tfdl_allreduce_sum(const TfdlFusedArParams* p, int algo, void* stream) {
   TFDL_REQUIRE(p && p->world >= 2 && p->world <= TFDL_MAX_RANKS, "allreduce_sum: world %d out of range",
                p ? p->world : -1);
-  TFDL_REQUIRE(p->n > 0 && p->n % 4 == 0, "allreduce_sum: n must be a positive multiple of 4");
+  TFDL_REQUIRE(p->n > 0, "allreduce_sum: n must be positive");
   cudaStream_t s = (cudaStream_t)stream;
   const int threads = 512;
-  int grid = pick_grid(p, (p->n / 4 + p->world - 1) / p->world, threads);
+  int grid = pick_grid(p, ((p->n + 3) / 4 + p->world - 1) / p->world, threads);
   if (algo == TFDL_AR_MULTIMEM) {
     TFDL_REQUIRE(p->mc_grads[0], "allreduce_sum: multicast pointer missing");
     allreduce_sum_kernel<true><<<grid, threads, 0, s>>>(*p);
@@ -372,9 +628,9 @@ extern "C" int tfdl_enable_peer_access(int device, int peer) {
 extern "C" int tfdl_broadcast_f32(const TfdlFusedArParams* p, int root, void* stream) {
   TFDL_REQUIRE(p && p->world >= 2 && p->world <= TFDL_MAX_RANKS && root >= 0 && root < p->world,
                "broadcast_f32: bad world / root");
-  TFDL_REQUIRE(p->n > 0 && p->n % 4 == 0, "broadcast_f32: n must be a positive multiple of 4");
+  TFDL_REQUIRE(p->n > 0, "broadcast_f32: n must be positive");
   const int threads = 512;
-  int grid = pick_grid(p, p->n / 4, threads);
+  int grid = pick_grid(p, (p->n + 3) / 4, threads);
   broadcast_kernel<<<grid, threads, 0, (cudaStream_t)stream>>>(*p, root);
   TFDL_CUDA_OK(cudaGetLastError());
   return 0;

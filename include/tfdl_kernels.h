@@ -132,7 +132,7 @@ int tfdl_batchnorm_bwd(const void* dy, const void* x, const void* y, const float
  * gradient arenas, 1/N scale, SGD/momentum update of the fp32 master weights, bf16 shadow
  * refresh, clear of the other-parity gradient buffer. See csrc/kernels/allreduce.cu. */
 #define TFDL_MAX_RANKS 8
-enum { TFDL_AR_ONESHOT = 0, TFDL_AR_TWOSHOT = 1, TFDL_AR_MULTIMEM = 2 };
+enum { TFDL_AR_ONESHOT = 0, TFDL_AR_TWOSHOT = 1, TFDL_AR_MULTIMEM = 2, TFDL_AR_PUSH = 3, TFDL_AR_PUSH2 = 4 };
 
 typedef struct {
   float lr, momentum, nesterov, scale; /* read on the device each step: LR schedules need no re-capture */
@@ -156,8 +156,14 @@ typedef struct {
   const TfdlHyper* hyper;               /* device memory */
   const uint32_t* abort_word;           /* host-mapped or device word; non-zero releases every spin */
   int parity;                           /* gradient buffer of this step: 0/1 fixed by the host, -1 = (epoch & 1) */
+  void* inbox[TFDL_MAX_RANKS];          /* push / push2 only: every rank's packet inbox (peer-mapped, zeroed once) */
+  int64_t inbox_bytes;                  /* size of each inbox, >= tfdl_fused_ar_inbox_bytes(algo, world, n) */
 } TfdlFusedArParams;
 
+/* TFDL_AR_PUSH / TFDL_AR_PUSH2 move 16-byte {value, epoch, value, epoch} packets into the peers' inboxes instead of
+ * raising flags and loading from peers: the receiver polls its own memory and needs no barrier (allreduce.cu).
+ * n must be a multiple of 4 except on the one-shot path, which finishes a ragged tail with scalar accesses. */
+int64_t tfdl_fused_ar_inbox_bytes(int algo, int world, int64_t n);
 int tfdl_fused_allreduce_sgd(const TfdlFusedArParams* p, int algo, void* stream);
 /* In-place sum of grads[0][*] over ranks (no update); the bandwidth-sweep primitive. */
 int tfdl_allreduce_sum(const TfdlFusedArParams* p, int algo, void* stream);

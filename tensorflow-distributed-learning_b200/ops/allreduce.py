@@ -11,10 +11,13 @@ Buffers per rank (all symmetric when world > 1):
     shadow   bf16 copy of params            flags                3 barrier pads of MAX_BLOCKS*world u32
 Device-local: epoch / done counters, hyper-parameters {lr, momentum, nesterov, scale}, abort word.
 
-Algorithm choice (`AUTO`): the one-shot kernel moves (W-1)*S bytes per GPU but needs one barrier;
-the sliced kernels move ~2*S*(W-1)/W and need two. With S = arena bytes the crossover measured on
-8xB200 sits near 256 KB*W/(W-1); multimem replaces two-shot whenever the multicast mapping exists.
-Override with TFDL_AR_ALGO=oneshot|twoshot|multimem.
+Algorithm choice (`AUTO`, `pick_algo`): small buckets are PUSHED - every rank writes {value, epoch} packets into
+its peers' inboxes and polls its own, one NVLink one-way trip and no barrier; mid-size buckets take the same
+packets in two hops (slices to their owner, new weights back: push2); large arenas go through the NVSwitch
+(multimem: in-switch reduction, one multicast store of the fp32 weights, bf16 shadow cast locally) or, without a
+multicast mapping, two-shot peer loads/stores. The pull-style one-shot kernel (one barrier, then peer loads)
+remains for ragged element counts and for comparison. Override with
+TFDL_AR_ALGO=oneshot|twoshot|multimem|push|push2; thresholds TFDL_AR_PUSH_MAX / TFDL_AR_PUSH2_MAX (bytes).
 """
 from __future__ import annotations
 
@@ -27,24 +30,32 @@ import torch
 
 from ..parallel.cross_device_ops import CrossDeviceOps
 from . import _lib
-from .structs import AR_MULTIMEM, AR_NAMES, AR_ONESHOT, AR_TWOSHOT, MAX_RANKS, FusedArParams, Hyper
+from .structs import (AR_MULTIMEM, AR_NAMES, AR_ONESHOT, AR_PUSH, AR_PUSH2, AR_TWOSHOT, MAX_RANKS, FusedArParams,
+                      Hyper)
 
 MAX_BLOCKS = 148
-ONESHOT_MAX_BYTES = int(os.environ.get("TFDL_AR_ONESHOT_MAX", 4 * 1024 * 1024))  # measured crossover, 2xB200
+ONESHOT_MAX_BYTES = int(os.environ.get("TFDL_AR_ONESHOT_MAX", 4 * 1024 * 1024))  # pull one-shot vs sliced crossover
+PUSH_MAX_BYTES = int(os.environ.get("TFDL_AR_PUSH_MAX", 2 * 1024 * 1024))        # bytes x (W-1) sent per rank, one hop
+PUSH2_MAX_BYTES = int(os.environ.get("TFDL_AR_PUSH2_MAX", 8 * 1024 * 1024))      # arena bytes, two hops
+_ALGOS = {"oneshot": AR_ONESHOT, "twoshot": AR_TWOSHOT, "multimem": AR_MULTIMEM, "push": AR_PUSH, "push2": AR_PUSH2}
 
 
 def pick_algo(nbytes: int, world: int, has_multicast: bool) -> int:
     """The reference's AUTO: choose by message size, world size and hardware (README.md:21)."""
     forced = os.environ.get("TFDL_AR_ALGO", "").lower()
     if forced:
-        a = {"oneshot": AR_ONESHOT, "twoshot": AR_TWOSHOT, "multimem": AR_MULTIMEM}[forced]
+        a = _ALGOS[forced]
         if a == AR_MULTIMEM and not has_multicast:
             raise RuntimeError("TFDL_AR_ALGO=multimem but the symmetric allocation has no multicast mapping")
-        return a
+        return a if world > 1 else AR_ONESHOT
     if world == 1:
         return AR_ONESHOT
-    if nbytes * (world - 1) <= ONESHOT_MAX_BYTES:
-        return AR_ONESHOT
+    if nbytes % 16:
+        return AR_ONESHOT if nbytes * (world - 1) <= ONESHOT_MAX_BYTES else AR_TWOSHOT  # ragged tail: scalar path
+    if nbytes * (world - 1) <= PUSH_MAX_BYTES:
+        return AR_PUSH
+    if nbytes <= PUSH2_MAX_BYTES:
+        return AR_PUSH2
     return AR_MULTIMEM if has_multicast else AR_TWOSHOT
 
 
@@ -198,7 +209,7 @@ class FusedState:
         self.ops = ops
         dev, W, R = ops.device, ops.world, ops.rank
         n = grads0.numel
-        assert n % 4 == 0
+        assert plain or n % 4 == 0, "parameter arenas are padded to 16 bytes (parallel/values.py)"
         self.n = n
         self.params, self.grads = params, [grads0]
         self.shadow: Optional[SymmetricBuffer] = None
@@ -212,12 +223,16 @@ class FusedState:
         self.hyper = torch.zeros(4, dtype=torch.float32, device=dev)
         self.has_multicast = bool(W > 1 and grads0.multicast_ptr and (plain or (
             params is not None and params.multicast_ptr and self.grads[1].multicast_ptr)))
-        self.algo = pick_algo(n * 4, W, self.has_multicast)
+        self.algo = pick_algo(n * 4, W, self.has_multicast) if not plain else (
+            AR_MULTIMEM if self.has_multicast else AR_TWOSHOT)
         self.offset = 0
         self.max_blocks = MAX_BLOCKS
+        self.inbox: Optional[SymmetricBuffer] = None
         self._structs = [self._make_struct(par) for par in (0, 1)]
         if W > 1:
             grads0.barrier()  # every rank has zeroed its flags before anyone signals
+        if not plain:
+            self.ensure_inbox(self.algo)
 
     def bucket(self, offset: int, length: int, max_blocks: int = MAX_BLOCKS) -> "FusedState":
         """A view of elements [offset, offset+length) of the same buffers with its OWN flag pad, step counter
@@ -234,10 +249,29 @@ class FusedState:
         b.hyper = torch.zeros(4, dtype=torch.float32, device=dev)
         b.has_multicast = self.has_multicast
         b.algo = pick_algo(length * 4, W, b.has_multicast)
+        b.inbox = None
         b._structs = [b._make_struct(par) for par in (0, 1)]
         if W > 1:
             b.flags.barrier()
+        b.ensure_inbox(b.algo)
         return b
+
+    def ensure_inbox(self, algo: int) -> None:
+        """Packet inbox for the push paths (collective: every rank calls it in the same order). Zeroed once - epoch 0
+        is never sent - and never cleared again: stale packets carry an older epoch."""
+        W = self.ops.world
+        if W == 1 or algo not in (AR_PUSH, AR_PUSH2):
+            return
+        lib = _lib.kernels()
+        lib.tfdl_fused_ar_inbox_bytes.restype = C.c_int64
+        lib.tfdl_fused_ar_inbox_bytes.argtypes = [C.c_int, C.c_int, C.c_int64]
+        need = int(lib.tfdl_fused_ar_inbox_bytes(algo, W, self.n))
+        if self.inbox is not None and self.inbox.numel * 4 >= need:
+            return
+        torch.cuda.synchronize(self.ops.device)
+        self.inbox = SymmetricBuffer((need + 3) // 4, torch.int32, self.ops.device, W, self.ops.rank)
+        self.inbox.barrier()  # nobody's first packet can land in memory that is zeroed afterwards
+        self._structs = [self._make_struct(par) for par in (0, 1)]
 
     def _make_struct(self, parity: int) -> FusedArParams:
         p = FusedArParams()
@@ -262,6 +296,10 @@ class FusedState:
                 if self.shadow is not None else None
             for k, g in enumerate(self.grads):
                 p.mc_grads[k] = g.multicast_ptr + o4
+        if self.inbox is not None:
+            for r in range(W):
+                p.inbox[r] = self.inbox.ptrs[r]
+            p.inbox_bytes = self.inbox.numel * 4
         base = self.counters.data_ptr()
         p.epoch, p.done, p.abort_word = base, base + 4, base + 8
         p.hyper = self.hyper.data_ptr()
@@ -282,13 +320,15 @@ class FusedState:
 
     def step(self, parity: int, algo: Optional[int] = None) -> None:
         """One fused all-reduce + update on the current stream (eager; the training path captures it)."""
+        if algo is not None and algo != self.algo:
+            self.ensure_inbox(algo)
         _lib.check(_lib.kernels().tfdl_fused_allreduce_sgd(C.byref(self._structs[parity]),
                                                            self.algo if algo is None else algo, _lib.cur_stream()),
                    "fused_allreduce_sgd")
 
     def allreduce_sum(self, algo: Optional[int] = None) -> None:
         a = self.algo if algo is None else algo
-        if a == AR_ONESHOT:
+        if a not in (AR_MULTIMEM, AR_TWOSHOT):
             a = AR_MULTIMEM if self.has_multicast else AR_TWOSHOT
         _lib.check(_lib.kernels().tfdl_allreduce_sum(C.byref(self._structs[0]), a, _lib.cur_stream()), "allreduce_sum")
 

@@ -4,8 +4,8 @@ from __future__ import annotations
 import ctypes as C
 
 MAX_RANKS = 8
-AR_ONESHOT, AR_TWOSHOT, AR_MULTIMEM = 0, 1, 2
-AR_NAMES = {AR_ONESHOT: "oneshot", AR_TWOSHOT: "twoshot", AR_MULTIMEM: "multimem"}
+AR_ONESHOT, AR_TWOSHOT, AR_MULTIMEM, AR_PUSH, AR_PUSH2 = 0, 1, 2, 3, 4
+AR_NAMES = {AR_ONESHOT: "oneshot", AR_TWOSHOT: "twoshot", AR_MULTIMEM: "multimem", AR_PUSH: "push", AR_PUSH2: "push2"}
 
 
 class Hyper(C.Structure):
@@ -31,6 +31,8 @@ class FusedArParams(C.Structure):
         ("hyper", C.c_void_p),
         ("abort_word", C.c_void_p),
         ("parity", C.c_int),
+        ("inbox", C.c_void_p * MAX_RANKS),
+        ("inbox_bytes", C.c_int64),
     ]
 
 

@@ -13,7 +13,7 @@ sys.path.insert(0, ROOT)
 import tfdl  # noqa: E402
 from tfdl import keras  # noqa: E402
 from tfdl.ops.allreduce import P2PFusedAllReduce  # noqa: E402
-from tfdl.ops.structs import AR_MULTIMEM, AR_NAMES, AR_ONESHOT, AR_TWOSHOT  # noqa: E402
+from tfdl.ops.structs import AR_MULTIMEM, AR_NAMES, AR_ONESHOT, AR_PUSH, AR_PUSH2, AR_TWOSHOT  # noqa: E402
 
 
 def main() -> None:
@@ -30,7 +30,9 @@ def main() -> None:
     for n in (1024, 225280, 4 * 1024 * 1024 + 64):
         params, grads = ops.alloc_arena(n, dev), ops.alloc_arena(n, dev)
         st = ops.fused_state(params, grads, momentum=True)
-        algos = [AR_ONESHOT, AR_TWOSHOT] + ([AR_MULTIMEM] if st.has_multicast else [])
+        algos = [AR_ONESHOT, AR_TWOSHOT, AR_PUSH2] + ([AR_MULTIMEM] if st.has_multicast else [])
+        if n * 4 * (world - 1) <= 32 << 20:
+            algos.append(AR_PUSH)
         report["multicast"] = bool(st.has_multicast)
         for algo in algos:
             torch.manual_seed(1)
@@ -43,7 +45,7 @@ def main() -> None:
             torch.cuda.synchronize(dev)
             dist.barrier()
             w_ref, v_ref = w0.clone(), torch.zeros(n, device=dev)
-            steps = 6
+            steps = 8
             all_g = [[torch.Generator(device="cpu").manual_seed(100 * s + r) for r in range(world)] for s in range(steps)]
             for s in range(steps):
                 par = s & 1
@@ -51,6 +53,13 @@ def main() -> None:
                 if (s + rank) % 2 == 0:
                     torch.cuda._sleep(20_000_000)  # skew the ranks: ~10 ms
                 st.grads[par].tensor.copy_(gs[rank])
+                # step counters that wrap (flag values are compared wrap-safe / for equality): every rank moves its
+                # device epoch forward at the same point of its stream, in two hops of < 2^31 so that each looks
+                # monotonic to the barrier; steps 4..7 then run with epochs 0xFFFFFFFE, 0xFFFFFFFF, 0, 1
+                if s == 2:
+                    st.counters[0:1].fill_(0x7FFFFFF0)
+                if s == 4:
+                    st.counters[0:1].fill_(-3)
                 st.step(par, algo)  # no host sync between steps
                 gsum = gs[0].clone()
                 for r in range(1, world):
@@ -59,7 +68,7 @@ def main() -> None:
                 v_ref = 0.9 * v_ref - 0.1 * gsum
                 w_ref = w_ref + v_ref
             torch.cuda.synchronize(dev)
-            if algo == AR_ONESHOT:
+            if algo in (AR_ONESHOT, AR_PUSH, AR_PUSH2):  # rank-ordered fp32 sums: the host order exactly
                 torch.testing.assert_close(params, w_ref, rtol=1e-5, atol=1e-5)
             else:
                 torch.testing.assert_close(params, w_ref, rtol=1e-4, atol=1e-4)  # in-switch / sliced order differs
@@ -71,7 +80,7 @@ def main() -> None:
             report[f"fused_{AR_NAMES[algo]}_{n}"] = "ok"
 
     # ---- plain in-place sum (odd sizes) --------------------------------------------------------------
-    for n in (4, 1000, 1 << 20):
+    for n in (4, 7, 1001, (1 << 20) + 3):  # element counts that are not multiples of 4: the kernels finish the tail
         buf = ops.alloc_arena(n, dev)
         buf.copy_(torch.arange(n, device=dev, dtype=torch.float32) * (rank + 1))
         torch.cuda.synchronize(dev)
@@ -93,11 +102,11 @@ def main() -> None:
         allv = [torch.empty(3, dtype=torch.float64, device=dev) for _ in range(world)]
         dist.all_gather(allv, torch.from_numpy(tot).to(dev))
         assert all(torch.equal(allv[0], a) for a in allv)
-    bc = ops.alloc_arena(4096 + 4, dev)
-    bc.copy_(torch.arange(4100, device=dev, dtype=torch.float32) * (rank + 3))
+    bc = ops.alloc_arena(4096 + 5, dev)
+    bc.copy_(torch.arange(4101, device=dev, dtype=torch.float32) * (rank + 3))
     torch.cuda.synchronize(dev)
     ops.broadcast_params([bc])
-    torch.testing.assert_close(bc, torch.arange(4100, device=dev, dtype=torch.float32) * 3, rtol=0, atol=0)
+    torch.testing.assert_close(bc, torch.arange(4101, device=dev, dtype=torch.float32) * 3, rtol=0, atol=0)
     report["scalars_and_broadcast"] = "ok"
 
     # ---- training: N GPUs at global batch 64*N == one GPU fed the same global batches -----------------------

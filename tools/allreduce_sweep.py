@@ -23,7 +23,7 @@ ROOT = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
 sys.path.insert(0, ROOT)
 
 import tfdl  # noqa: E402
-from tfdl.ops.structs import AR_MULTIMEM, AR_NAMES, AR_ONESHOT, AR_TWOSHOT  # noqa: E402
+from tfdl.ops.structs import AR_MULTIMEM, AR_NAMES, AR_ONESHOT, AR_PUSH, AR_PUSH2, AR_TWOSHOT  # noqa: E402
 
 
 def timed_graph(fn, stream, iters, reps, dist, dev):
@@ -53,7 +53,8 @@ def main() -> None:
     ap = argparse.ArgumentParser()
     ap.add_argument("--max-mb", type=int, default=1024)
     ap.add_argument("--min-kb", type=int, default=1)
-    ap.add_argument("--algos", default="oneshot,twoshot,multimem")
+    ap.add_argument("--algos", default="oneshot,twoshot,multimem,push,push2")
+    ap.add_argument("--tag", default="")
     ap.add_argument("--no-sum", action="store_true")
     args = ap.parse_args()
     import torch.distributed as dist
@@ -74,7 +75,9 @@ def main() -> None:
         row = {"bytes": size}
         algos = [AR_TWOSHOT] + ([AR_MULTIMEM] if st.has_multicast else [])
         if size * (world - 1) <= (32 << 20):
-            algos = [AR_ONESHOT] + algos
+            algos = [AR_ONESHOT, AR_PUSH] + algos
+        if size <= (64 << 20):
+            algos.append(AR_PUSH2)
         algos = [a for a in algos if AR_NAMES[a] in args.algos.split(",")]
         for algo in algos:
             par = [0]
@@ -89,7 +92,7 @@ def main() -> None:
                 print(f"  size {size} fused {AR_NAMES[algo]} ok {t * 1e6:.2f} us", flush=True)
             row[f"fused_{AR_NAMES[algo]}_us"] = t * 1e6
             row[f"fused_{AR_NAMES[algo]}_busbw"] = size / t * 2 * (world - 1) / world / 1e9
-        for algo in [a for a in algos if a != AR_ONESHOT and not args.no_sum]:
+        for algo in [a for a in algos if a in (AR_TWOSHOT, AR_MULTIMEM) and not args.no_sum]:
             plain = ops._plain.get(grads.data_ptr())
             if plain is None:
                 # one state = one stream: create (and first use) it on the stream that will run it
@@ -119,7 +122,7 @@ def main() -> None:
         size *= 4 if size < (1 << 20) else 2
     if rank == 0:
         os.makedirs(os.path.join(ROOT, "profiles"), exist_ok=True)
-        out = os.path.join(ROOT, "gpurun_out", f"allreduce_sweep_N{world}.json")
+        out = os.path.join(ROOT, "gpurun_out", f"allreduce_sweep_N{world}{args.tag}.json")
         os.makedirs(os.path.dirname(out), exist_ok=True)
         json.dump({"world": world, "rows": rows}, open(out, "w"), indent=1)
         keys = [k for k in rows[-1] if k.endswith("_busbw")]
