@@ -289,6 +289,12 @@ int tfdl_cnn_program_create(const TfdlCnnStep steps[2], const TfdlFusedArParams 
 int tfdl_cnn_program_create2(const TfdlCnnStep steps[2], const TfdlFusedArParams ar[2], int algo,
                              const TfdlFusedArParams ar_early[2], int algo_early, int use_graph, TfdlCnnProgram** out);
 int tfdl_cnn_program_destroy(TfdlCnnProgram* p);
+/* The run entry points launch up to 8 steps per CUDA graph (TFDL_STEPS_PER_GRAPH=1|2|4|8): a graph boundary after
+ * kernels that wrote peer memory costs ~3-4 us. Each step's batch is fetched by a copy kernel on a parallel branch of
+ * the step before it (source pointers come from a device table rewritten before each launch), and the same kernel
+ * writes the previous step's (loss, accuracy) into host_out through mapped pinned memory.
+ * tfdl_cnn_program_prepare captures and uploads every graph variant up front; nothing is executed. */
+int tfdl_cnn_program_prepare(TfdlCnnProgram* p, void* stream);
 /* One step on data already resident in steps[parity].x / .labels. */
 int tfdl_cnn_program_step(TfdlCnnProgram* p, void* stream);
 /* host_batches: n_steps records of (B*H0*W0 floats, B int32) back to back in PINNED memory (record i at
@@ -305,6 +311,12 @@ int tfdl_host_unregister(void* ptr);
 /* As tfdl_cnn_program_run with the records already on the device (one D2D copy + one graph launch per step). */
 int tfdl_cnn_program_run_device(TfdlCnnProgram* p, const void* dev_batches, int64_t n_records, int64_t n_steps,
                                 void* stream);
+/* Step timeline for diagnostics: after this call every step launched or captured drops one-thread marker kernels
+ * between its stages (0 step start, 1 conv forward done, 2 dense block done, 3 conv2 wgrad done, 4 conv backward done,
+ * 5 early-bucket all-reduce done, 6 last all-reduce done). Marker id stores %globaltimer (ns) into
+ * buf[id*TFDL_TRACE_CAP + k % TFDL_TRACE_CAP], k = counters[id]++ (device memory, 8 ids). NULL switches it off. */
+#define TFDL_TRACE_CAP 256
+int tfdl_trace_enable(unsigned long long* buf, unsigned* counters);
 int64_t tfdl_cnn_program_steps_done(const TfdlCnnProgram* p);
 int64_t tfdl_cnn_program_launches_per_step(const TfdlCnnProgram* p);
 

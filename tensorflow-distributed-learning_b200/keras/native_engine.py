@@ -246,6 +246,10 @@ class NativeCnnEngine:
         for g in self.state.grads:
             g.tensor.zero_()
         torch.cuda.synchronize(dev)
+        # every graph variant (1/2/4/8 steps x parity) is captured now, not inside the first fit()
+        self.lib.tfdl_cnn_program_prepare.argtypes = [C.c_void_p, C.c_void_p]
+        _lib.check(self.lib.tfdl_cnn_program_prepare(self._prog, self.stream.cuda_stream), "cnn_program_prepare")
+        torch.cuda.synchronize(dev)
 
     # ------------------------------------------------------------------------------------------
     def pack_record(self, slot: int, x: np.ndarray, y: np.ndarray) -> None:

@@ -45,7 +45,7 @@ def main() -> None:
             torch.cuda.synchronize(dev)
             dist.barrier()
             w_ref, v_ref = w0.clone(), torch.zeros(n, device=dev)
-            steps = 8
+            steps = 9
             all_g = [[torch.Generator(device="cpu").manual_seed(100 * s + r) for r in range(world)] for s in range(steps)]
             for s in range(steps):
                 par = s & 1
@@ -54,11 +54,13 @@ def main() -> None:
                     torch.cuda._sleep(20_000_000)  # skew the ranks: ~10 ms
                 st.grads[par].tensor.copy_(gs[rank])
                 # step counters that wrap (flag values are compared wrap-safe / for equality): every rank moves its
-                # device epoch forward at the same point of its stream, in two hops of < 2^31 so that each looks
-                # monotonic to the barrier; steps 4..7 then run with epochs 0xFFFFFFFE, 0xFFFFFFFF, 0, 1
-                if s == 2:
-                    st.counters[0:1].fill_(0x7FFFFFF0)
-                if s == 4:
+                # device epoch forward at the same point of its stream, in three hops of < 2^31 so that each looks
+                # monotonic to the barrier; steps 5..8 then run with epochs 0xFFFFFFFE, 0xFFFFFFFF, 0, 1
+                if s == 1:
+                    st.counters[0:1].fill_(0x50000000)
+                if s == 3:
+                    st.counters[0:1].fill_(-0x60000000)  # 0xA0000000
+                if s == 5:
                     st.counters[0:1].fill_(-3)
                 st.step(par, algo)  # no host sync between steps
                 gsum = gs[0].clone()
