@@ -6,6 +6,9 @@
 // into a (pinned) staging buffer, optionally fusing the uint8 -> float32 /255 scale of
 // tf_dist_example.py:22-25.
 #include <algorithm>
+#include <condition_variable>
+#include <functional>
+#include <mutex>
 #include <thread>
 #include "rt_common.h"
 #include "../../include/tfdl_runtime.h"
@@ -117,20 +120,109 @@ extern "C" int tfdl_rt_shuffle_indices(const int64_t* src, int64_t n, int64_t bu
   return 0;
 }
 
+// A small persistent worker pool: the input pipeline calls into here once per chunk of steps (every ~0.8 ms of
+// device time for the reference CNN), and creating + joining threads per call costs more than the copy they do.
+namespace {
+class Pool {
+ public:
+  explicit Pool(int n) {
+    for (int i = 0; i < n; ++i) workers_.emplace_back([this] { loop(); });
+  }
+  ~Pool() {
+    {
+      std::lock_guard<std::mutex> g(mu_);
+      stop_ = true;
+    }
+    cv_.notify_all();
+    for (auto& t : workers_) t.join();
+  }
+  int size() const { return (int)workers_.size(); }
+  // runs fn(part) for part in [0, parts) on the workers + the calling thread; returns when all are done
+  void run(int parts, const std::function<void(int)>& fn) {
+    if (parts <= 1) {
+      if (parts == 1) fn(0);
+      return;
+    }
+    std::unique_lock<std::mutex> g(mu_);
+    fn_ = &fn;
+    next_ = 0;
+    parts_ = parts;
+    pending_ = parts;
+    ++gen_;
+    g.unlock();
+    cv_.notify_all();
+    work();
+    g.lock();
+    done_cv_.wait(g, [this] { return pending_ == 0; });
+    fn_ = nullptr;
+  }
+
+ private:
+  void work() {
+    for (;;) {
+      int part;
+      const std::function<void(int)>* f;
+      {
+        std::lock_guard<std::mutex> g(mu_);
+        if (!fn_ || next_ >= parts_) return;
+        part = next_++;
+        f = fn_;
+      }
+      (*f)(part);
+      std::lock_guard<std::mutex> g(mu_);
+      if (--pending_ == 0) done_cv_.notify_all();
+    }
+  }
+  void loop() {
+    uint64_t seen = 0;
+    for (;;) {
+      {
+        std::unique_lock<std::mutex> g(mu_);
+        cv_.wait(g, [&] { return stop_ || gen_ != seen; });
+        if (stop_) return;
+        seen = gen_;
+      }
+      work();
+    }
+  }
+  std::vector<std::thread> workers_;
+  std::mutex mu_;
+  std::condition_variable cv_, done_cv_;
+  const std::function<void(int)>* fn_ = nullptr;
+  int next_ = 0, parts_ = 0, pending_ = 0;
+  uint64_t gen_ = 0;
+  bool stop_ = false;
+};
+Pool& pool() {
+  static Pool* p = new Pool(std::max(1, std::min(7, (int)std::thread::hardware_concurrency() - 1)));  // leaked on purpose: no static-destruction order games at exit
+  return *p;
+}
+std::mutex g_pool_mu;  // one parallel region at a time (callers are the per-process input pipeline)
+}  // namespace
+
+template <class F>
+static void parallel_ranges(int64_t n, int parts, F fn) {
+  if (parts <= 1 || n <= 1) {
+    fn(0, n);
+    return;
+  }
+  parts = (int)std::min<int64_t>(parts, n);
+  const int64_t per = (n + parts - 1) / parts;
+  std::lock_guard<std::mutex> g(g_pool_mu);
+  std::function<void(int)> job = [&](int t) {
+    const int64_t lo = t * per, hi = std::min(n, lo + per);
+    if (lo < hi) fn(lo, hi);
+  };
+  pool().run(parts, job);
+}
+
 template <class F>
 static void parallel_rows(int64_t n, int threads, F fn) {
   if (threads <= 1 || n < 256) {
     fn(0, n);
     return;
   }
-  std::vector<std::thread> ts;
-  int64_t per = (n + threads - 1) / threads;
-  for (int t = 0; t < threads; ++t) {
-    int64_t lo = t * per, hi = std::min(n, lo + per);
-    if (lo >= hi) break;
-    ts.emplace_back([=] { fn(lo, hi); });
-  }
-  for (auto& t : ts) t.join();
+  parallel_ranges(n, threads, fn);
 }
 
 // dst[i, :] = src[idx[i], :]  (row_bytes each)
@@ -193,16 +285,92 @@ extern "C" int tfdl_rt_pack_records(const void* const* xs, const void* const* ys
   };
   // records are large (hundreds of KB): split across threads as soon as there is ~1 MB to move
   const int64_t nt = std::min<int64_t>(std::min<int64_t>(threads, k), (k * x_bytes) >> 19);
-  if (nt <= 1) {
-    work(0, k);
-  } else {
-    std::vector<std::thread> ts;
-    const int64_t per = (k + nt - 1) / nt;
-    for (int64_t t = 0; t < nt; ++t) {
-      const int64_t lo = t * per, hi = std::min(k, lo + per);
-      if (lo < hi) ts.emplace_back([=] { work(lo, hi); });
-    }
-    for (auto& t : ts) t.join();
-  }
+  parallel_ranges(k, (int)nt, work);
   return 0;
 }
+
+// Builds k records straight from the (cached) dataset arrays: record r = [x[idx[r*B + b]] for b < B | labels as int32].
+// This is `.shuffle(...).batch(...)` of tf_dist_example.py:31-33 done as ONE gather into the executor's pinned ring -
+// no per-batch arrays, no second staging copy (shuffle / batch / rebatch kernels).
+extern "C" int tfdl_rt_gather_records(const void* x_src, int64_t num_rows, int64_t x_row_bytes, const void* y_src,
+                                      int label_bytes, const int64_t* idx, int64_t k, int64_t B, void* ring,
+                                      int64_t rec_bytes, int threads) {
+  if (!x_src || !y_src || !idx || !ring || k < 0 || B < 1 || (label_bytes != 1 && label_bytes != 4 && label_bytes != 8) ||
+      rec_bytes < B * x_row_bytes + B * 4) {
+    set_error("gather_records: bad arguments (k=%lld B=%lld row=%lld label_bytes=%d rec=%lld)", (long long)k, (long long)B,
+              (long long)x_row_bytes, label_bytes, (long long)rec_bytes);
+    return -1;
+  }
+  for (int64_t i = 0; i < k * B; ++i)
+    if (idx[i] < 0 || idx[i] >= num_rows) {
+      set_error("gather_records: index %lld out of range [0,%lld)", (long long)idx[i], (long long)num_rows);
+      return -1;
+    }
+  const char* xs = static_cast<const char*>(x_src);
+  auto work = [=](int64_t lo, int64_t hi) {
+    for (int64_t r = lo; r < hi; ++r) {
+      char* rec = static_cast<char*>(ring) + r * rec_bytes;
+      int32_t* yl = reinterpret_cast<int32_t*>(rec + B * x_row_bytes);
+      for (int64_t b = 0; b < B; ++b) {
+        const int64_t j = idx[r * B + b];
+        std::memcpy(rec + b * x_row_bytes, xs + j * x_row_bytes, (size_t)x_row_bytes);
+        yl[b] = label_bytes == 8 ? (int32_t) static_cast<const int64_t*>(y_src)[j]
+                : label_bytes == 4 ? static_cast<const int32_t*>(y_src)[j]
+                                   : (int32_t) static_cast<const uint8_t*>(y_src)[j];
+      }
+    }
+  };
+  const int64_t nt = std::min<int64_t>(std::min<int64_t>(threads, k), (k * B * x_row_bytes) >> 18);
+  parallel_ranges(k, (int)nt, work);
+  return 0;
+}
+
+// Streaming form of the shuffle buffer: the same algorithm as tfdl_rt_shuffle_indices, producing its output on
+// demand. A fit() of 20 steps draws 1,280 of MNIST's 60,000 elements; shuffling all of them up front cost more than
+// the 20 steps themselves.
+namespace {
+struct Shuffler {
+  std::vector<int64_t> src, buf;  // src empty = the identity stream 0..n-1 (a cached / in-memory dataset)
+  int64_t n = 0, t = 0, drained = 0;  // next source element to feed the buffer; elements already drained at the end
+  int64_t buffer = 0;
+  bool tail_shuffled = false;
+  Rng rng;
+  Shuffler(const int64_t* s, int64_t n_, int64_t b, uint64_t seed) : n(n_), buffer(std::min(b, n_)), rng(seed) {
+    if (s) src.assign(s, s + n);
+    buf.resize(buffer);
+    for (int64_t i = 0; i < buffer; ++i) buf[i] = s ? s[i] : i;
+    t = buffer;
+  }
+  int64_t at(int64_t i) const { return src.empty() ? i : src[i]; }
+  // multiply-shift range reduction: one 64x64->128 multiply instead of two 64-bit divisions per draw
+  uint64_t below(uint64_t m) { return (uint64_t)(((unsigned __int128)rng.next() * m) >> 64); }
+};
+}  // namespace
+
+extern "C" void* tfdl_rt_shuffler_create(const int64_t* src, int64_t n, int64_t buffer, uint64_t seed) {
+  if (n < 0 || buffer < 1) {  // src == NULL: the source stream is 0..n-1
+    set_error("shuffler_create: bad arguments n=%lld buffer=%lld", (long long)n, (long long)buffer);
+    return nullptr;
+  }
+  return new Shuffler(src, n, buffer, seed);
+}
+// Writes up to `max` further indices to `out`; returns how many (0 = exhausted).
+extern "C" int64_t tfdl_rt_shuffler_next(void* h, int64_t* out, int64_t max) {
+  auto* s = static_cast<Shuffler*>(h);
+  const int64_t n = s->n;
+  int64_t o = 0;
+  while (o < max && s->t < n) {
+    const uint64_t j = s->below((uint64_t)s->buffer);
+    out[o++] = s->buf[j];
+    s->buf[j] = s->at(s->t++);
+  }
+  if (o < max && s->t >= n) {
+    if (!s->tail_shuffled) {
+      for (int64_t i = s->buffer - 1; i > 0; --i) std::swap(s->buf[i], s->buf[s->below((uint64_t)i + 1)]);
+      s->tail_shuffled = true;
+    }
+    while (o < max && s->drained < s->buffer) out[o++] = s->buf[s->drained++];
+  }
+  return o;
+}
+extern "C" void tfdl_rt_shuffler_destroy(void* h) { delete static_cast<Shuffler*>(h); }

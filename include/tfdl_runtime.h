@@ -20,6 +20,10 @@ uint32_t tfdl_rt_crc32c_mask(uint32_t crc);
 
 /* ---- input pipeline helpers (ref: tf_dist_example.py:22-33 map/shuffle/batch) ------------ */
 int tfdl_rt_shuffle_indices(const int64_t* src, int64_t n, int64_t buffer, uint64_t seed, int64_t* out);
+/* the same shuffle, produced on demand: next() writes up to `max` more indices and returns the count (0 = done) */
+void* tfdl_rt_shuffler_create(const int64_t* src, int64_t n, int64_t buffer, uint64_t seed);
+int64_t tfdl_rt_shuffler_next(void* shuffler, int64_t* out, int64_t max);
+void tfdl_rt_shuffler_destroy(void* shuffler);
 int tfdl_rt_gather_rows(const void* src, int64_t num_rows, int64_t row_bytes, const int64_t* idx, int64_t n,
                         void* dst, int threads);
 int tfdl_rt_gather_rows_u8_to_f32(const uint8_t* src, int64_t num_rows, int64_t row_elems, const int64_t* idx,
@@ -28,6 +32,11 @@ int tfdl_rt_gather_rows_u8_to_f32(const uint8_t* src, int64_t num_rows, int64_t 
 /* k records [x_i | int32 labels_i] into a (pinned) ring; labels given as int32 (label_bytes 4) or int64 (8) */
 int tfdl_rt_pack_records(const void* const* xs, const void* const* ys, int64_t k, int64_t x_bytes, int64_t n_labels,
                          int label_bytes, void* ring, int64_t rec_bytes, int threads);
+
+/* k records gathered straight from dataset arrays: record r = [x rows idx[r*B .. r*B+B) | their labels as int32]
+ * (labels stored as uint8, int32 or int64: label_bytes 1, 4, 8). shuffle + batch + staging in one pass. */
+int tfdl_rt_gather_records(const void* x_src, int64_t num_rows, int64_t x_row_bytes, const void* y_src, int label_bytes,
+                           const int64_t* idx, int64_t k, int64_t B, void* ring, int64_t rec_bytes, int threads);
 
 /* ---- TCP control plane + RING collective (ref: README.md:21-23,65-68) -------------------- */
 /* Binds the port of addrs[rank], connects ring/control/heartbeat channels, returns once every

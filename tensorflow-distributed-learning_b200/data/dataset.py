@@ -392,6 +392,10 @@ class Dataset:
     def _index_chunks(self) -> Iterator[np.ndarray]:
         raise TypeError(f"{type(self).__name__} is not an element-stage dataset")
 
+    def _identity_count(self) -> Optional[int]:
+        """n when the index stream of this (indexable) dataset is exactly 0..n-1, else None."""
+        return None
+
     def _with_parent(self, parent: "Dataset") -> "Dataset":
         """Shallow copy of this node on top of a different parent (pipeline rewrites)."""
         import copy
@@ -429,6 +433,9 @@ class _TensorSliceDataset(_IndexableDataset):
         for lo in range(0, n, self._CHUNK):
             yield np.arange(lo, min(n, lo + self._CHUNK), dtype=np.int64)
 
+    def _identity_count(self) -> Optional[int]:
+        return len(self._b)
+
     def cardinality(self) -> int:
         return len(self._b)
 
@@ -459,6 +466,9 @@ class _MapDataset(Dataset):
 
     def _index_chunks(self) -> Iterator[np.ndarray]:
         return self._parent._index_chunks()
+
+    def _identity_count(self) -> Optional[int]:
+        return self._parent._identity_count() if self._is_indexable() else None
 
     def _elements(self) -> Iterator[Any]:
         if self._is_indexable():
@@ -509,6 +519,9 @@ class _CacheDataset(_IndexableDataset):
         for lo in range(0, n, self._CHUNK):
             yield np.arange(lo, min(n, lo + self._CHUNK), dtype=np.int64)
 
+    def _identity_count(self) -> Optional[int]:
+        return len(self._materialise())
+
     def cardinality(self) -> int:
         c = self._parent.cardinality()
         return c if c >= 0 else len(self._materialise())
@@ -544,8 +557,23 @@ class _ShuffleDataset(Dataset):
 
     def _index_chunks(self) -> Iterator[np.ndarray]:
         seed = self._next_seed()
-        chunks = list(self._parent._index_chunks())
-        src = np.concatenate(chunks) if chunks else np.zeros(0, np.int64)
+        ident = self._parent._identity_count()
+        if ident is not None:
+            src: Any = ident  # the parent's stream is 0..n-1: nothing to materialise
+        else:
+            chunks = list(self._parent._index_chunks())
+            src = np.concatenate(chunks) if chunks else np.zeros(0, np.int64)
+        try:
+            from ..runtime import native as _native
+
+            stream = _native.shuffle_stream(src, self._buf, seed) if _native.available() else None
+        except Exception:
+            stream = None
+        if stream is None and ident is not None:
+            src = np.arange(ident, dtype=np.int64)
+        if stream is not None:  # produced on demand: a 20-step fit() draws 1,280 indices, not all 60,000
+            yield from stream
+            return
         out = _shuffle_indices(src, self._buf, seed)
         step = _IndexableDataset._CHUNK
         for lo in range(0, out.size, step):
@@ -710,25 +738,33 @@ class _BatchDataset(Dataset):
     def batch_size(self) -> int:
         return self._bs
 
+    def index_batches(self) -> Iterator[np.ndarray]:
+        """The row numbers of every batch, without gathering anything (indexable parents only). Consumers that can
+        gather for themselves - the native executor fills its pinned ring straight from the dataset arrays - use this
+        instead of iterating the dataset."""
+        p = self._parent
+        pending: List[np.ndarray] = []
+        have = 0
+        for c in p._index_chunks():
+            pending.append(c)
+            have += c.size
+            if have < self._bs:
+                continue
+            buf = np.concatenate(pending) if len(pending) > 1 else pending[0]
+            lo = 0
+            while buf.size - lo >= self._bs:
+                yield buf[lo:lo + self._bs]
+                lo += self._bs
+            pending, have = ([buf[lo:]], buf.size - lo) if lo < buf.size else ([], 0)
+        if have and not self._drop:
+            yield np.concatenate(pending)
+
     def _elements(self) -> Iterator[Any]:
         p = self._parent
         if p._is_indexable():
             base = p._base()
-            pending: List[np.ndarray] = []
-            have = 0
-            for c in p._index_chunks():
-                pending.append(c)
-                have += c.size
-                if have < self._bs:
-                    continue
-                buf = np.concatenate(pending) if len(pending) > 1 else pending[0]
-                lo = 0
-                while buf.size - lo >= self._bs:
-                    yield base.gather(buf[lo:lo + self._bs])
-                    lo += self._bs
-                pending, have = ([buf[lo:]], buf.size - lo) if lo < buf.size else ([], 0)
-            if have and not self._drop:
-                yield base.gather(np.concatenate(pending))
+            for idx in self.index_batches():
+                yield base.gather(idx)
             return
         buf_e: List[Any] = []
         for e in p:
@@ -814,6 +850,9 @@ class _OptionsDataset(Dataset):
     def _index_chunks(self) -> Iterator[np.ndarray]:
         return self._parent._index_chunks()
 
+    def _identity_count(self) -> Optional[int]:
+        return self._parent._identity_count() if self._is_indexable() else None
+
     def _elements(self) -> Iterator[Any]:
         return iter(self._parent)
 
@@ -824,6 +863,17 @@ class _OptionsDataset(Dataset):
 # --------------------------------------------------------------------------------------------
 # pipeline rewrites used by the strategies
 # --------------------------------------------------------------------------------------------
+
+def index_stream(ds: Dataset) -> Optional[Tuple[_Base, Iterator[np.ndarray]]]:
+    """(element store, iterator over the row numbers of each batch) when `ds` is a batch over an indexable pipeline
+    with nothing but options / prefetch above it; None otherwise (the caller then iterates `ds` normally)."""
+    node: Optional[Dataset] = ds
+    while isinstance(node, (_OptionsDataset, _PrefetchDataset)):
+        node = node._parent
+    if not isinstance(node, _BatchDataset) or node._parent is None or not node._parent._is_indexable():
+        return None
+    return node._parent._base(), node.index_batches()
+
 
 def find_batch_node(ds: Dataset) -> Optional[_BatchDataset]:
     node: Optional[Dataset] = ds

@@ -12,6 +12,11 @@ from typing import Any, Callable, Dict, List, Optional, Sequence, Union
 
 
 class Callback:
+    # True for callbacks that only consume an epoch's logs (history, progress line, scalar writers): fit() may then
+    # hand them epoch k's logs while epoch k+1 is already running, so the device never waits for the host at an epoch end.
+    # Anything that acts on the model at the epoch boundary (checkpoints, early stopping, LR schedules) keeps False.
+    lag_ok = False
+
     def __init__(self) -> None:
         self.model: Any = None
         self.params: Dict[str, Any] = {}
@@ -52,6 +57,10 @@ class CallbackList:
     def has_batch_hooks(self) -> bool:
         return bool(self._batch_begin or self._batch_end)
 
+    @property
+    def lag_ok(self) -> bool:
+        return all(c.lag_ok for c in self.callbacks)
+
     def initial_epoch(self, requested: int) -> int:
         for c in self.callbacks:
             requested = c.initial_epoch(requested)
@@ -84,6 +93,7 @@ class CallbackList:
 
 class ProgbarLogger(Callback):
     """One line per epoch on every worker: `Epoch 3/10 - 20/20 - 0.1s - loss: ... - accuracy: ...`."""
+    lag_ok = True
 
     def on_epoch_end(self, epoch: int, logs=None) -> None:
         logs = logs or {}
@@ -216,6 +226,7 @@ class ModelCheckpoint(Callback):
 
 class TensorBoard(Callback):
     """Chief-only scalar summaries in TensorBoard's event-file format (native writer)."""
+    lag_ok = True
 
     def __init__(self, log_dir: str = "logs", update_freq: Union[str, int] = "epoch", **_: Any) -> None:
         super().__init__()
@@ -280,6 +291,8 @@ class BackupAndRestore(Callback):
 
 
 class CSVLogger(Callback):
+    lag_ok = True
+
     def __init__(self, filename: str) -> None:
         super().__init__()
         self.filename = filename

@@ -49,6 +49,8 @@ class mixed_precision:  # tf.keras.mixed_precision look-alike
 
 
 class History(_cb.Callback):
+    lag_ok = True
+
     def __init__(self) -> None:
         super().__init__()
         self.history: Dict[str, List[float]] = {}
@@ -263,6 +265,7 @@ class Model:
         is one full pass."""
         if self.optimizer is None or self.loss is None:
             raise RuntimeError("compile(optimizer=..., loss=...) must be called before fit()")
+        t_fit = time.time()
         ds = _as_dataset(x, y, batch_size, shuffle=shuffle and not isinstance(x, Dataset))
         dist = ds if isinstance(x, DistributedDataset) else self.strategy.experimental_distribute_dataset(ds)
         if not self.built:
@@ -277,21 +280,56 @@ class Model:
         logs: Dict[str, float] = {}
         cbs.on_train_begin()
         initial_epoch = cbs.initial_epoch(initial_epoch)
-        it: Optional[Iterator[PerReplica]] = None
+        chunked = hasattr(engine, "train_chunk") and not cbs.has_batch_hooks
+        # Index path: the engine gathers its batches itself, straight from the dataset arrays into its pinned ring.
+        idx_mode = None
+        if chunked and hasattr(engine, "train_index_chunk") and os.environ.get("TFDL_FIT_INDEX", "1") == "1":
+            st = dist.index_stream() if hasattr(dist, "index_stream") else None
+            if st is not None:
+                arrs = engine.index_arrays(st[0])
+                if arrs is not None:
+                    idx_mode = arrs
+        # Lagged epoch ends: when every callback only consumes logs, epoch k's totals are read (and its callbacks run)
+        # after epoch k+1 has been queued, so the device never idles at an epoch boundary. The totals themselves are
+        # exact - they are closed on the device, stream-ordered after the epoch's last step.
+        lag = (chunked and hasattr(engine, "epoch_mark") and validation_data is None and cbs.lag_ok
+               and os.environ.get("TFDL_FIT_LAG", "1") == "1")
+        pending: Optional[Tuple[int, Any, float, int]] = None
+
+        def deliver(p: Tuple[int, Any, float, int]) -> Dict[str, float]:
+            ep, handle, t_start, n_steps = p
+            loss_sum, correct, count = engine.epoch_read(handle)
+            out = {"loss": loss_sum / count if count else 0.0}
+            for met in self.compiled_metrics:
+                out[met.name] = correct / count if count else 0.0
+            out["_epoch_time"] = time.time() - t_start
+            out["_steps"] = n_steps
+            cbs.on_epoch_end(ep, out)
+            return out
+
+        it: Any = None
+        self.reset_metrics()
         for epoch in range(initial_epoch, epochs):
-            self.reset_metrics()
+            if not lag and epoch > initial_epoch:
+                self.reset_metrics()
             cbs.on_epoch_begin(epoch)
             t0 = time.time()
             if it is None or steps_per_epoch is None:
-                it = iter(dist)
+                if idx_mode is not None:
+                    if it is not None:
+                        st = dist.index_stream()  # a new pass over the data: fresh shuffle order
+                    it = iter(st[1])
+                else:
+                    it = iter(dist)
             step = 0
-            chunked = hasattr(engine, "train_chunk") and not cbs.has_batch_hooks
             while steps_per_epoch is None or step < steps_per_epoch:
                 want = 1
                 if chunked:
-                    # chunk sizes ramp 8, 16, 32, ... so the device starts after 8 batches are staged, not after CHUNK
-                    ramp = min(engine.CHUNK, 8 << min(step // 8, 16).bit_length()) if step < engine.CHUNK else engine.CHUNK
-                    want = ramp if steps_per_epoch is None else min(ramp, steps_per_epoch - step)
+                    if steps_per_epoch is not None:
+                        want = min(engine.CHUNK, steps_per_epoch - step)  # the epoch length is known: no ramp
+                    else:
+                        # chunk sizes ramp 8, 16, 32, ... so the device starts after 8 batches are staged, not after CHUNK
+                        want = min(engine.CHUNK, 8 << min(step // 8, 16).bit_length()) if step < engine.CHUNK else engine.CHUNK
                 group, exhausted = [], False
                 for _ in range(want):
                     try:
@@ -300,7 +338,9 @@ class Model:
                         exhausted = True
                         break
                 if group:
-                    if chunked:
+                    if idx_mode is not None:
+                        engine.train_index_chunk(idx_mode[0], idx_mode[1], group)
+                    elif chunked:
                         engine.train_chunk(group)  # the native executor runs the whole chunk without Python
                     else:
                         cbs.on_train_batch_begin(step)
@@ -318,16 +358,29 @@ class Model:
                     break
                 if self.stop_training:
                     break
-            logs = self._read_logs()
-            if validation_data is not None:
-                val = self.evaluate(validation_data, steps=validation_steps, verbose=0, return_dict=True,
-                                    _prefix="val_")
-                logs.update(val)
-            logs["_epoch_time"] = time.time() - t0
-            logs["_steps"] = step
-            cbs.on_epoch_end(epoch, logs)
+            if lag:
+                handle = engine.epoch_mark()
+                if pending is not None:
+                    logs = deliver(pending)
+                pending = (epoch, handle, t0, step)
+            else:
+                logs = self._read_logs()
+                if validation_data is not None:
+                    val = self.evaluate(validation_data, steps=validation_steps, verbose=0, return_dict=True,
+                                        _prefix="val_")
+                    logs.update(val)
+                logs["_epoch_time"] = time.time() - t0
+                logs["_steps"] = step
+                cbs.on_epoch_end(epoch, logs)
             if self.stop_training:
                 break
+        if pending is not None:
+            logs = deliver(pending)
+        if os.environ.get("TFDL_FIT_PROFILE") and hasattr(engine, "prof"):
+            print("[tfdl fit profile, host ms] " + ", ".join(f"{k} {1e3 * v:.2f}" for k, v in engine.prof.items())
+                  + f", fit total {1e3 * (time.time() - t_fit):.2f}", file=sys.stderr)
+            for k in engine.prof:
+                engine.prof[k] = 0.0
         cbs.on_train_end(logs)
         for k in ("_epoch_time", "_steps"):
             history.history.pop(k, None)

@@ -16,6 +16,7 @@ from __future__ import annotations
 
 import ctypes as C
 import os
+import time
 from typing import Any, List, Optional, Tuple
 
 import numpy as np
@@ -105,6 +106,7 @@ class NativeCnnEngine:
         self._torch_engine: Any = None
         self._keep: List[Any] = []
         self._pinned: dict = {}            # host ranges page-locked for the zero-staging input path
+        self.prof = {"gather": 0.0, "enqueue": 0.0, "mark": 0.0, "read_wait": 0.0, "ring_wait": 0.0}  # host seconds
         self._ptr_keep: List[Any] = [None, None]
         torch.cuda.set_device(self.device)
         # graphs cannot be captured on the legacy default stream: the engine owns its stream
@@ -390,6 +392,102 @@ class NativeCnnEngine:
 
     def train_step(self, batches: PerReplica) -> None:
         self.train_chunk([batches])
+
+    # ---- index path: the executor's ring is filled straight from the dataset arrays ---------------------------------
+    def index_arrays(self, base: Any) -> Optional[Tuple[np.ndarray, np.ndarray]]:
+        """(images, labels) when `base` is a plain array store this engine can gather from itself: float32 images of the
+        model's input size and integer labels (what `.map(scale).cache()` of tf_dist_example.py:31 leaves)."""
+        arrays = getattr(base, "arrays", None)
+        if not isinstance(arrays, (tuple, list)) or len(arrays) != 2:
+            return None
+        x, y = arrays
+        if not (isinstance(x, np.ndarray) and isinstance(y, np.ndarray)):
+            return None
+        H0, W0 = self.shape[:2]
+        if x.dtype != np.float32 or not x.flags.c_contiguous or int(np.prod(x.shape[1:])) != H0 * W0:
+            return None
+        if y.ndim != 1 or y.dtype not in (np.uint8, np.int32, np.int64) or not y.flags.c_contiguous:
+            return None
+        return x, y
+
+    def train_index_chunk(self, x: np.ndarray, y: np.ndarray, idxs: List[np.ndarray]) -> None:
+        """Train on len(idxs) consecutive batches given as row numbers into (x, y): ONE multi-threaded gather builds the
+        records in the pinned ring (shuffle + batch + staging in a single pass), one executor call runs them."""
+        i = 0
+        while i < len(idxs):
+            B = int(idxs[i].size)
+            if B == 0:
+                i += 1
+                continue
+            if B % 16 != 0:  # ragged last batch: the portable step
+                self._fallback_step(PerReplica([(x[idxs[i]], y[idxs[i]])]))
+                i += 1
+                continue
+            if self._B != B:
+                self._build_program(B)
+            r = self._ring_i
+            self._ring_i ^= 1
+            self.ring, self.host_out = self.rings[r], self.host_outs[r]
+            tw = time.perf_counter()
+            self.ring_done[r].synchronize()
+            self.prof["ring_wait"] += time.perf_counter() - tw
+            k = 0
+            # the first group of a call is short (8 steps): the device starts on it while the rest is being gathered
+            cap = 8 if i == 0 and len(idxs) > 8 else self.ring.shape[0]
+            while i + k < len(idxs) and k < cap and idxs[i + k].size == B:
+                k += 1
+            t0 = time.perf_counter()
+            group = idxs[i:i + k]
+            if all(int(g[-1]) - int(g[0]) == B - 1 and int(g[B // 2]) - int(g[0]) == B // 2 for g in group) and \
+                    y.dtype == np.int32:
+                # consecutive rows (an unshuffled dataset): no gather at all - the executor reads the dataset array in place
+                xs = [x[int(g[0]):int(g[0]) + B] for g in group]
+                ys = [y[int(g[0]):int(g[0]) + B] for g in group]
+                if self._zero_copy_ok(xs, ys):
+                    self._run_ptrs(xs, ys, r)
+                    self.ring_done[r].record(self.stream)
+                    self._last_k = k
+                    i += k
+                    continue
+            flat = np.ascontiguousarray(np.concatenate(group), dtype=np.int64)
+            _rt.gather_records(x, y, flat, k, B, self.ring.data_ptr(), self.rec_bytes)
+            t1 = time.perf_counter()
+            self.run_pinned(self.ring, k, self.host_out)
+            self.prof["gather"] += t1 - t0
+            self.prof["enqueue"] += time.perf_counter() - t1
+            self.ring_done[r].record(self.stream)
+            self._last_k = k
+            i += k
+
+    # ---- epoch totals without stopping the device ----------------------------------------------------------------
+    def epoch_mark(self) -> Tuple[int, Any]:
+        """Close an epoch on the device: stream-ordered after the epoch's last step, the (loss sum, correct, examples)
+        counters are summed over replicas (NVLink kernel), copied to a pinned slot and cleared. Returns a handle for
+        epoch_read(); the host does not wait here, so the next epoch's batches can be staged while this one runs."""
+        if not hasattr(self, "_ep_pinned"):
+            self._ep_pinned = [torch.zeros(3, dtype=torch.float64).pin_memory() for _ in range(4)]
+            self._ep_i = 0
+        slot = self._ep_i
+        self._ep_i = (self._ep_i + 1) % len(self._ep_pinned)
+        tm = time.perf_counter()
+        with torch.cuda.stream(self.stream):
+            tot = self.metrics_dev.double()
+            if self.ops.world > 1:
+                tot = self.ops.allreduce_scalars_device(tot)
+            self._ep_pinned[slot].copy_(tot, non_blocking=True)
+            self.metrics_dev.zero_()
+            ev = torch.cuda.Event()
+            ev.record(self.stream)
+        self.prof["mark"] += time.perf_counter() - tm
+        return slot, ev
+
+    def epoch_read(self, handle: Tuple[int, Any]) -> Tuple[float, float, float]:
+        slot, ev = handle
+        tw = time.perf_counter()
+        ev.synchronize()
+        self.prof["read_wait"] += time.perf_counter() - tw
+        t = self._ep_pinned[slot]
+        return float(t[0]), float(t[1]), float(t[2])
 
     def last_step_out(self) -> Tuple[float, float]:
         self.stream.synchronize()

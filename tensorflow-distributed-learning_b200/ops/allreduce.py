@@ -171,6 +171,26 @@ class P2PFusedAllReduce(CrossDeviceOps):
                                                            _lib.cur_stream()), "allreduce_small_f64")
         return out[:v.size].cpu().numpy().reshape(np.shape(vals))
 
+    def allreduce_scalars_device(self, vals: torch.Tensor) -> torch.Tensor:
+        """Sum of <= 256 float64 values over the ranks with input and result on the device, ordered on the current
+        stream - no host round trip (epoch totals are read one epoch late, keras/engine.py). Same kernel and slot
+        scheme as allreduce_scalars; the two must not be interleaved on different streams."""
+        if self.world == 1:
+            return vals
+        n = int(vals.numel())
+        assert n <= 256 and vals.dtype == torch.float64 and vals.is_cuda
+        if self._scalars is None:
+            buf = SymmetricBuffer(512, torch.float64, self.device, self.world, self.rank)
+            st = FusedState(self, None, buf, False, plain=True)
+            self._scalars = [buf, st, torch.zeros(256, dtype=torch.float64, device=self.device), 0]
+        buf, st, out, calls = self._scalars
+        par = calls & 1
+        self._scalars[3] = calls + 1
+        buf.tensor[par * 256:par * 256 + n].copy_(vals.reshape(-1))
+        _lib.check(_lib.kernels().tfdl_allreduce_small_f64(C.byref(st.struct(0)), _lib.ptr(out), n, _lib.cur_stream()),
+                   "allreduce_small_f64")
+        return out[:n].clone()
+
     def broadcast_params(self, params: Sequence[torch.Tensor]) -> None:
         """Initial values from the chief (tf_dist_example.py:56-57): every other rank copies rank 0's arena over NVLink
         with peer loads (csrc/kernels/allreduce.cu:broadcast_kernel)."""

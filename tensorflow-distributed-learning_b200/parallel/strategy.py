@@ -100,6 +100,13 @@ class DistributedDataset:
         c = self.dataset.cardinality()
         return c if c < 0 else (c + self.num_local - 1) // self.num_local
 
+    def index_stream(self):
+        """(element store, iterator of per-step row numbers) for a single local replica over an indexable pipeline,
+        else None. Lets an engine gather its batches itself (data/dataset.py:index_stream)."""
+        if self.num_local != 1:
+            return None
+        return _ds.index_stream(self.dataset)
+
 
 class Strategy:
     """Common machinery; see MirroredStrategy / MultiWorkerMirroredStrategy."""

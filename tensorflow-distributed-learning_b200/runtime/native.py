@@ -27,8 +27,16 @@ def lib() -> C.CDLL:
         L.tfdl_rt_crc32c_mask.argtypes = [C.c_uint32]
         L.tfdl_rt_shuffle_indices.argtypes = [vp, C.c_int64, C.c_int64, C.c_uint64, vp]
         L.tfdl_rt_gather_rows.argtypes = [vp, C.c_int64, C.c_int64, vp, C.c_int64, vp, C.c_int]
+        L.tfdl_rt_shuffler_create.restype = vp
+        L.tfdl_rt_shuffler_create.argtypes = [vp, C.c_int64, C.c_int64, C.c_uint64]
+        L.tfdl_rt_shuffler_next.restype = C.c_int64
+        L.tfdl_rt_shuffler_next.argtypes = [vp, vp, C.c_int64]
+        L.tfdl_rt_shuffler_destroy.restype = None
+        L.tfdl_rt_shuffler_destroy.argtypes = [vp]
         L.tfdl_rt_pack_records.argtypes = [vp, vp, C.c_int64, C.c_int64, C.c_int64, C.c_int, vp, C.c_int64, C.c_int]
         L.tfdl_rt_gather_rows_u8_to_f32.argtypes = [vp, C.c_int64, C.c_int64, vp, C.c_int64, C.c_float, vp, C.c_int]
+        L.tfdl_rt_gather_records.argtypes = [vp, C.c_int64, C.c_int64, vp, C.c_int, vp, C.c_int64, C.c_int64, vp,
+                                             C.c_int64, C.c_int]
         L.tfdl_rt_group_create.restype = vp
         L.tfdl_rt_group_create.argtypes = [C.c_int, C.c_int, C.POINTER(C.c_char_p), C.c_int, C.c_int, C.c_int]
         L.tfdl_rt_group_destroy.argtypes = [vp]
@@ -94,6 +102,30 @@ def shuffle_indices(src: np.ndarray, buffer_size: int, seed: int) -> np.ndarray:
     return out
 
 
+def shuffle_stream(src, buffer_size: int, seed: int, chunk: int = 8192):
+    """Generator over chunks of the shuffled index stream (tf.data shuffle-buffer semantics), produced on demand.
+    ``src``: the index stream to shuffle, or an int n for the identity stream 0..n-1 (nothing is materialised)."""
+    if isinstance(src, (int, np.integer)):
+        h = lib().tfdl_rt_shuffler_create(None, int(src), int(buffer_size), C.c_uint64(seed & ((1 << 64) - 1)))
+    else:
+        src = np.ascontiguousarray(src, dtype=np.int64)
+        h = lib().tfdl_rt_shuffler_create(_np_ptr(src), src.size, int(buffer_size), C.c_uint64(seed & ((1 << 64) - 1)))
+    if not h:
+        raise RuntimeError(_lib.runtime_error() if hasattr(_lib, "runtime_error") else "shuffler_create failed")
+    try:
+        first = True
+        while True:
+            # a small first chunk: the consumer's first batches should not wait for 8192 draws
+            out = np.empty(min(chunk, 2048) if first else chunk, dtype=np.int64)
+            first = False
+            n = int(lib().tfdl_rt_shuffler_next(h, _np_ptr(out), out.size))
+            if n == 0:
+                return
+            yield out[:n]
+    finally:
+        lib().tfdl_rt_shuffler_destroy(h)
+
+
 def gather_rows(src: np.ndarray, idx: np.ndarray, out: Optional[np.ndarray] = None, threads: int = 4) -> np.ndarray:
     src = np.ascontiguousarray(src)
     idx = np.ascontiguousarray(idx, dtype=np.int64)
@@ -113,6 +145,16 @@ def pack_records(xs: list, ys: list, ring_ptr: int, rec_bytes: int, threads: int
     py = (C.c_void_p * k)(*[a.ctypes.data for a in ys])
     _lib.check_rt(lib().tfdl_rt_pack_records(px, py, k, xs[0].nbytes, ys[0].size, ys[0].dtype.itemsize, ring_ptr,
                                              rec_bytes, threads), "pack_records")
+
+
+def gather_records(x: np.ndarray, y: np.ndarray, idx: np.ndarray, k: int, B: int, ring_ptr: int, rec_bytes: int,
+                   threads: int = 4) -> None:
+    """k records [x[idx[r*B:(r+1)*B]] | int32 labels] gathered from dataset arrays into the ring at ``ring_ptr``:
+    shuffle + batch + staging of tf_dist_example.py:31-33 in one multi-threaded pass. x: C-contiguous rows of any
+    dtype; y: C-contiguous uint8 / int32 / int64 vector; idx: k*B int64 row numbers."""
+    row = int(np.prod(x.shape[1:], dtype=np.int64)) * x.itemsize
+    _lib.check_rt(lib().tfdl_rt_gather_records(_np_ptr(x), x.shape[0], row, _np_ptr(y), y.dtype.itemsize, _np_ptr(idx),
+                                              k, B, C.c_void_p(ring_ptr), rec_bytes, threads), "gather_records")
 
 
 def gather_rows_u8_to_f32(src: np.ndarray, idx: np.ndarray, scale: float, out_ptr: int, threads: int = 4) -> None:

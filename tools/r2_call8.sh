@@ -1,0 +1,11 @@
+#!/bin/bash
+mkdir -p gpurun_out
+TR="python -m torch.distributed.run --nnodes=1 --nproc-per-node 2 --master-addr 127.0.0.1"
+timeout 900 python -m pytest tests/test_native_engine_gpu.py -x -q > gpurun_out/c8_pytest.log 2>&1; echo "pytest rc=$?"; tail -15 gpurun_out/c8_pytest.log
+export TFDL_FIT_PROFILE=1
+for st in 20 400; do
+timeout 300 python bench.py --steps $st --warmup 5 2>gpurun_out/c8_n1_$st.err | tee gpurun_out/c8_n1_$st.json | python -c "import json,sys; d=json.loads(sys.stdin.read()); print(d['n_gpus'], d['steps'], d['ms_per_step'], d['e2e']['ms_per_step'])"
+grep "fit profile" gpurun_out/c8_n1_$st.err
+timeout 300 $TR --master-port 29641 bench.py --gpus 2 --steps $st --warmup 5 2>gpurun_out/c8_n2_$st.err | tee gpurun_out/c8_n2_$st.json | python -c "import json,sys; d=json.loads(sys.stdin.read().strip().splitlines()[-1]); print(d['n_gpus'], d['steps'], d['ms_per_step'], d['e2e']['ms_per_step'])"
+grep "fit profile" gpurun_out/c8_n2_$st.err
+done
