@@ -278,9 +278,14 @@ __device__ __forceinline__ uint4 ld_packet(const uint4* src) {
                : "memory");
   return v;
 }
-__device__ __forceinline__ void push_f4(uint4* dst, float4 g, uint32_t e) {
+// Packet layout of one inbox region: float4 #i occupies packets pkt_of(i) and pkt_of(i) + 32, so the 32 lanes of a
+// warp (consecutive i) store 512 contiguous bytes per instruction instead of 16-byte pieces at a 32-byte stride.
+__host__ __device__ __forceinline__ int64_t pkt_of(int64_t i) { return ((i >> 5) << 6) + (i & 31); }
+__host__ __device__ __forceinline__ int64_t region_packets(int64_t n4) { return ((n4 + 31) >> 5) << 6; }
+__device__ __forceinline__ void push_f4(uint4* region, int64_t i, float4 g, uint32_t e) {
+  uint4* dst = region + pkt_of(i);
   st_packet(dst, g.x, g.y, e);
-  st_packet(dst + 1, g.z, g.w, e);
+  st_packet(dst + 32, g.z, g.w, e);
 }
 
 // Sum over ranks of float4 #slot: peers' values from this rank's inbox regions (region r at base + r*stride),
@@ -293,8 +298,8 @@ __device__ __forceinline__ bool poll_sum(const uint4* base, int64_t stride, int6
 #pragma unroll
     for (int r = 0; r < TFDL_MAX_RANKS; ++r)
       if (r < W && r != rank) {
-        a[r] = ld_packet(base + r * stride + slot * 2);
-        b[r] = ld_packet(base + r * stride + slot * 2 + 1);
+        a[r] = ld_packet(base + r * stride + pkt_of(slot));
+        b[r] = ld_packet(base + r * stride + pkt_of(slot) + 32);
       }
     bool ready = true;
 #pragma unroll
@@ -319,10 +324,12 @@ __device__ __forceinline__ bool poll_sum(const uint4* base, int64_t stride, int6
   out = g;
   return true;
 }
-__device__ __forceinline__ bool poll_one(const uint4* src, uint32_t e, const uint32_t* abort_word, float4& out) {
+__device__ __forceinline__ bool poll_one(const uint4* region, int64_t slot, uint32_t e, const uint32_t* abort_word,
+                                         float4& out) {
+  const uint4* src = region + pkt_of(slot);
   uint32_t spins = 0;
   for (;;) {
-    uint4 a = ld_packet(src), b = ld_packet(src + 1);
+    uint4 a = ld_packet(src), b = ld_packet(src + 32);
     if (a.y == e && a.w == e && b.y == e && b.w == e) {
       out = make_float4(__uint_as_float(a.x), __uint_as_float(a.z), __uint_as_float(b.x), __uint_as_float(b.z));
       return true;
@@ -342,7 +349,7 @@ __global__ void __launch_bounds__(256) fused_ar_push_kernel(TfdlFusedArParams p)
   const TfdlHyper h = *p.hyper;
   const int W = p.world, rank = p.rank;
   const int64_t n4 = p.n >> 2;
-  const int64_t region = n4 * 2;  // packets per (parity, source)
+  const int64_t region = region_packets(n4);  // packets per (parity, source)
   const float4* g4 = reinterpret_cast<const float4*>(p.grads[par][rank]);
   const int64_t tid = (int64_t)blockIdx.x * blockDim.x + threadIdx.x, nth = (int64_t)gridDim.x * blockDim.x;
   // ---- out: my gradients into every peer's inbox ----
@@ -351,7 +358,7 @@ __global__ void __launch_bounds__(256) fused_ar_push_kernel(TfdlFusedArParams p)
 #pragma unroll
     for (int r = 0; r < TFDL_MAX_RANKS; ++r)
       if (r < W && r != rank)
-        push_f4(reinterpret_cast<uint4*>(p.inbox[r]) + ((int64_t)ipar * W + rank) * region + i * 2, g, e);
+        push_f4(reinterpret_cast<uint4*>(p.inbox[r]) + ((int64_t)ipar * W + rank) * region, i, g, e);
   }
   // ---- in: sum in rank order, update ----
   const uint4* mine = reinterpret_cast<const uint4*>(p.inbox[rank]) + (int64_t)ipar * W * region;
@@ -380,7 +387,7 @@ __global__ void __launch_bounds__(256) fused_ar_push2_kernel(TfdlFusedArParams p
   const TfdlHyper h = *p.hyper;
   const int W = p.world, rank = p.rank;
   const int64_t n4 = p.n >> 2;
-  const int64_t per = (n4 + W - 1) / W, region = per * 2;
+  const int64_t per = (n4 + W - 1) / W, region = region_packets(per);
   const int64_t lo = per * rank, hi = min(n4, lo + per);
   const float4* g4 = reinterpret_cast<const float4*>(p.grads[par][rank]);
   float4* w4 = reinterpret_cast<float4*>(p.params[rank]);
@@ -392,7 +399,7 @@ __global__ void __launch_bounds__(256) fused_ar_push2_kernel(TfdlFusedArParams p
   for (int64_t i = tid; i < n4; i += nth) {
     const int owner = (int)(i / per);
     if (owner == rank) continue;
-    push_f4(reinterpret_cast<uint4*>(p.inbox[owner]) + hop0 + (int64_t)rank * region + (i - owner * per) * 2, g4[i], e);
+    push_f4(reinterpret_cast<uint4*>(p.inbox[owner]) + hop0 + (int64_t)rank * region, i - owner * per, g4[i], e);
   }
   // ---- my slice: sum, update, hop 1 out (the new weights) ----
   const uint4* in0 = reinterpret_cast<const uint4*>(p.inbox[rank]) + hop0;
@@ -406,7 +413,7 @@ __global__ void __launch_bounds__(256) fused_ar_push2_kernel(TfdlFusedArParams p
 #pragma unroll
     for (int r = 0; r < TFDL_MAX_RANKS; ++r)
       if (r < W && r != rank)
-        push_f4(reinterpret_cast<uint4*>(p.inbox[r]) + hop1 + (int64_t)rank * region + (i - lo) * 2, w, e);
+        push_f4(reinterpret_cast<uint4*>(p.inbox[r]) + hop1 + (int64_t)rank * region, i - lo, w, e);
   }
   // ---- clear the other-parity gradients while the owners work ----
   float4* z4 = reinterpret_cast<float4*>(p.grads[par ^ 1][rank]);
@@ -418,7 +425,7 @@ __global__ void __launch_bounds__(256) fused_ar_push2_kernel(TfdlFusedArParams p
     const int owner = (int)(i / per);
     if (owner == rank) continue;
     float4 w;
-    if (!poll_one(in1 + (int64_t)owner * region + (i - owner * per) * 2, e, p.abort_word, w)) return;
+    if (!poll_one(in1 + (int64_t)owner * region, i - owner * per, e, p.abort_word, w)) return;
     w4[i] = w;
     if (s2) s2[i] = to_bf16x4(w);
   }
@@ -540,8 +547,9 @@ static int pick_grid(const TfdlFusedArParams* p, int64_t work4, int threads) {
 // Bytes of inbox every rank must provide for the push paths (peer-mapped, zero-initialised once).
 extern "C" int64_t tfdl_fused_ar_inbox_bytes(int algo, int world, int64_t n) {
   const int64_t n4 = (n + 3) / 4;
-  if (algo == TFDL_AR_PUSH) return 2 * (int64_t)world * n4 * 32;                                // [parity][source][float4 -> 2 packets]
-  if (algo == TFDL_AR_PUSH2) return 2 * 2 * (int64_t)world * ((n4 + world - 1) / world) * 32;   // [parity][hop][rank][slice]
+  if (algo == TFDL_AR_PUSH) return 2 * (int64_t)world * tfdl::region_packets(n4) * 16;  // [parity][source][region]
+  if (algo == TFDL_AR_PUSH2)                                                             // [parity][hop][rank][slice region]
+    return 2 * 2 * (int64_t)world * tfdl::region_packets((n4 + world - 1) / world) * 16;
   return 0;
 }
 

@@ -6,6 +6,7 @@
 // into a (pinned) staging buffer, optionally fusing the uint8 -> float32 /255 scale of
 // tf_dist_example.py:22-25.
 #include <algorithm>
+#include <cstdlib>
 #include <condition_variable>
 #include <functional>
 #include <mutex>
@@ -194,7 +195,16 @@ class Pool {
   bool stop_ = false;
 };
 Pool& pool() {
-  static Pool* p = new Pool(std::max(1, std::min(7, (int)std::thread::hardware_concurrency() - 1)));  // leaked on purpose: no static-destruction order games at exit
+  // Workers per process: the host's cores shared between the worker processes of this node (one per GPU under
+  // torchrun / TF_CONFIG launches), minus the caller; TFDL_IO_THREADS overrides. Leaked on purpose: no
+  // static-destruction order games at exit.
+  static Pool* p = [] {
+    int n = (int)std::thread::hardware_concurrency();
+    if (const char* lw = getenv("LOCAL_WORLD_SIZE")) n /= std::max(1, atoi(lw));
+    n = std::max(1, std::min(7, n - 1));
+    if (const char* e = getenv("TFDL_IO_THREADS")) n = std::max(1, std::min(32, atoi(e)));
+    return new Pool(n);
+  }();
   return *p;
 }
 std::mutex g_pool_mu;  // one parallel region at a time (callers are the per-process input pipeline)

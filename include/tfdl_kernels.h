@@ -126,6 +126,36 @@ int tfdl_batchnorm_bwd(const void* dy, const void* x, const void* y, const float
                        int C, int relu, void* stream);
 
 
+/* ---- Conv2D as an implicit GEMM on tcgen05 (ref: tf.keras.layers.Conv2D, tf_dist_example.py:41,43) ---------------
+ * NHWC bf16 activations, OHWI bf16 weights [K][R][S][C] (the storage layout of a Conv2D kernel variable), fp32
+ * accumulation. The activation operand is fetched by TMA in im2col mode (one [pixels x 64 channels] tile per filter
+ * tap, stride and zero padding applied by the TMA unit), so there is no im2col buffer. C and K multiples of 8.
+ * Output size: P = (H + pad_t + pad_b - R) / stride_h + 1, Q likewise. act: 0 none, 1 relu.
+ *   fwd    y[N][P][Q][K] = act(conv(x, w) + bias)
+ *   dgrad  dx[N][H][W][C] from dy[N][P][Q][K]             (stride 1)
+ *   wgrad  dw[K][R][S][C] fp32 += dy^T im2col(x)          (ACCUMULATES: zero dw first; split over pixels, TMA reduce-add) */
+int tfdl_conv2d_supported(int C, int K);
+int tfdl_conv2d_fwd(const void* x, const void* w, const float* bias, void* y, int N, int H, int W, int C, int K, int R,
+                    int S, int stride_h, int stride_w, int pad_t, int pad_l, int pad_b, int pad_r, int act, void* stream);
+int tfdl_conv2d_dgrad(const void* dy, const void* w, void* dx, int N, int H, int W, int C, int K, int R, int S, int pad_t,
+                      int pad_l, int pad_b, int pad_r, void* stream);
+int tfdl_conv2d_wgrad(const void* x, const void* dy, float* dw, int N, int H, int W, int C, int K, int R, int S,
+                      int stride_h, int stride_w, int pad_t, int pad_l, int pad_b, int pad_r, void* stream);
+
+/* ---- pooling for NHWC bf16 activations (ref: tf.keras.layers.MaxPooling2D, tf_dist_example.py:42,44; C % 8 == 0) --------
+ * maxpool_fwd stores the winning window position r*S+s per output element in idx (uint8 [N][P][Q][C]); maxpool_bwd is a
+ * deterministic gather over the windows covering each input element (dx is fully written). Padding positions never win.
+ * global_avgpool: y[N][C] = mean over HW. scatter_strided: dst[n][p*sh][q*sw] = src[n][p][q], zero elsewhere - the input
+ * gradient of a strided 1x1 convolution from its GEMM result. */
+int tfdl_maxpool_fwd(const void* x, void* y, uint8_t* idx, int N, int H, int W, int C, int R, int S, int stride_h,
+                     int stride_w, int pad_t, int pad_l, int P, int Q, void* stream);
+int tfdl_maxpool_bwd(const void* dy, const uint8_t* idx, void* dx, int N, int H, int W, int C, int R, int S, int stride_h,
+                     int stride_w, int pad_t, int pad_l, int P, int Q, void* stream);
+int tfdl_global_avgpool_fwd(const void* x, void* y, int N, int HW, int C, void* stream);
+int tfdl_global_avgpool_bwd(const void* dy, void* dx, int N, int HW, int C, void* stream);
+int tfdl_scatter_strided_nhwc(const void* src, void* dst, int N, int H, int W, int C, int P, int Q, int stride_h,
+                              int stride_w, void* stream);
+
 /* ---- fused gradient all-reduce + SGD over NVLink peer memory ------------------------------
  * ref: README.md:17,21,23,67 (NcclAllReduce / CollectiveOps after every batch) and
  * tf_dist_example.py:51 (SGD). One kernel per step: cross-GPU flag barrier, peer loads of the

@@ -560,7 +560,14 @@ class TorchEngine:
 
     def _ctx(self, r: int, training: bool) -> CallContext:
         leaves = self.leaves[r]
-        return CallContext(r, training, lambda v: leaves[id(v)], self.model.compute_dtype)
+        # CUDA replicas run the layer ops on the native kernels under either policy (same precision contract as the
+        # native step program); an engine explicitly requested as "torch" stays on library ops unless mixed_bfloat16
+        # asks for bf16 anyway - that is the independent reference the tests compare against.
+        native = None
+        if self.devices[r].type == "cuda" and self.model._engine_pref != "torch" and \
+                os.environ.get("TFDL_NATIVE_OPS", "1") == "1":
+            native = True
+        return CallContext(r, training, lambda v: leaves[id(v)], self.model.compute_dtype, native)
 
     def _to_device(self, a: Any, dev: torch.device) -> torch.Tensor:
         t = torch.from_numpy(np.ascontiguousarray(a)) if not isinstance(a, torch.Tensor) else a

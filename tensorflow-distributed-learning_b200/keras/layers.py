@@ -111,8 +111,12 @@ class CallContext:
     autograd leaf that aliases a variable in that replica's arena."""
 
     def __init__(self, replica: int, training: bool, param: Callable[[MirroredVariable], torch.Tensor],
-                 compute_dtype: torch.dtype = torch.float32) -> None:
+                 compute_dtype: torch.dtype = torch.float32, native: Optional[bool] = None) -> None:
         self.replica, self.training, self.param, self.compute_dtype = replica, training, param, compute_dtype
+        # native: run Conv2D / Dense / pooling on the sm_100a kernels (bf16 tensor-core operands, fp32 accumulation,
+        # fp32 master weights - the precision contract of the native step program) whenever the shapes allow it.
+        # Default: under the mixed_bfloat16 policy only; the training engine turns it on for CUDA replicas.
+        self.native = (compute_dtype == torch.bfloat16) if native is None else bool(native)
         # in-place updates of non-trainable variables (BatchNorm statistics) that must wait until autograd
         # has finished: every variable is a view of one arena, so they share a version counter
         self.deferred: List[Callable[[], None]] = []
@@ -246,7 +250,9 @@ class Conv2D(Layer):
         free (no extra pass over the activations, no bias-gradient reduction)."""
         assert self.kernel is not None
         b = ctx.param(self.bias) if (self.bias is not None and add_bias) else None
-        if (self.kernel_size == (1, 1) and self.strides == (1, 1) and x.is_cuda and ctx.compute_dtype == torch.bfloat16
+        fused_act = self.activation if self.activation in (None, "linear", "relu") else None
+        post = None if fused_act == self.activation or self.activation == "linear" else _ACTS[self.activation]
+        if (self.kernel_size == (1, 1) and self.strides == (1, 1) and x.is_cuda and ctx.native
                 and x.shape[-1] % 8 == 0 and self.filters % 8 == 0 and os.environ.get("TFDL_CONV1X1", "gemm") == "gemm"):
             # a 1x1 stride-1 convolution over NHWC activations IS a GEMM over [N*H*W, Cin]: forward, dgrad and wgrad
             # run on the TMA + tcgen05 kernels (OHWI storage of a 1x1 kernel is the [out][in] matrix itself)
@@ -257,6 +263,21 @@ class Conv2D(Layer):
             if self.activation not in (None, "relu", "gelu"):
                 y = _ACTS[self.activation](y)
             return y
+        if x.is_cuda and ctx.native and self.filters % 8 == 0 and os.environ.get("TFDL_CONV", "native") == "native":
+            # general Conv2D on the implicit-GEMM kernels (TMA im2col + tcgen05): any filter size / stride / padding
+            from ..ops import conv as _conv
+
+            pt, pb = self._pads(x.shape[1], self.kernel_size[0], self.strides[0])
+            pl, pr = self._pads(x.shape[2], self.kernel_size[1], self.strides[1])
+            pads = (pt, pl, pb, pr)
+            y = None
+            if x.shape[-1] % 8 == 0:
+                y = _conv.conv2d(x, ctx.param(self.kernel), b, self.strides, pads, None if fused_act == "linear" else fused_act)
+            elif not x.requires_grad and self.kernel_size[0] * self.kernel_size[1] * x.shape[-1] <= 512:
+                y = _conv.conv2d_small_cin(x, ctx.param(self.kernel), b, self.strides, pads,
+                                           None if fused_act == "linear" else fused_act)
+            if y is not None:
+                return post(y) if post else y
         w = ctx.param(self.kernel).permute(0, 3, 1, 2)  # OHWI storage viewed as OIHW (channels_last strides)
         xin = x.permute(0, 3, 1, 2)
         pad = (0, 0)
@@ -270,6 +291,8 @@ class Conv2D(Layer):
         if ctx.compute_dtype != torch.float32:
             xin, w = xin.to(ctx.compute_dtype), w.to(ctx.compute_dtype)
             b = b.to(ctx.compute_dtype) if b is not None else None
+        elif xin.dtype != w.dtype:  # bf16 activations from a native layer upstream
+            xin = xin.to(w.dtype)
         y = F.conv2d(xin, w, b, stride=self.strides, padding=pad).permute(0, 2, 3, 1)
         act = _ACTS[self.activation]
         return act(y) if act else y
@@ -292,6 +315,16 @@ class MaxPooling2D(Layer):
         return ((h - self.pool_size[0]) // self.strides[0] + 1, (w - self.pool_size[1]) // self.strides[1] + 1, c)
 
     def call(self, x: torch.Tensor, ctx: CallContext) -> torch.Tensor:
+        if type(self) is MaxPooling2D and ctx.native:
+            from ..ops import pool as _pool
+
+            if _pool.supported(x) and self.pool_size[0] * self.pool_size[1] <= 255:
+                oh, ow, _ = self.compute_output_shape(tuple(x.shape[1:]))
+                pt = pl = 0
+                if self.padding == "same":
+                    pt = max((oh - 1) * self.strides[0] + self.pool_size[0] - x.shape[1], 0) // 2
+                    pl = max((ow - 1) * self.strides[1] + self.pool_size[1] - x.shape[2], 0) // 2
+                return _pool.max_pool(x, self.pool_size, self.strides, (pt, pl), (oh, ow))
         xin = x.permute(0, 3, 1, 2)
         if self.padding == "same":
             oh, ow, _ = self.compute_output_shape(tuple(x.shape[1:]))
@@ -311,6 +344,11 @@ class GlobalAveragePooling2D(Layer):
         return (input_shape[2],)
 
     def call(self, x: torch.Tensor, ctx: CallContext) -> torch.Tensor:
+        if ctx.native:
+            from ..ops import pool as _pool
+
+            if _pool.supported(x) and (x.shape[-1] <= 2048 or x.shape[-1] % 2048 == 0):
+                return _pool.global_avg_pool(x)
         return x.mean(dim=(1, 2))
 
 
@@ -350,7 +388,7 @@ class Dense(Layer):
         assert self.kernel is not None
         w = ctx.param(self.kernel)
         b = ctx.param(self.bias) if self.bias is not None else None
-        if (x.is_cuda and ctx.compute_dtype == torch.bfloat16 and self.activation in (None, "linear", "relu", "gelu")
+        if (x.is_cuda and ctx.native and self.activation in (None, "linear", "relu", "gelu")
                 and x.shape[-1] % 8 == 0 and self.units % 8 == 0 and (x.numel() // x.shape[-1]) % 8 == 0):
             # mixed_bfloat16 on a B200: forward, input-gradient and weight-gradient GEMMs on the persistent
             # TMA + tcgen05 kernel (ops/gemm.py), fp32 master weights and fp32 weight gradients
@@ -360,6 +398,8 @@ class Dense(Layer):
         if ctx.compute_dtype != torch.float32:
             x, w = x.to(ctx.compute_dtype), w.to(ctx.compute_dtype)
             b = b.to(ctx.compute_dtype) if b is not None else None
+        elif x.dtype != w.dtype:  # bf16 activations from a native layer upstream
+            x = x.to(w.dtype)
         y = F.linear(x, w, b)
         act = _ACTS[self.activation]
         return act(y) if act else y
