@@ -207,6 +207,102 @@ def run_ours(args) -> dict:
     return out if rank == 0 else {}
 
 
+MODEL_CFG = {
+    "resnet50": {"metric": "images/sec (device-timed, max over ranks)", "unit": "images/sec", "batch": 256,
+                 "name": "Keras ResNet-50 (25,636,712 parameters), SGD momentum 0.9, synthetic 224x224x3"},
+    "bert": {"metric": "sequences/sec (device-timed, max over ranks)", "unit": "sequences/sec", "batch": 64,
+             "name": "BERT-base MLM (12 layers, hidden 768, vocab 30522), SGD, synthetic sequences of 128 tokens"},
+}
+
+
+def run_model(args) -> dict:
+    """BASELINE.json configs 3 and 4 through the same contract: `--model resnet50|bert`, bf16 (mixed_bfloat16 policy),
+    device-timed steps on device-resident synthetic batches, and model.fit() on host arrays for the end-to-end number."""
+    import numpy as np
+    import torch
+
+    import tfdl
+    from tfdl import keras
+    from tfdl.parallel.values import PerReplica
+
+    cfg = MODEL_CFG[args.model]
+    rank, world, local_rank = _env_world()
+    if world != args.gpus:
+        raise SystemExit(f"--gpus {args.gpus} but WORLD_SIZE={world}: launch N>1 with torch.distributed.run")
+    B = args.batch_per_gpu or cfg["batch"]
+    keras.mixed_precision.set_global_policy("mixed_bfloat16")
+    strategy = tfdl.distribute.MirroredStrategy() if world > 1 else tfdl.distribute.MirroredStrategy(devices=["gpu:0"])
+    dev = strategy.local_devices[0]
+    with strategy.scope():
+        if args.model == "resnet50":
+            from tfdl.models import build_and_compile_resnet50
+
+            model = build_and_compile_resnet50(0.1, 0.9)
+        else:
+            from tfdl.models import build_and_compile_bert_mlm
+
+            model = build_and_compile_bert_mlm(1e-3, optimizer="sgd")
+    rng = np.random.default_rng(7 + rank)
+    n_host = 4  # distinct host batches (ResNet: 154 MB each, so every step's input comes from HBM, not L2)
+    if args.model == "resnet50":
+        xs = [rng.random((B, 224, 224, 3), dtype=np.float32) for _ in range(n_host)]
+        ys = [rng.integers(0, 1000, size=(B,)) for _ in range(n_host)]
+    else:
+        xs = [rng.integers(0, 30522, size=(B, 128)) for _ in range(n_host)]
+        ys = [np.where(rng.random((B, 128)) < 0.15, x, -100) for x in xs]
+    eng = model._make_engine()
+    dbatches = [PerReplica([(torch.from_numpy(x).to(dev), torch.from_numpy(y).to(dev))]) for x, y in zip(xs, ys)]
+    W = max(args.warmup, 5)  # three eager steps precede the step graph's capture
+    for i in range(W):
+        eng.train_step(dbatches[i % n_host])
+    _barrier(world, dev)
+    sampler = ClockSampler(local_rank)
+    sampler.start()
+    e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+    _barrier(world, dev)
+    e0.record()
+    for i in range(args.steps):
+        eng.train_step(dbatches[i % n_host])
+    e1.record()
+    _barrier(world, dev)
+    ms = _max_over_ranks(e0.elapsed_time(e1), world, dev)
+    clocks = sampler.stop()
+    # ---- end to end: fit() on host arrays, one pinned H2D copy of the batch per step, loss read back at the end ----
+    xh, yh = np.concatenate(xs), np.concatenate(ys)
+    reps = -(-args.steps // n_host)
+    ds = tfdl.data.Dataset.from_tensor_slices((xh, yh)).batch(B * world).repeat(reps + 1)
+    opts = tfdl.data.Options()
+    opts.experimental_distribute.auto_shard_policy = tfdl.data.AutoShardPolicy.OFF
+    ds = ds.with_options(opts)
+    model.fit(ds, epochs=1, steps_per_epoch=2, verbose=0)
+    _barrier(world, dev)
+    t0 = time.perf_counter()
+    hist = model.fit(ds, epochs=1, steps_per_epoch=args.steps, verbose=0)
+    _barrier(world, dev)
+    e2e_ms = _max_over_ranks((time.perf_counter() - t0) * 1e3, world, dev)
+    gb = B * world
+    fused = getattr(eng, "_fused", None)
+    out = {
+        "metric": cfg["metric"], "value": round(gb * args.steps / (ms / 1e3), 1), "unit": cfg["unit"], "n_gpus": world,
+        "steps": args.steps, "warmup": W, "ms_per_step": round(ms / args.steps, 4), "higher_is_better": True,
+        "scaling": "weak", "vs_baseline": None, "dtype": "bf16", "data": "synthetic",
+        "config": {"model": cfg["name"], "global_batch": gb, "per_gpu_batch": B, "parallelism": f"dp{world}",
+                   "engine": type(eng).__name__, "fused_allreduce_sgd": fused is not None,
+                   "buckets": getattr(eng, "bucket_info", None),
+                   "l2_policy": "inputs and activations far larger than L2 (126 MB): every step streams from HBM",
+                   "optimizer_step_in_timed_region": True},
+        "clocks": clocks,
+        "e2e": {"value": round(gb * args.steps / (e2e_ms / 1e3), 1), "unit": cfg["unit"],
+                "ms_per_step": round(e2e_ms / args.steps, 4), "api": "model.fit(dataset, steps_per_epoch=K)",
+                "h2d_bytes_per_step": int(xs[0].nbytes + ys[0].nbytes), "d2h_bytes_per_step": 8,
+                "final_loss": float(hist.history["loss"][-1])},
+        "gpu_launches": int(getattr(eng, "launches_per_step", 0) * args.steps),
+        "impl": "tfdl",
+    }
+    strategy.close()
+    return out if rank == 0 else {}
+
+
 def run_standin(args) -> dict:
     """Stand-in baseline (NOT the reference): the same model on PyTorch library kernels (cuDNN / cuBLAS, bf16 autocast,
     channels_last) with an NCCL all-reduce of one flat gradient bucket, the WHOLE step (zero grads, forward, backward,
@@ -308,15 +404,26 @@ def main() -> None:
     ap.add_argument("--steps", type=int, default=2000)
     ap.add_argument("--warmup", type=int, default=50)
     ap.add_argument("--impl", default="tfdl", choices=["tfdl", "reference", "standin"])
-    ap.add_argument("--batch-per-gpu", type=int, default=64)
+    ap.add_argument("--batch-per-gpu", type=int, default=0, help="0 = the config's batch (64 CNN, 256 ResNet-50, 64 BERT)")
+    ap.add_argument("--model", default="cnn", choices=["cnn", "resnet50", "bert"],
+                    help="cnn = the reference model (BASELINE.json config 2, the headline); resnet50 / bert = configs 3 / 4")
     args = ap.parse_args()
+    if args.model == "cnn" and not args.batch_per_gpu:
+        args.batch_per_gpu = 64
+    if args.model != "cnn" and args.steps == 2000:
+        args.steps, args.warmup = 20, 5
     if args.impl == "reference":
         print(json.dumps({"impl": "reference",
                           "unavailable": "the reference is a TensorFlow 2.x script: /root/reference has no setup.py/"
                                          "pyproject (pip install fails) and no tensorflow/keras/tfds wheel exists in "
                                          "/opt/wheelhouse or the image"}))
         return
-    out = run_standin(args) if args.impl == "standin" else run_ours(args)
+    if args.model != "cnn":
+        if args.impl == "standin":
+            raise SystemExit("the ResNet-50 / BERT stand-ins live in tools/bench_models.py --impl standin")
+        out = run_model(args)
+    else:
+        out = run_standin(args) if args.impl == "standin" else run_ours(args)
     if out:
         print(json.dumps(out), flush=True)
     try:  # leave the process group cleanly so the JSON line is the last line of output

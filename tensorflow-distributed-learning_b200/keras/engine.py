@@ -534,6 +534,12 @@ class TorchEngine:
         self._graphs: Dict[Any, Any] = {}
         self._graph_seen: Dict[Any, int] = {}
         self._graph_off = False
+        self._buckets: List[Any] = []        # (FusedState view, algo) in reverse layer order
+        self._bucket_of: Dict[int, int] = {}  # id(variable) -> bucket number
+        self._bucket_left: List[int] = []
+        self._bucket_need: List[int] = []
+        self._comm_stream: Any = None
+        self.launches_per_step = 0
         ops = self.strategy.cross_device_ops
         if (type(ops).__name__ == "P2PFusedAllReduce" and isinstance(model.optimizer, _optimizers.SGD)
                 and len(self.devices) == 1 and os.environ.get("TFDL_TORCH_FUSED_AR", "1") == "1"):
@@ -548,6 +554,7 @@ class TorchEngine:
 
             st.torch_algo = AR_ONESHOT if ops.world == 1 else (AR_MULTIMEM if st.has_multicast else AR_TWOSHOT)
             self._fused = st
+            self._make_buckets(ops)
         for r, arena in enumerate(model.arenas):
             d: Dict[int, torch.Tensor] = {}
             for w in model.weights:
@@ -555,8 +562,68 @@ class TorchEngine:
                 if w.trainable:
                     leaf.requires_grad_(True)
                     leaf.grad = w.grad(r)
+                    if r == 0 and id(w) in self._bucket_of:
+                        leaf.register_post_accumulate_grad_hook(lambda _t, _i=id(w): self._grad_ready(_i))
                 d[id(w)] = leaf
             self.leaves.append(d)
+
+    # ---- gradient buckets reduced while backward is still running ----------------------------------------------
+    # The reference reduces ONE packed buffer after the whole backward pass (num_packs=1, no overlap). Here
+    # the arena is cut into buckets in reverse layer order; when the last gradient of a bucket has been accumulated
+    # (post-accumulate-grad hooks count them down) the bucket's fused all-reduce + update kernel is queued on a
+    # communication stream and runs next to the rest of backward. Updating a bucket's weights early is safe: every
+    # backward op that reads them has been queued before the hook fires. The whole arrangement is captured in the step's
+    # CUDA graph, so the hooks only run while capturing and in the eager warm-up steps.
+    def _make_buckets(self, ops: Any) -> None:
+        if ops.world == 1 or os.environ.get("TFDL_TORCH_BUCKETS", "1") != "1":
+            return
+        target = int(float(os.environ.get("TFDL_BUCKET_MB", "32")) * (1 << 20)) // 4  # elements
+        ws = [w for w in self.model.weights]
+        n = self._fused.n
+        cuts, hi = [], n
+        for w in reversed(ws):
+            if hi - w.spec.offset >= target and w.spec.offset > 0:
+                cuts.append((w.spec.offset, hi))
+                hi = w.spec.offset
+        cuts.append((0, hi))
+        if len(cuts) < 2:
+            return
+        from ..ops.allreduce import pick_algo
+        from ..ops.structs import AR_MULTIMEM, AR_PUSH, AR_PUSH2, AR_TWOSHOT
+
+        for k, (lo, hi) in enumerate(cuts):
+            b = self._fused.bucket(lo, hi - lo)
+            algo = pick_algo((hi - lo) * 4, ops.world, b.has_multicast)
+            if algo not in (AR_PUSH, AR_PUSH2, AR_MULTIMEM, AR_TWOSHOT):  # one gradient buffer: no barrier-less pull
+                algo = AR_MULTIMEM if b.has_multicast else AR_TWOSHOT
+            b.ensure_inbox(algo)
+            self._buckets.append((b, algo))
+            need = 0
+            for w in ws:
+                if lo <= w.spec.offset < hi and w.trainable:
+                    self._bucket_of[id(w)] = k
+                    need += 1
+            self._bucket_need.append(need)
+        self._comm_stream = torch.cuda.Stream(self.devices[0])
+        self.bucket_info = [{"elements": hi - lo, "algo": int(a)} for (lo, hi), (_, a) in zip(cuts, self._buckets)]
+
+    def _fire_bucket(self, k: int) -> None:
+        b, algo = self._buckets[k]
+        cur = torch.cuda.current_stream(self.devices[0])
+        ev = torch.cuda.Event()
+        ev.record(cur)
+        self._comm_stream.wait_event(ev)
+        with torch.cuda.stream(self._comm_stream):
+            b.step(0, algo)
+        self._bucket_left[k] = -1
+
+    def _grad_ready(self, var_id: int) -> None:
+        k = self._bucket_of.get(var_id)
+        if k is None or not self._bucket_left or self._bucket_left[k] <= 0:
+            return
+        self._bucket_left[k] -= 1
+        if self._bucket_left[k] == 0:
+            self._fire_bucket(k)
 
     def _ctx(self, r: int, training: bool) -> CallContext:
         leaves = self.leaves[r]
@@ -616,7 +683,8 @@ class TorchEngine:
             opt = self.model.optimizer
             if self._fused_lr != opt.learning_rate:
                 self._fused_lr = opt.learning_rate
-                self._fused.set_hyper(opt.learning_rate, opt.momentum, opt.nesterov, 1.0)
+                for st in [self._fused] + [b for b, _ in self._buckets]:
+                    st.set_hyper(opt.learning_rate, opt.momentum, opt.nesterov, 1.0)
 
     def _train_step_graphed(self, xt: torch.Tensor, yt: torch.Tensor) -> None:
         opt = self.model.optimizer
@@ -634,8 +702,12 @@ class TorchEngine:
                 sx, sy = xt.clone(), yt.clone()
                 torch.cuda.synchronize(self.devices[0])
                 graph = torch.cuda.CUDAGraph()
+                from ..ops import _lib as _nl
+
+                calls0 = _nl.native_calls
                 with torch.cuda.graph(graph):
                     self._step_body([(sx, sy)])
+                self.launches_per_step = _nl.native_calls - calls0  # native entry points captured in one step
                 ent = self._graphs[key] = (graph, sx, sy)
             except Exception as e:  # an op that cannot be captured: stay eager for this engine
                 self._graph_off = True
@@ -658,6 +730,8 @@ class TorchEngine:
         for r, item in enumerate(per_replica):
             arena = m.arenas[r]
             arena.grads.zero_()
+            if self._buckets and r == 0:
+                self._bucket_left = list(self._bucket_need)
             if item is None:
                 continue
             xt, yt = item
@@ -675,7 +749,14 @@ class TorchEngine:
                     met.update_state(yt, pred.detach(), r)
         if self._fused is not None:
             with nvtx_range("tfdl/allreduce+sgd"):
-                self._fused.step(0, self._fused.torch_algo)
+                if self._buckets:
+                    for k in range(len(self._buckets)):  # buckets whose variables saw no gradient this step
+                        if self._bucket_left[k] >= 0:
+                            self._fire_bucket(k)
+                    torch.cuda.current_stream(self.devices[0]).wait_stream(self._comm_stream)
+                    self._bucket_left = []
+                else:
+                    self._fused.step(0, self._fused.torch_algo)
             return
         with nvtx_range("tfdl/allreduce"):
             s.cross_device_ops.allreduce_grads([a.grads for a in m.arenas])

@@ -59,7 +59,12 @@ def kernels_available() -> bool:
     return os.path.exists(os.path.join(_NATIVE, "libtfdl_kernels.so"))
 
 
+native_calls = 0  # entry points of libtfdl_kernels.so invoked so far (each launches at least one kernel)
+
+
 def check(rc: int, what: str = "") -> None:
+    global native_calls
+    native_calls += 1
     if rc != 0:
         msg = kernels().tfdl_last_error().decode(errors="replace")
         raise NativeError(f"{what or 'native call'} failed (rc={rc}): {msg}")

@@ -41,7 +41,7 @@ def test_bert_small_native_path_tracks_fp32(monkeypatch):
         ids = rng.integers(0, 1003, size=(8, 128))
         batches.append((ids, np.where(rng.random((8, 128)) < 0.15, ids, -100)))
     native, eng = _train(build, batches, "mixed_bfloat16", monkeypatch)
-    ref, _ = _train(build, batches, "float32", monkeypatch, {"TFDL_TORCH_GRAPH": "0"})
+    ref, _ = _train(build, batches, "float32", monkeypatch, {"TFDL_TORCH_GRAPH": "0", "TFDL_NATIVE_OPS": "0"})
     assert eng == "TorchEngine" and all(np.isfinite(native))
     np.testing.assert_allclose(native, ref, rtol=6e-2, atol=5e-2)
 
@@ -54,7 +54,7 @@ def test_resnet50_small_images_native_path_tracks_fp32(monkeypatch):
     build = lambda: build_and_compile_resnet50(1e-3, 0.0, classes=16, input_shape=(64, 64, 3))  # noqa: E731
     native, eng = _train(build, batches, "mixed_bfloat16", monkeypatch)
     eager, _ = _train(build, batches, "mixed_bfloat16", monkeypatch, {"TFDL_TORCH_GRAPH": "0"})
-    ref, _ = _train(build, batches, "float32", monkeypatch, {"TFDL_TORCH_GRAPH": "0"})
+    ref, _ = _train(build, batches, "float32", monkeypatch, {"TFDL_TORCH_GRAPH": "0", "TFDL_NATIVE_OPS": "0"})
     assert eng == "TorchEngine" and all(np.isfinite(native))
     # ResNet-50 at initialisation with batch statistics over 16 images is chaotic: the summation order of the fp32
     # atomics moves a mean by 1e-7, that flips bf16 roundings, and 53 normalised layers amplify it to a few percent in
@@ -63,3 +63,39 @@ def test_resnet50_small_images_native_path_tracks_fp32(monkeypatch):
     np.testing.assert_allclose(native[:3], eager[:3], rtol=0.25, atol=0.2)
     np.testing.assert_allclose(native[:3], ref[:3], rtol=0.25, atol=0.2)
     assert all(0.5 < v < 12 for v in native)
+
+
+def test_modified_reference_cnn_stays_on_native_kernels(monkeypatch):
+    """The reference CNN with filters=48 and padding='same' (tf_dist_example.py:41-44 with other arguments) has no fused
+    step program, but every Conv2D / MaxPooling2D / Dense still runs on the sm_100a kernels - under the DEFAULT float32
+    policy, like the reference script - and tracks the fp32 library path."""
+    from tfdl import keras
+    from tfdl.ops import conv as conv_ops, pool as pool_ops
+
+    calls = {"conv": 0, "small": 0, "pool": 0}
+    for name, key, mod in (("conv2d", "conv", conv_ops), ("conv2d_small_cin", "small", conv_ops), ("max_pool", "pool", pool_ops)):
+        orig = getattr(mod, name)
+
+        def wrapped(*a, _orig=orig, _key=key, **k):
+            calls[_key] += 1
+            return _orig(*a, **k)
+
+        monkeypatch.setattr(mod, name, wrapped)
+
+    def build():
+        m = keras.Sequential([
+            keras.layers.Conv2D(48, 3, activation="relu", padding="same", input_shape=(28, 28, 1)),
+            keras.layers.MaxPooling2D(), keras.layers.Conv2D(48, 3, activation="relu", padding="same"),
+            keras.layers.MaxPooling2D(), keras.layers.Flatten(), keras.layers.Dense(128, activation="relu"),
+            keras.layers.Dense(16)])
+        m.compile(loss=keras.losses.SparseCategoricalCrossentropy(from_logits=True),
+                  optimizer=keras.optimizers.SGD(learning_rate=0.05), metrics=[keras.metrics.SparseCategoricalAccuracy()])
+        return m
+
+    rng = np.random.default_rng(9)
+    batches = [(rng.random((64, 28, 28, 1), dtype=np.float32), rng.integers(0, 10, size=64)) for _ in range(6)]
+    native, eng = _train(build, batches, "float32", monkeypatch)
+    assert eng == "TorchEngine"
+    assert calls["small"] >= 1 and calls["conv"] >= 1 and calls["pool"] >= 2, calls
+    ref, _ = _train(build, batches, "float32", monkeypatch, {"TFDL_TORCH_GRAPH": "0", "TFDL_NATIVE_OPS": "0"})
+    np.testing.assert_allclose(native, ref, rtol=3e-2, atol=3e-2)
