@@ -7,6 +7,8 @@
 // writes bf16, and hands the accumulator back zeroed. That accumulator is scratch memory: it is neither
 // an input nor an output of the op. tfdl_dense_fwd_splitk takes it from the caller (B*N floats, zero on
 // entry, zero on exit); tfdl_dense_fwd_splitk_static keeps it in a fixed array inside this library.
+#include <atomic>
+#include <string.h>
 #include "common.cuh"
 #include "../../include/tfdl_kernels.h"
 
@@ -55,7 +57,8 @@ static __device__ __align__(256) float g_static_scratch[TFDL_STATIC_SCRATCH_FLOA
 
 static float* static_scratch_for_current_device(int* rc_out) {
   constexpr int kMaxDevices = 64;
-  static float* ptrs[kMaxDevices] = {nullptr};
+  // one slot per device, filled on first use; two threads racing on the same device store the same address
+  static std::atomic<float*> ptrs[kMaxDevices];
   int dev = -1;
   cudaError_t e = cudaGetDevice(&dev);
   if (e != cudaSuccess || dev < 0 || dev >= kMaxDevices) {
@@ -64,7 +67,8 @@ static float* static_scratch_for_current_device(int* rc_out) {
     *rc_out = e == cudaSuccess ? -1 : (int)e;
     return nullptr;
   }
-  if (!ptrs[dev]) {
+  float* cached = ptrs[dev].load(std::memory_order_acquire);
+  if (!cached) {
     float* p = nullptr;
     e = cudaGetSymbolAddress((void**)&p, g_static_scratch);
     if (e != cudaSuccess || !p) {
@@ -73,10 +77,11 @@ static float* static_scratch_for_current_device(int* rc_out) {
       *rc_out = e == cudaSuccess ? -1 : (int)e;
       return nullptr;
     }
-    ptrs[dev] = p;
+    ptrs[dev].store(p, std::memory_order_release);
+    cached = p;
   }
   *rc_out = 0;
-  return ptrs[dev];
+  return cached;
 }
 
 }  // namespace tfdl
@@ -104,4 +109,25 @@ extern "C" int tfdl_dense_fwd_splitk_static(const void* x, const void* w, const 
   // left partial sums), so the part used here is cleared first.
   TFDL_CUDA_OK(cudaMemsetAsync(scratch, 0, sizeof(float) * (size_t)B * N, st));
   return dense_fwd_impl(x, w, bias, out, scratch, B, N, K, relu, k_split, st);
+}
+
+// Diagnostic hook: fills the first n floats of the built-in array with `value` on the current device (stream-ordered).
+// Tests use it to leave the array dirty - NaNs - before a call, to prove the entry point clears what it uses.
+extern "C" int tfdl_static_scratch_fill(float value, int n, void* stream) {
+  TFDL_REQUIRE(n >= 0 && n <= TFDL_STATIC_SCRATCH_FLOATS, "static_scratch_fill: n out of range");
+  int rc = 0;
+  float* scratch = static_scratch_for_current_device(&rc);
+  if (!scratch) return rc;
+  if (n == 0) return 0;
+  if (value == 0.f) {
+    TFDL_CUDA_OK(cudaMemsetAsync(scratch, 0, sizeof(float) * (size_t)n, (cudaStream_t)stream));
+    return 0;
+  }
+  unsigned bits;
+  memcpy(&bits, &value, 4);
+  // every float gets the same 32-bit pattern; a byte memset only works for patterns of four equal bytes (0xFF.. = NaN)
+  TFDL_REQUIRE(((bits >> 24) & 0xFF) == (bits & 0xFF) && ((bits >> 16) & 0xFF) == (bits & 0xFF) &&
+               ((bits >> 8) & 0xFF) == (bits & 0xFF), "static_scratch_fill: only 0 and byte-uniform patterns (e.g. NaN 0xFFFFFFFF)");
+  TFDL_CUDA_OK(cudaMemsetAsync(scratch, (int)(bits & 0xFF), sizeof(float) * (size_t)n, (cudaStream_t)stream));
+  return 0;
 }

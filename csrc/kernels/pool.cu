@@ -171,6 +171,52 @@ __global__ void __launch_bounds__(256) scatter_strided_kernel(const uint4* __res
   }
 }
 
+// Patch matrix of a convolution whose input has few channels (the 1- or 3-channel first layer of an image model):
+// cols[m][k], m = output pixel, k = (r*S + s)*C + c, zero-padded to kp columns. One thread per 16-byte chunk of the
+// output; the input window is re-read through L1/L2. IN_F32: the input is still fp32 (cast fused into the gather).
+template <bool IN_F32>
+__global__ void __launch_bounds__(256) im2col_small_kernel(const void* __restrict__ xin, uint4* __restrict__ cols, PoolGeom g,
+                                                           int kp) {
+  const int chunks = kp >> 3;
+  const long total = (long)g.N * g.P * g.Q * chunks;
+  const int K = g.R * g.S * g.C, SC = g.S * g.C;
+  for (long i = (long)blockIdx.x * blockDim.x + threadIdx.x; i < total; i += (long)gridDim.x * blockDim.x) {
+    const int j = (int)(i % chunks);
+    long pix = i / chunks;
+    const int q = (int)(pix % g.Q);
+    pix /= g.Q;
+    const int p = (int)(pix % g.P), n = (int)(pix / g.P);
+    const int h0 = p * g.sh - g.pt, w0 = q * g.sw - g.pl;
+    float f[8];
+    // decode the first column of the chunk once, then walk (c, s, r) incrementally: no division per element
+    int k = j * 8;
+    int r = k / SC, rem = k - r * SC;
+    int sx = rem / g.C, c = rem - sx * g.C;
+    const long img = (long)n * g.H;
+#pragma unroll
+    for (int e = 0; e < 8; ++e, ++k) {
+      float v = 0.f;
+      if (k < K) {
+        const int h = h0 + r, w = w0 + sx;
+        if (h >= 0 && h < g.H && w >= 0 && w < g.W) {
+          const long o = ((img + h) * g.W + w) * g.C + c;
+          v = IN_F32 ? __ldg(static_cast<const float*>(xin) + o)
+                     : __bfloat162float(static_cast<const __nv_bfloat16*>(xin)[o]);
+        }
+      }
+      f[e] = v;
+      if (++c == g.C) {
+        c = 0;
+        if (++sx == g.S) {
+          sx = 0;
+          ++r;
+        }
+      }
+    }
+    cols[i] = pack8(f);
+  }
+}
+
 static int grid_for(long total) {
   long b = (total + 255) / 256;
   return (int)(b < 1 ? 1 : (b > 148 * 16 ? 148 * 16 : b));
@@ -229,6 +275,19 @@ extern "C" int tfdl_scatter_strided_nhwc(const void* src, void* dst, int N, int 
   PoolGeom g{N, H, W, C, P, Q, 1, 1, stride_h, stride_w, 0, 0};
   const long total = (long)N * H * W * (C / 8);
   scatter_strided_kernel<<<grid_for(total), 256, 0, (cudaStream_t)stream>>>((const uint4*)src, (uint4*)dst, g);
+  TFDL_CUDA_OK(cudaGetLastError());
+  return 0;
+}
+
+extern "C" int tfdl_im2col_small(const void* x, int x_is_f32, void* cols, int N, int H, int W, int C, int R, int S,
+                                 int stride_h, int stride_w, int pad_t, int pad_l, int P, int Q, int kp, void* stream) {
+  TFDL_REQUIRE(N > 0 && C > 0 && R > 0 && S > 0 && P > 0 && Q > 0 && kp % 8 == 0 && kp >= R * S * C,
+               "im2col_small: kp must be a multiple of 8 and at least R*S*C");
+  TFDL_REQUIRE(((uintptr_t)cols & 15) == 0, "im2col_small: cols must be 16-byte aligned");
+  PoolGeom g{N, H, W, C, P, Q, R, S, stride_h, stride_w, pad_t, pad_l};
+  const long total = (long)N * P * Q * (kp / 8);
+  if (x_is_f32) im2col_small_kernel<true><<<grid_for(total), 256, 0, (cudaStream_t)stream>>>(x, (uint4*)cols, g, kp);
+  else im2col_small_kernel<false><<<grid_for(total), 256, 0, (cudaStream_t)stream>>>(x, (uint4*)cols, g, kp);
   TFDL_CUDA_OK(cudaGetLastError());
   return 0;
 }

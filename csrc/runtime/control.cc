@@ -78,6 +78,10 @@ struct Group {
   std::vector<int> hb;    // same indexing
   std::thread hb_thread;
   std::atomic<int> failed_rank{-1};
+  // host-visible word that device kernels poll inside their spin loops (pinned, device-mapped memory owned by the
+  // caller): the heartbeat thread stores failed_rank + 1 there the moment a peer is declared dead, which releases every
+  // kernel waiting for that peer's gradients instead of letting it spin into its trap limit
+  std::atomic<uint32_t*> abort_word{nullptr};
   std::atomic<bool> stop{false};
   std::mutex ctrl_mu;
   std::vector<char> scratch;
@@ -190,10 +194,14 @@ void heartbeat_loop(Group* g) {
   const bool leader = g->rank == 0;
   std::vector<int64_t> last(g->world, now_ms());
   std::vector<bool> quit(g->world, false);
+  std::vector<bool> want_rank(g->world, false);  // an 'F' was the last byte of a recv: its rank byte comes next
   int64_t last_ping = 0;
   int announced = -1;
   while (!g->stop.load()) {
     int64_t t = now_ms();
+    if (int f = g->failed_rank.load(); f >= 0) {
+      if (uint32_t* w = g->abort_word.load()) *reinterpret_cast<volatile uint32_t*>(w) = (uint32_t)f + 1u;
+    }
     if (!leader && t - last_ping >= g->hb_interval_ms) {
       char c = 'P';
       if (::send(g->hb[0], &c, 1, MSG_NOSIGNAL | MSG_DONTWAIT) < 0 && errno != EAGAIN && errno != EWOULDBLOCK) {
@@ -227,10 +235,19 @@ void heartbeat_loop(Group* g) {
         if (r > 0) {
           last[peer] = now_ms();
           for (ssize_t k = 0; k < r; ++k) {
+            if (want_rank[peer]) {  // second byte of a failure notice whose 'F' ended the previous recv
+              want_rank[peer] = false;
+              if (g->failed_rank.load() < 0) g->failed_rank = (unsigned char)buf[k];
+              continue;
+            }
             if (buf[k] == 'Q') quit[peer] = true;  // graceful goodbye
-            if (buf[k] == 'F' && k + 1 < r) {      // failure notice from the leader: next byte = rank
-              if (g->failed_rank.load() < 0) g->failed_rank = (unsigned char)buf[k + 1];
-              ++k;
+            if (buf[k] == 'F') {                   // failure notice from the leader: next byte = rank
+              if (k + 1 < r) {
+                if (g->failed_rank.load() < 0) g->failed_rank = (unsigned char)buf[k + 1];
+                ++k;
+              } else {
+                want_rank[peer] = true;
+              }
             }
           }
         } else if (r == 0 || (errno != EAGAIN && errno != EWOULDBLOCK && errno != EINTR)) {
@@ -363,6 +380,11 @@ extern "C" void tfdl_rt_group_destroy(void* h) { delete static_cast<Group*>(h); 
 extern "C" int tfdl_rt_group_rank(void* h) { return static_cast<Group*>(h)->rank; }
 extern "C" int tfdl_rt_group_world(void* h) { return static_cast<Group*>(h)->world; }
 extern "C" int tfdl_rt_group_failed_rank(void* h) { return static_cast<Group*>(h)->failed_rank.load(); }
+extern "C" void tfdl_rt_group_set_abort_word(void* h, uint32_t* word) {
+  auto* g = static_cast<Group*>(h);
+  g->abort_word.store(word);
+  if (int f = g->failed_rank.load(); f >= 0 && word) *reinterpret_cast<volatile uint32_t*>(word) = (uint32_t)f + 1u;
+}
 extern "C" void tfdl_rt_group_set_timeout(void* h, int ms) { static_cast<Group*>(h)->timeout_ms = ms; }
 extern "C" uint64_t tfdl_rt_group_bytes_sent(void* h) { return static_cast<Group*>(h)->bytes_sent; }
 

@@ -65,6 +65,9 @@ int tfdl_dense_fwd_splitk(const void* x_bf16, const void* w_bf16, const float* b
 #define TFDL_STATIC_SCRATCH_FLOATS 65536
 int tfdl_dense_fwd_splitk_static(const void* x_bf16, const void* w_bf16, const float* bias, void* out_bf16, int B,
                                  int N, int K, int relu, int k_split, void* stream);
+/* Diagnostic: fill the first n floats of that built-in array with 0 or with a byte-uniform pattern such as the NaN
+ * 0xFFFFFFFF (stream-ordered, current device). Tests dirty the array with it before a call. */
+int tfdl_static_scratch_fill(float value, int n, void* stream);
 
 /* D[M,N] = act(A[M,K] * B[N,K]^T + bias): persistent warp-specialised TMA + tcgen05 kernel
  * (128B-swizzled tiles, 4-8 stage mbarrier ring, double-buffered TMEM accumulators).
@@ -155,6 +158,11 @@ int tfdl_global_avgpool_fwd(const void* x, void* y, int N, int HW, int C, void* 
 int tfdl_global_avgpool_bwd(const void* dy, void* dx, int N, int HW, int C, void* stream);
 int tfdl_scatter_strided_nhwc(const void* src, void* dst, int N, int H, int W, int C, int P, int Q, int stride_h,
                               int stride_w, void* stream);
+/* Patch matrix for a convolution over few input channels (the first layer of an image model; ref: tf_dist_example.py:41,
+ * Conv2D over a 1-channel image): cols[N*P*Q][kp] bf16, column (r*S+s)*C+c, zero-padded to kp (multiple of 8). The input is
+ * NHWC fp32 (x_is_f32) or bf16. The convolution is then a plain GEMM of cols with the [K][kp] weight matrix. */
+int tfdl_im2col_small(const void* x, int x_is_f32, void* cols, int N, int H, int W, int C, int R, int S, int stride_h,
+                      int stride_w, int pad_t, int pad_l, int P, int Q, int kp, void* stream);
 
 /* ---- fused gradient all-reduce + SGD over NVLink peer memory ------------------------------
  * ref: README.md:17,21,23,67 (NcclAllReduce / CollectiveOps after every batch) and

@@ -47,6 +47,9 @@ void tfdl_rt_group_destroy(void* group);
 int tfdl_rt_group_rank(void* group);
 int tfdl_rt_group_world(void* group);
 int tfdl_rt_group_failed_rank(void* group); /* -1 while everyone is alive */
+/* word: a uint32 in pinned, device-mapped host memory that GPU kernels poll in their spin loops. The heartbeat thread
+ * stores failed_rank + 1 into it as soon as a peer is declared dead (NULL detaches it before the memory is freed). */
+void tfdl_rt_group_set_abort_word(void* group, uint32_t* word);
 void tfdl_rt_group_set_timeout(void* group, int ms);
 uint64_t tfdl_rt_group_bytes_sent(void* group);
 int tfdl_rt_barrier(void* group);

@@ -152,11 +152,20 @@ def _write_bundle(model: Any, prefix: str, include_optimizer: bool, extra: Optio
     os.replace(tmp, os.path.join(d, "checkpoint"))
 
 
+def _sync_slots(model: Any) -> None:
+    """Every worker takes part in a save: optimizer slots that the sliced NVLink all-reduce paths keep
+    distributed over the ranks are made whole before the chief reads them."""
+    sync = getattr(model.strategy.cross_device_ops, "sync_optimizer_slots", None)
+    if sync is not None and model.optimizer is not None and getattr(model.optimizer, "_slots", None):
+        sync()
+
+
 def save_model_weights(model: Any, filepath: str, save_format: Optional[str] = None) -> None:
     """Chief writes; everyone synchronises afterwards so no worker races ahead of the file."""
     model._finalize()
     strategy = model.strategy
     fmt = save_format or ("npz" if filepath.endswith(".npz") else "tf")
+    _sync_slots(model)
     if strategy.is_chief:
         if fmt == "npz":
             names = [w.name for w in model.weights]
@@ -207,10 +216,16 @@ def save_training_state(model: Any, prefix: str, epoch: int) -> None:
     """Backup for BackupAndRestore: weights + optimizer + progress counters."""
     model._finalize()
     s = model.strategy
+    _sync_slots(model)
     if s.is_chief:
+        ds = getattr(model, "_data_state", None) or {"shuffle": [], "batches": 0}
+        shuf = np.array(ds["shuffle"], np.int64).reshape(-1, 2)
         _write_bundle(model, prefix, include_optimizer=True,
                       extra={"_tfdl/epoch": np.array(epoch, np.int64),
-                             "_tfdl/steps_done": np.array(model._steps_done, np.int64)})
+                             "_tfdl/steps_done": np.array(model._steps_done, np.int64),
+                             # the data iterator's position (SURVEY 5.4): seeds of the current pass + steps handed out
+                             "_tfdl/iter_batches": np.array(ds["batches"], np.int64),
+                             "_tfdl/iter_shuffle": shuf if shuf.size else np.zeros((1, 2), np.int64) - 1})
     s.barrier()
 
 
@@ -225,6 +240,10 @@ def load_training_state(model: Any, prefix: str) -> Optional[Dict[str, int]]:
     r = BundleReader(prefix)
     try:
         st = {"epoch": int(r.read("_tfdl/epoch")), "steps_done": int(r.read("_tfdl/steps_done"))}
+        if "_tfdl/iter_batches" in r.entries:
+            shuf = np.asarray(r.read("_tfdl/iter_shuffle")).reshape(-1, 2)
+            shuf = [] if (shuf.size and shuf[0, 0] == -1 and shuf[0, 1] == -1) else [(int(a), int(b)) for a, b in shuf]
+            model._resume_data = {"batches": int(r.read("_tfdl/iter_batches")), "shuffle": shuf}
     finally:
         r.close()
     model._steps_done = st["steps_done"]

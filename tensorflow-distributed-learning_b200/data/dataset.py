@@ -875,6 +875,31 @@ def index_stream(ds: Dataset) -> Optional[Tuple[_Base, Iterator[np.ndarray]]]:
     return node._parent._base(), node.index_batches()
 
 
+def shuffle_nodes(ds: Dataset) -> List["_ShuffleDataset"]:
+    """The shuffle stages of a pipeline, outermost first (their seeds are what makes an iterator reproducible)."""
+    out: List[_ShuffleDataset] = []
+    node: Optional[Dataset] = ds
+    while node is not None:
+        if isinstance(node, _ShuffleDataset):
+            out.append(node)
+        node = getattr(node, "_parent", None)
+    return out
+
+
+def iterator_state(ds: Dataset) -> List[Tuple[int, int]]:
+    """What a NEW iterator over `ds` would be seeded with: (entropy, pass counter) per shuffle stage. Saved with a
+    training backup so that a restarted run can rebuild the same order and skip what was already consumed."""
+    return [(int(n._entropy), int(n._epoch)) for n in shuffle_nodes(ds)]
+
+
+def restore_iterator_state(ds: Dataset, state: Sequence[Tuple[int, int]]) -> None:
+    nodes = shuffle_nodes(ds)
+    if len(nodes) != len(state):
+        raise ValueError(f"saved iterator state has {len(state)} shuffle stages, the dataset has {len(nodes)}")
+    for n, (entropy, epoch) in zip(nodes, state):
+        n._entropy, n._epoch = int(entropy), int(epoch)
+
+
 def find_batch_node(ds: Dataset) -> Optional[_BatchDataset]:
     node: Optional[Dataset] = ds
     while node is not None:

@@ -93,6 +93,8 @@ class Model:
         self._engine_pref = os.environ.get("TFDL_ENGINE", "auto")
         self.history: Optional[History] = None
         self._train_iter: Optional[Iterator[PerReplica]] = None
+        self._data_state: Dict[str, Any] = {"shuffle": [], "batches": 0}  # position of fit()'s data iterator
+        self._resume_data: Optional[Dict[str, Any]] = None                # set by load_training_state
         self._steps_done = 0
         self._input_shape: Optional[Tuple[int, ...]] = None
 
@@ -315,12 +317,25 @@ class Model:
             cbs.on_epoch_begin(epoch)
             t0 = time.time()
             if it is None or steps_per_epoch is None:
+                from ..data import dataset as _dsmod
+
+                resume = self._resume_data
+                self._resume_data = None
+                if resume is not None and steps_per_epoch is not None:
+                    _dsmod.restore_iterator_state(dist.dataset, resume["shuffle"])  # same order as the interrupted run
+                # remembered for backups: the seeds this pass starts from and how many steps it has handed out
+                self._data_state = {"shuffle": _dsmod.iterator_state(dist.dataset), "batches": 0}
                 if idx_mode is not None:
-                    if it is not None:
+                    if it is not None or resume is not None:
                         st = dist.index_stream()  # a new pass over the data: fresh shuffle order
                     it = iter(st[1])
                 else:
                     it = iter(dist)
+                if resume is not None and steps_per_epoch is not None:
+                    for _ in range(int(resume["batches"])):  # skip what the interrupted run already consumed
+                        if next(it, None) is None:
+                            break
+                    self._data_state["batches"] = int(resume["batches"])
             step = 0
             while steps_per_epoch is None or step < steps_per_epoch:
                 want = 1
@@ -346,6 +361,7 @@ class Model:
                         cbs.on_train_batch_begin(step)
                         engine.train_step(group[0])
                     self._steps_done += len(group)
+                    self._data_state["batches"] += len(group)
                     if not chunked:
                         cbs.on_train_batch_end(step, None)
                     step += len(group)
@@ -554,6 +570,7 @@ class TorchEngine:
 
             st.torch_algo = AR_ONESHOT if ops.world == 1 else (AR_MULTIMEM if st.has_multicast else AR_TWOSHOT)
             self._fused = st
+            st.refresh_shadow()
             self._make_buckets(ops)
         for r, arena in enumerate(model.arenas):
             d: Dict[int, torch.Tensor] = {}
@@ -634,7 +651,30 @@ class TorchEngine:
         if self.devices[r].type == "cuda" and self.model._engine_pref != "torch" and \
                 os.environ.get("TFDL_NATIVE_OPS", "1") == "1":
             native = True
-        return CallContext(r, training, lambda v: leaves[id(v)], self.model.compute_dtype, native)
+        ctx = CallContext(r, training, lambda v: leaves[id(v)], self.model.compute_dtype, native)
+        if native and self._fused is not None and r == 0 and os.environ.get("TFDL_TORCH_INPLACE", "1") == "1":
+            ctx.param_lp = self._lp_view
+            ctx.grad_sink = self._sink_for
+        return ctx
+
+    # bf16 copies of the weights come from the shadow arena that the fused all-reduce + update kernel rewrites every step
+    # (no per-layer cast kernels); weight gradients of Conv2D / Dense are written into the gradient arena by the
+    # weight-gradient kernels themselves (no dW tensors, no autograd accumulate pass).
+    def _lp_view(self, v: Any) -> Optional[torch.Tensor]:
+        sh = self._fused.shadow
+        if sh is None or not v.trainable:
+            return None
+        sp = v.spec
+        return sh.tensor[sp.offset:sp.offset + sp.numel].view(sp.storage_shape)
+
+    def _sink_for(self, v: Any) -> Any:
+        if not v.trainable:
+            return None
+        return v.grad(0), (lambda _i=id(v): self._grad_ready(_i))
+
+    def weights_changed(self) -> None:
+        if self._fused is not None and self._fused.shadow is not None:
+            self._fused.refresh_shadow()
 
     def _to_device(self, a: Any, dev: torch.device) -> torch.Tensor:
         t = torch.from_numpy(np.ascontiguousarray(a)) if not isinstance(a, torch.Tensor) else a
@@ -650,6 +690,9 @@ class TorchEngine:
     def train_step(self, batches: PerReplica) -> None:
         m = self.model
         assert m.loss is not None and m.optimizer is not None
+        chk = getattr(self.strategy.cross_device_ops, "check_abort", None)
+        if chk is not None:
+            chk()  # a peer died: the previous step's collective was released, fail here instead of training on
         if self._graph_eligible():
             x, y = self._split(batches[0])
             n = int(np.asarray(x).shape[0]) if not isinstance(x, torch.Tensor) else x.shape[0]

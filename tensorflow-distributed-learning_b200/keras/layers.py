@@ -117,9 +117,20 @@ class CallContext:
         # fp32 master weights - the precision contract of the native step program) whenever the shapes allow it.
         # Default: under the mixed_bfloat16 policy only; the training engine turns it on for CUDA replicas.
         self.native = (compute_dtype == torch.bfloat16) if native is None else bool(native)
+        # Optional services of the training engine (None elsewhere): param_lp(var) -> a current bf16 copy of the variable
+        # (the shadow arena the fused all-reduce refreshes), grad_sink(var) -> (fp32 gradient view in the arena, callback
+        # to run once the gradient is complete) so a kernel can write the weight gradient in place.
+        self.param_lp: Optional[Callable[[MirroredVariable], Optional[torch.Tensor]]] = None
+        self.grad_sink: Optional[Callable[[MirroredVariable], Any]] = None
         # in-place updates of non-trainable variables (BatchNorm statistics) that must wait until autograd
         # has finished: every variable is a view of one arena, so they share a version counter
         self.deferred: List[Callable[[], None]] = []
+
+    def lp(self, var: MirroredVariable) -> Optional[torch.Tensor]:
+        return self.param_lp(var) if self.param_lp is not None else None
+
+    def sink(self, var: MirroredVariable) -> Any:
+        return self.grad_sink(var) if (self.grad_sink is not None and self.training) else None
 
 
 class Layer:
@@ -259,7 +270,9 @@ class Conv2D(Layer):
             from ..ops.gemm import linear
 
             w2 = ctx.param(self.kernel).reshape(self.filters, x.shape[-1])
-            y = linear(x, w2, b, self.activation if self.activation in (None, "relu", "gelu") else None)
+            lp = ctx.lp(self.kernel)
+            y = linear(x, w2, b, self.activation if self.activation in (None, "relu", "gelu") else None,
+                       None if lp is None else lp.reshape(self.filters, x.shape[-1]), ctx.sink(self.kernel))
             if self.activation not in (None, "relu", "gelu"):
                 y = _ACTS[self.activation](y)
             return y
@@ -272,7 +285,8 @@ class Conv2D(Layer):
             pads = (pt, pl, pb, pr)
             y = None
             if x.shape[-1] % 8 == 0:
-                y = _conv.conv2d(x, ctx.param(self.kernel), b, self.strides, pads, None if fused_act == "linear" else fused_act)
+                y = _conv.conv2d(x, ctx.param(self.kernel), b, self.strides, pads, None if fused_act == "linear" else fused_act,
+                                 ctx.lp(self.kernel), ctx.sink(self.kernel))
             elif not x.requires_grad and self.kernel_size[0] * self.kernel_size[1] * x.shape[-1] <= 512:
                 y = _conv.conv2d_small_cin(x, ctx.param(self.kernel), b, self.strides, pads,
                                            None if fused_act == "linear" else fused_act)
@@ -394,7 +408,8 @@ class Dense(Layer):
             # TMA + tcgen05 kernel (ops/gemm.py), fp32 master weights and fp32 weight gradients
             from ..ops.gemm import linear as _tc_linear
 
-            return _tc_linear(x, w, b, None if self.activation == "linear" else self.activation)
+            return _tc_linear(x, w, b, None if self.activation == "linear" else self.activation, ctx.lp(self.kernel),
+                              ctx.sink(self.kernel))
         if ctx.compute_dtype != torch.float32:
             x, w = x.to(ctx.compute_dtype), w.to(ctx.compute_dtype)
             b = b.to(ctx.compute_dtype) if b is not None else None

@@ -485,12 +485,14 @@ class NativeCnnEngine:
         slot, ev = handle
         tw = time.perf_counter()
         ev.synchronize()
+        self.ops.check_abort()
         self.prof["read_wait"] += time.perf_counter() - tw
         t = self._ep_pinned[slot]
         return float(t[0]), float(t[1]), float(t[2])
 
     def last_step_out(self) -> Tuple[float, float]:
         self.stream.synchronize()
+        self.ops.check_abort()
         k = max(1, getattr(self, "_last_k", 1))
         return float(self.host_out[k - 1, 0]), float(self.host_out[k - 1, 1])
 
@@ -498,6 +500,7 @@ class NativeCnnEngine:
     def flush_metrics(self) -> None:
         """Fold the device-side (loss sum, correct, examples) counters into the Keras metric objects."""
         self.stream.synchronize()
+        self.ops.check_abort()
         m = self.metrics_dev.cpu()
         if float(m[2]) == 0.0:
             return

@@ -114,9 +114,16 @@ class P2PFusedAllReduce(CrossDeviceOps):
         if self.world > MAX_RANKS:
             raise RuntimeError(f"the fused NVLink all-reduce supports up to {MAX_RANKS} GPUs per group, got {self.world}")
         _lib.kernels()  # fail loudly on a GPU box without the native library
+        # Abort word: one uint32 in pinned, device-mapped host memory. Every spin loop of the collective kernels polls
+        # it; the control group's heartbeat thread stores failed_rank + 1 there when a peer dies (csrc/runtime/
+        # control.cc), so survivors leave their kernels within the heartbeat timeout and check_abort() raises.
+        self._abort = torch.zeros(1, dtype=torch.int32).pin_memory() if device.type == "cuda" else None
+        if self._abort is not None and self.control is not None and hasattr(self.control, "set_abort_word"):
+            self.control.set_abort_word(self._abort.data_ptr())
         self._arenas: List[SymmetricBuffer] = []
         self._states: Dict[int, "FusedState"] = {}
         self._plain: Dict[Any, "FusedState"] = {}
+        self._fused_states: List["FusedState"] = []  # every updating state / bucket (sync_optimizer_slots)
         self._scalars: Optional[list] = None
 
     # ---- arena allocation hook used by parallel.values.ParamArena -----------------------------
@@ -154,6 +161,7 @@ class P2PFusedAllReduce(CrossDeviceOps):
         order, so every rank reads bit-identical totals. No NCCL call."""
         if self.world == 1:
             return vals
+        self.check_abort()
         v = np.ascontiguousarray(vals, dtype=np.float64).reshape(-1)
         if v.size > 256:  # not a metric read any more: generic path
             t = torch.from_numpy(v.copy()).to(self.device)
@@ -169,7 +177,9 @@ class P2PFusedAllReduce(CrossDeviceOps):
         buf.tensor[par * 256:par * 256 + v.size].copy_(torch.from_numpy(v))
         _lib.check(_lib.kernels().tfdl_allreduce_small_f64(C.byref(st.struct(0)), _lib.ptr(out), int(v.size),
                                                            _lib.cur_stream()), "allreduce_small_f64")
-        return out[:v.size].cpu().numpy().reshape(np.shape(vals))
+        res = out[:v.size].cpu().numpy().reshape(np.shape(vals))
+        self.check_abort()  # a kernel released by the abort word returns garbage: never hand that out as a total
+        return res
 
     def allreduce_scalars_device(self, vals: torch.Tensor) -> torch.Tensor:
         """Sum of <= 256 float64 values over the ranks with input and result on the device, ordered on the current
@@ -190,6 +200,32 @@ class P2PFusedAllReduce(CrossDeviceOps):
         _lib.check(_lib.kernels().tfdl_allreduce_small_f64(C.byref(st.struct(0)), _lib.ptr(out), n, _lib.cur_stream()),
                    "allreduce_small_f64")
         return out[:n].clone()
+
+    def sync_optimizer_slots(self) -> None:
+        """Make every rank's momentum buffer complete (collective: every rank calls it, e.g. before a checkpoint).
+        The sliced paths (two-shot, multimem, push2) update the momentum of a slice only on the rank that owns the
+        slice, so between steps rank r holds slice r of each such bucket; here the slices are gathered - each rank
+        contributes its slice in an otherwise zero buffer and the plain NVLink sum reassembles the whole."""
+        if self.world == 1:
+            return
+        for st in list(self._fused_states):
+            if st.mom is None or st.last_algo not in (AR_TWOSHOT, AR_MULTIMEM, AR_PUSH2):
+                continue
+            n = st.n
+            per = (((n + 3) // 4 + self.world - 1) // self.world) * 4
+            lo, hi = min(n, per * self.rank), min(n, per * (self.rank + 1))
+            if st._gather_tmp is None:
+                buf = SymmetricBuffer(n, torch.float32, self.device, self.world, self.rank)
+                st._gather_tmp = (buf, FusedState(self, None, buf, False, plain=True))
+            buf, plain = st._gather_tmp
+            view = st.mom[st.offset:st.offset + n]
+            buf.tensor.zero_()
+            buf.tensor[lo:hi].copy_(view[lo:hi])
+            torch.cuda.synchronize(self.device)
+            self.dist.barrier()
+            plain.allreduce_sum()
+            view.copy_(buf.tensor)
+        torch.cuda.synchronize(self.device)
 
     def broadcast_params(self, params: Sequence[torch.Tensor]) -> None:
         """Initial values from the chief (tf_dist_example.py:56-57): every other rank copies rank 0's arena over NVLink
@@ -216,8 +252,19 @@ class P2PFusedAllReduce(CrossDeviceOps):
         if self.control is not None:
             self.control.barrier()
 
+    def check_abort(self) -> None:
+        """Raise if a peer has been declared dead (cheap: one read of pinned host memory). Called by the engines
+        whenever they are about to wait for, or have just waited for, the device."""
+        if self._abort is not None and int(self._abort[0]) != 0:
+            from ..runtime.native import CollectiveError
+
+            raise CollectiveError(f"collective aborted: worker rank {int(self._abort[0]) - 1} failed (heartbeat lost); "
+                                  "restart all workers and resume from the last checkpoint")
+
     def close(self) -> None:
         if self.control is not None:
+            if hasattr(self.control, "set_abort_word"):
+                self.control.set_abort_word(0)
             self.control.close()
 
 
@@ -248,6 +295,10 @@ class FusedState:
         self.offset = 0
         self.max_blocks = MAX_BLOCKS
         self.inbox: Optional[SymmetricBuffer] = None
+        self.last_algo: Optional[int] = None
+        self._gather_tmp: Any = None
+        if not plain:
+            ops._fused_states.append(self)
         self._structs = [self._make_struct(par) for par in (0, 1)]
         if W > 1:
             grads0.barrier()  # every rank has zeroed its flags before anyone signals
@@ -270,6 +321,8 @@ class FusedState:
         b.has_multicast = self.has_multicast
         b.algo = pick_algo(length * 4, W, b.has_multicast)
         b.inbox = None
+        b.last_algo, b._gather_tmp = None, None
+        self.ops._fused_states.append(b)
         b._structs = [b._make_struct(par) for par in (0, 1)]
         if W > 1:
             b.flags.barrier()
@@ -321,7 +374,8 @@ class FusedState:
                 p.inbox[r] = self.inbox.ptrs[r]
             p.inbox_bytes = self.inbox.numel * 4
         base = self.counters.data_ptr()
-        p.epoch, p.done, p.abort_word = base, base + 4, base + 8
+        p.epoch, p.done = base, base + 4
+        p.abort_word = self.ops._abort.data_ptr() if self.ops._abort is not None else base + 8
         p.hyper = self.hyper.data_ptr()
         p.parity = parity
         return p
@@ -342,6 +396,7 @@ class FusedState:
         """One fused all-reduce + update on the current stream (eager; the training path captures it)."""
         if algo is not None and algo != self.algo:
             self.ensure_inbox(algo)
+        self.last_algo = self.algo if algo is None else algo
         _lib.check(_lib.kernels().tfdl_fused_allreduce_sgd(C.byref(self._structs[parity]),
                                                            self.algo if algo is None else algo, _lib.cur_stream()),
                    "fused_allreduce_sgd")

@@ -80,47 +80,59 @@ def conv2d_wgrad(x: torch.Tensor, dy: torch.Tensor, w_shape: Tuple[int, ...], st
 
 
 class _Conv2dFn(torch.autograd.Function):
+    """w_lp / sink as in ops/gemm.py:_LinearFn: a ready bf16 copy of the kernel, and a gradient-arena view that the
+    weight-gradient kernel accumulates into directly (TMA reduce-add) instead of returning a tensor to autograd."""
+
     @staticmethod
-    def forward(ctx, x, w, bias, strides, pads, act):
+    def forward(ctx, x, w, bias, strides, pads, act, w_lp=None, sink=None):
         xb = x if x.dtype == torch.bfloat16 else x.bfloat16()
         xb = xb.contiguous()
-        wb = (w if w.dtype == torch.bfloat16 else w.bfloat16()).contiguous()
+        wb = w_lp if w_lp is not None else (w if w.dtype == torch.bfloat16 else w.bfloat16()).contiguous()
         y = conv2d_fwd(xb, wb, None if bias is None else bias.float(), strides, pads, act)
         ctx.save_for_backward(xb, wb, y if act == "relu" else None)
-        ctx.meta = (strides, pads, act, bias is not None, w.dtype, x.requires_grad)
+        ctx.meta = (strides, pads, act, bias is not None, w.dtype, x.requires_grad, sink)
         return y
 
     @staticmethod
     def backward(ctx, dy):
         xb, wb, y = ctx.saved_tensors
-        strides, pads, act, has_bias, w_dtype, need_dx = ctx.meta
+        strides, pads, act, has_bias, w_dtype, need_dx, sink = ctx.meta
         dy = dy if dy.dtype == torch.bfloat16 else dy.bfloat16()
         if act == "relu":
             dy = dy * (y > 0)
         dy = dy.contiguous()
         dx = conv2d_dgrad(dy, wb, tuple(xb.shape), strides, pads) if need_dx else None
-        dw = conv2d_wgrad(xb, dy, tuple(wb.shape), strides, pads)
         db = colsum(dy.reshape(-1, dy.shape[-1])) if has_bias else None
-        return dx, dw.to(w_dtype), db, None, None, None
+        if sink is not None:
+            view, done = sink
+            conv2d_wgrad(xb, dy, tuple(wb.shape), strides, pads, out=view)
+            done()
+            return dx, None, db, None, None, None, None, None
+        dw = conv2d_wgrad(xb, dy, tuple(wb.shape), strides, pads)
+        return dx, dw.to(w_dtype), db, None, None, None, None, None
 
 
 def conv2d(x: torch.Tensor, w: torch.Tensor, bias: Optional[torch.Tensor], strides: Tuple[int, int],
-           pads: Tuple[int, int, int, int], act: Optional[str] = None) -> torch.Tensor:
+           pads: Tuple[int, int, int, int], act: Optional[str] = None, w_lp: Optional[torch.Tensor] = None,
+           sink=None) -> torch.Tensor:
     """Conv2D with autograd on the implicit-GEMM kernels. x NHWC (cast to bf16), w OHWI fp32/bf16."""
-    return _Conv2dFn.apply(x, w, bias, tuple(strides), tuple(pads), act)
+    return _Conv2dFn.apply(x, w, bias, tuple(strides), tuple(pads), act, w_lp, sink)
 
 
 # ---- first layers: C not a multiple of 8 (1 or 3 input channels) -------------------------------------------------------
 def _patches(x: torch.Tensor, R: int, S: int, strides: Tuple[int, int], pads: Tuple[int, int, int, int], kp: int) -> torch.Tensor:
-    """[N*P*Q, kp] bf16 patch matrix (columns (r, s, c), zero-padded to kp): one strided gather, no convolution."""
+    """[N*P*Q, kp] bf16 patch matrix (columns (r, s, c), zero-padded to kp) from an fp32 or bf16 NHWC input: one native
+    gather kernel with the cast fused in (csrc/kernels/pool.cu:im2col_small_kernel)."""
     N, H, W, C = x.shape
     pt, pl, pb, pr = pads
-    xp = torch.nn.functional.pad(x, (0, 0, pl, pr, pt, pb)) if any(pads) else x
     P, Q = out_size(H, R, strides[0], pt, pb), out_size(W, S, strides[1], pl, pr)
-    sn, sh, sw, sc = xp.stride()
-    win = xp.as_strided((N, P, Q, R, S, C), (sn, sh * strides[0], sw * strides[1], sh, sw, sc))
-    out = torch.zeros((N * P * Q, kp), device=x.device, dtype=torch.bfloat16)
-    out[:, :R * S * C] = win.reshape(N * P * Q, R * S * C)
+    if x.dtype not in (torch.float32, torch.bfloat16):
+        x = x.float()
+    x = x.contiguous()
+    out = torch.empty((N * P * Q, kp), device=x.device, dtype=torch.bfloat16)
+    _lib.check(_lib.kernels().tfdl_im2col_small(_lib.ptr(x), int(x.dtype == torch.float32), _lib.ptr(out), N, H, W, C, R, S,
+                                                strides[0], strides[1], pt, pl, P, Q, kp, _lib.cur_stream()),
+               "im2col_small")
     return out
 
 
@@ -129,8 +141,7 @@ class _ConvSmallCinFn(torch.autograd.Function):
     def forward(ctx, x, w, bias, strides, pads, act):
         K, R, S, C = w.shape
         kp = (R * S * C + 7) // 8 * 8
-        xb = x if x.dtype == torch.bfloat16 else x.bfloat16()
-        cols = _patches(xb, R, S, strides, pads, kp)
+        cols = _patches(x, R, S, strides, pads, kp)
         wm = torch.zeros((K, kp), device=w.device, dtype=torch.bfloat16)
         wm[:, :R * S * C] = w.reshape(K, R * S * C)
         y = gemm_tma(cols, wm, bias=None if bias is None else bias.float(), act=act)

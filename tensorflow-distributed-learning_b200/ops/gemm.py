@@ -100,12 +100,16 @@ def colsum(x: torch.Tensor) -> torch.Tensor:
 
 
 class _LinearFn(torch.autograd.Function):
-    """y = act(x W^T + b) with forward, input-gradient and weight-gradient GEMMs all on tcgen05."""
+    """y = act(x W^T + b) with forward, input-gradient and weight-gradient GEMMs all on tcgen05.
+
+    w_lp: optional bf16 copy of W that the caller already has (the shadow arena the fused all-reduce keeps current), so no
+    cast runs here. sink: optional (fp32 gradient view in the arena, callback): the weight gradient is then written
+    straight into the arena by the GEMM epilogue and autograd gets None - no separate dW tensor, no accumulate pass."""
 
     @staticmethod
-    def forward(ctx, x, w, bias, act):
+    def forward(ctx, x, w, bias, act, w_lp=None, sink=None):
         xb = x if x.dtype == torch.bfloat16 else x.bfloat16()
-        wb = w if w.dtype == torch.bfloat16 else w.bfloat16()
+        wb = w_lp if w_lp is not None else (w if w.dtype == torch.bfloat16 else w.bfloat16())
         x2 = xb.reshape(-1, xb.shape[-1])
         pre_act = act in ("relu", "gelu")
         y = gemm_tma(x2, wb, bias=None if bias is None else bias.float(), act=None if pre_act else act)
@@ -116,7 +120,8 @@ class _LinearFn(torch.autograd.Function):
         else:
             ctx.save_for_backward(x2, wb, None)
             out = y
-        ctx.has_bias, ctx.x_shape, ctx.w_dtype = bias is not None, x.shape, w.dtype
+        ctx.has_bias, ctx.x_shape, ctx.w_dtype, ctx.sink = bias is not None, x.shape, w.dtype, sink
+        ctx.need_dx = x.requires_grad
         return out.reshape(*x.shape[:-1], w.shape[0])
 
     @staticmethod
@@ -128,16 +133,22 @@ class _LinearFn(torch.autograd.Function):
         elif ctx.act == "gelu":
             dy2 = torch.ops.aten.gelu_backward(dy2.to(pre.dtype), pre, approximate="tanh")
         dyb = dy2.bfloat16().contiguous()
-        dx = gemm_tma(dyb, wb, b_mn=True)                                      # [T,out] x W[out,in] (MN-major)
-        dw = gemm_tma(dyb, x2, a_mn=True, b_mn=True, out_dtype=torch.float32)  # dy^T x, both MN-major
+        dx = gemm_tma(dyb, wb, b_mn=True).reshape(ctx.x_shape) if ctx.need_dx else None  # [T,out] x W[out,in] (MN-major)
         db = colsum(dyb) if ctx.has_bias else None
-        return dx.reshape(ctx.x_shape), dw.to(ctx.w_dtype), db, None
+        if ctx.sink is not None:
+            view, done = ctx.sink
+            gemm_tma(dyb, x2, a_mn=True, b_mn=True, out=view.view(wb.shape[0], -1))  # dy^T x into the gradient arena
+            done()
+            return dx, None, db, None, None, None
+        dw = gemm_tma(dyb, x2, a_mn=True, b_mn=True, out_dtype=torch.float32)  # dy^T x, both MN-major
+        return dx, dw.to(ctx.w_dtype), db, None, None, None
 
 
-def linear(x: torch.Tensor, w: torch.Tensor, bias: torch.Tensor | None = None, act: str | None = None) -> torch.Tensor:
+def linear(x: torch.Tensor, w: torch.Tensor, bias: torch.Tensor | None = None, act: str | None = None,
+           w_lp: torch.Tensor | None = None, sink=None) -> torch.Tensor:
     """Dense layer on the tensor core with autograd (bf16 operands, fp32 accumulation, fp32 weight gradient).
     Needs every GEMM dimension (tokens, in, out) to be a multiple of 8."""
-    return _LinearFn.apply(x, w, bias, act)
+    return _LinearFn.apply(x, w, bias, act, w_lp, sink)
 
 
 class _TiedDecoderFn(torch.autograd.Function):

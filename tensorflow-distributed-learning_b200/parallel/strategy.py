@@ -312,7 +312,7 @@ class MirroredStrategy(Strategy):
             else:
                 dev = torch.device("cpu")
             _ensure_process_group(rank, world, dev)
-            ops = cross_device_ops or _make_group_ops(dev, CollectiveCommunication.AUTO, None)
+            ops = cross_device_ops or _make_group_ops(dev, CollectiveCommunication.AUTO, _launcher_control_group(rank, world, dev))
             super().__init__([dev], TFConfigClusterResolver.single_worker(), ops, world, rank)
             return
         devs = _parse_devices(devices)
@@ -350,17 +350,64 @@ class MultiWorkerMirroredStrategy(Strategy):
                              hb_timeout_s=heartbeat_timeout_s)
         self.group = group
         all_cuda = all(d.type == "cuda" for d in devs)
-        kinds = group.allgather_object(all_cuda)
-        use_p2p = communication != CollectiveCommunication.RING and all(kinds) and len(devs) == 1
+        # AUTO chooses by hardware and topology (README.md:21): the NVLink peer-memory kernels need every worker to
+        # drive one CUDA device of the SAME host (one NVLink / NVSwitch domain); workers spread over machines - the
+        # reference's own 172.16.16.5 / .6 deployment - get the TCP ring.
+        facts = group.allgather_object((all_cuda and len(devs) == 1, _host_identity()))
+        one_host = len({h for _, h in facts}) == 1
+        use_p2p = communication != CollectiveCommunication.RING and all(k for k, _ in facts) and one_host
         if communication == CollectiveCommunication.NCCL and not use_p2p:
             group.close()
-            raise ValueError("CollectiveCommunication.NCCL needs every worker to drive exactly one CUDA device")
+            why = ("the workers run on different hosts (the NVLink peer-memory kernels need one NVLink domain; use RING "
+                   "or AUTO across machines)" if not one_host else
+                   "every worker must drive exactly one CUDA device")
+            raise ValueError(f"CollectiveCommunication.NCCL is not possible here: {why}")
         if use_p2p:
             _ensure_process_group(res.id_in_cluster, res.num_workers, devs[0], master=res.leader_address)
             ops: CrossDeviceOps = _make_group_ops(devs[0], communication, group)
         else:
             ops = TcpRingAllReduce(group)
         super().__init__(devs, res, ops, res.num_workers, res.id_in_cluster)
+
+
+def _launcher_control_group(rank: int, world: int, dev: torch.device) -> Any:
+    """Under a torchrun-style launch there is no TF_CONFIG and so no cluster service - but the GPU collectives still
+    need failure detection (a dead peer must release the survivors' kernels). For a single-node launch a control group
+    with its heartbeat thread is opened on MASTER_ADDR, ports MASTER_PORT+17+rank. TFDL_HEARTBEAT=0 switches it off; if
+    the ports cannot be had, training goes on without it (a lost peer then ends in the kernels' spin limit)."""
+    if dev.type != "cuda" or os.environ.get("TFDL_HEARTBEAT", "1") == "0":
+        return None
+    if int(os.environ.get("LOCAL_WORLD_SIZE", str(world))) != world:
+        return None  # several nodes: ranks do not share MASTER_ADDR's host
+    try:
+        from ..runtime import native
+
+        host = os.environ.get("MASTER_ADDR", "127.0.0.1")
+        base = int(os.environ.get("MASTER_PORT", "29500")) + 17
+        addrs = [f"{host}:{base + r}" for r in range(world)]
+        return native.Group(rank, addrs, timeout_s=float(os.environ.get("TFDL_HEARTBEAT_CONNECT_S", "60")),
+                            hb_timeout_s=float(os.environ.get("TFDL_HEARTBEAT_TIMEOUT_S", "10")))
+    except Exception as e:  # noqa: BLE001
+        import sys
+
+        print(f"[tfdl] no heartbeat for this launch ({type(e).__name__}: {e}); a lost worker will not be detected early",
+              file=sys.stderr)
+        return None
+
+
+def _host_identity() -> str:
+    """Something equal for processes of one machine and different across machines: the kernel's boot id (falls back to
+    the host name). TFDL_HOST_ID overrides it (tests; containers that share a boot id but not an NVLink domain)."""
+    env = os.environ.get("TFDL_HOST_ID")
+    if env:
+        return env
+    try:
+        with open("/proc/sys/kernel/random/boot_id") as f:
+            return f.read().strip()
+    except OSError:
+        import socket
+
+        return socket.gethostname()
 
 
 def _make_group_ops(dev: torch.device, communication: CollectiveCommunication, group: Any) -> CrossDeviceOps:

@@ -43,6 +43,8 @@ def lib() -> C.CDLL:
         L.tfdl_rt_group_destroy.restype = None
         for f in ("tfdl_rt_group_rank", "tfdl_rt_group_world", "tfdl_rt_group_failed_rank", "tfdl_rt_barrier"):
             getattr(L, f).argtypes = [vp]
+        L.tfdl_rt_group_set_abort_word.argtypes = [vp, vp]
+        L.tfdl_rt_group_set_abort_word.restype = None
         L.tfdl_rt_group_set_timeout.argtypes = [vp, C.c_int]
         L.tfdl_rt_group_set_timeout.restype = None
         L.tfdl_rt_group_bytes_sent.argtypes = [vp]
@@ -194,6 +196,12 @@ class Group:
             self.close()
         except Exception:
             pass
+
+    def set_abort_word(self, ptr: int) -> None:
+        """Attach (ptr != 0) or detach (0) the pinned, device-mapped uint32 that the heartbeat thread sets to
+        failed_rank + 1 when a peer dies; GPU kernels poll it inside their spin loops."""
+        if self._h:
+            lib().tfdl_rt_group_set_abort_word(self._h, C.c_void_p(ptr))
 
     @property
     def failed_rank(self) -> int:

@@ -75,6 +75,9 @@ def main() -> None:
             else:
                 torch.testing.assert_close(params, w_ref, rtol=1e-4, atol=1e-4)  # in-switch / sliced order differs
             torch.testing.assert_close(st.shadow.tensor.float(), params.bfloat16().float(), rtol=0, atol=0)
+            # the sliced paths leave each rank with its own slice of the momentum; a checkpoint needs all of it
+            ops.sync_optimizer_slots()
+            torch.testing.assert_close(st.mom, v_ref, rtol=1e-4, atol=1e-4)
             gathered = [torch.empty_like(params) for _ in range(world)]
             dist.all_gather(gathered, params)
             for r in range(1, world):

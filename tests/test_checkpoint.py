@@ -231,6 +231,40 @@ def test_backup_and_restore_resumes_from_last_epoch(tmp_path):
     assert w_after_2[0].shape == (3, 3, 1, 32)
 
 
+def test_resume_restores_the_data_iterator_position(tmp_path):
+    """The reference's fit(epochs, steps_per_epoch) carries ONE iterator over a shuffled dataset across epochs
+    (tf_dist_example.py:31,59). A restart from a backup must continue in that iterator - same shuffle order, already
+    consumed batches skipped - so the epochs after the restart see the data (and the losses) the uninterrupted run saw."""
+    import tfdl
+
+    x, y = _xy(512, 7)
+
+    def data():
+        return tfdl.data.Dataset.from_tensor_slices((x, y)).shuffle(200).batch(32)
+
+    class Crash(keras.callbacks.Callback):
+        def on_epoch_begin(self, epoch, logs=None):
+            if epoch == 2:
+                raise KeyboardInterrupt("simulated worker loss")
+
+    bk = lambda: keras.callbacks.BackupAndRestore(str(tmp_path / "bk"))  # noqa: E731
+    ref = _model(5)
+    ds_ref = data()
+    entropy = tfdl.data.dataset.shuffle_nodes(ds_ref)[0]._entropy
+    h_ref = ref.fit(ds_ref, epochs=4, steps_per_epoch=3, verbose=0)
+    m = _model(5)
+    ds1 = data()
+    tfdl.data.dataset.shuffle_nodes(ds1)[0]._entropy = entropy  # the interrupted run draws the same order as the reference
+    with pytest.raises(KeyboardInterrupt):
+        m.fit(ds1, epochs=4, steps_per_epoch=3, verbose=0, callbacks=[bk(), Crash()])
+    m2 = _model(77)
+    h2 = m2.fit(data(), epochs=4, steps_per_epoch=3, verbose=0, callbacks=[bk()])  # fresh dataset object, random seed
+    assert h2.epoch == [2, 3]
+    np.testing.assert_allclose(h2.history["loss"], h_ref.history["loss"][2:], rtol=1e-5)
+    for u, v in zip(ref.get_weights(), m2.get_weights()):
+        np.testing.assert_allclose(u, v, rtol=1e-5, atol=1e-6)
+
+
 def test_tensorboard_events_are_readable_by_tensorboard(tmp_path):
     m = _model()
     x, y = _xy(64)

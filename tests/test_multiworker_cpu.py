@@ -109,3 +109,26 @@ def _roles(rank, addrs):
 def test_ps_role_is_parsed_but_rejected():
     res = run_workers(_roles, 1)
     assert "not a training replica" in res[0][1]
+
+
+def _topology(rank, addrs, comm):
+    """Workers that report different hosts: the reference's own two-machine deployment (tf_dist_example.py:7)."""
+    import tfdl
+
+    os.environ["TFDL_HOST_ID"] = f"machine-{rank}"
+    os.environ["TF_CONFIG"] = json.dumps({"cluster": {"worker": addrs}, "task": {"type": "worker", "index": rank}})
+    try:
+        s = tfdl.distribute.experimental.MultiWorkerMirroredStrategy(
+            getattr(tfdl.distribute.experimental.CollectiveCommunication, comm), timeout_s=30, heartbeat_timeout_s=2)
+    except ValueError as e:
+        return "ValueError: " + str(e)
+    name = s.cross_device_ops.name
+    s.close()
+    return name
+
+
+def test_auto_across_hosts_takes_the_ring_and_nccl_is_refused():
+    res = run_workers(_topology, 2, args=("AUTO",), timeout=60)
+    assert res[0][1] == "ring" and res[1][1] == "ring", res
+    res = run_workers(_topology, 2, args=("NCCL",), timeout=60)
+    assert all("different hosts" in v[1] for v in res.values()), res

@@ -42,6 +42,12 @@ def test_static_scratch_entry_point_matches_caller_scratch_twice_in_a_row():
         p = lambda t: C.c_void_p(t.data_ptr())  # noqa: E731
         rc = lib.tfdl_dense_fwd_splitk(p(x), p(w), p(bias), p(out_ref), p(scratch), B, N, K, relu, 0, stream)
         assert rc == 0, lib.tfdl_last_error()
+        if call == 1:
+            # leave the whole built-in array dirty (NaN bit pattern), as an aborted earlier call could: the entry point
+            # must clear the part it uses itself
+            lib.tfdl_static_scratch_fill.argtypes = [C.c_float, C.c_int, C.c_void_p]
+            nan = C.c_float.from_buffer_copy((0xFFFFFFFF).to_bytes(4, "little"))
+            assert lib.tfdl_static_scratch_fill(nan, STATIC_FLOATS, stream) == 0, lib.tfdl_last_error()
         rc = lib.tfdl_dense_fwd_splitk_static(p(x), p(w), p(bias), p(out_new), B, N, K, relu, 0, stream)
         assert rc == 0, lib.tfdl_last_error()
         torch.cuda.synchronize()
