@@ -80,25 +80,29 @@ def _match(model: Any) -> Optional[Tuple[int, int, int, int, int, int]]:
     return H0, W0, C1, C2, D1, NC
 
 
-def try_build(model: Any) -> Optional["NativeCnnEngine"]:
+def try_build(model: Any) -> Any:
     """Native engine for `model`, or None if its topology has no native step program."""
     _lib.kernels()  # raises NativeError when the library has not been built: no silent fallback on a GPU box
     s = model.strategy
-    if s.num_local_replicas != 1 or s.local_devices[0].type != "cuda":
+    if any(d.type != "cuda" for d in s.local_devices):
         return None
+    multi = s.num_local_replicas > 1
+    if multi and type(s.cross_device_ops).__name__ != "MirroredPeerAllReduce":
+        return None  # several local replicas without peer-mapped arenas: the portable engine
     shape = _match(model)
     if shape is None:
         return None
-    return NativeCnnEngine(model, shape)
+    return MirroredNativeEngine(model, shape) if multi else NativeCnnEngine(model, shape)
 
 
 class NativeCnnEngine:
     CHUNK = int(os.environ.get("TFDL_FIT_CHUNK", "64"))
 
-    def __init__(self, model: Any, shape: Tuple[int, int, int, int, int, int]) -> None:
+    def __init__(self, model: Any, shape: Tuple[int, int, int, int, int, int], replica: int = 0) -> None:
         self.model = model
         self.strategy = model.strategy
-        self.device = self.strategy.local_devices[0]
+        self.replica = replica  # which local replica (device, arena) this engine drives
+        self.device = self.strategy.local_devices[replica]
         self.shape = shape
         self.lib = _lib.kernels()
         self._prog: Optional[C.c_void_p] = None
@@ -111,8 +115,10 @@ class NativeCnnEngine:
         torch.cuda.set_device(self.device)
         # graphs cannot be captured on the legacy default stream: the engine owns its stream
         self.stream = torch.cuda.Stream(self.device)
-        arena = model.arenas[0]
+        arena = model.arenas[replica]
         ops = self.strategy.cross_device_ops
+        if type(ops).__name__ == "MirroredPeerAllReduce":
+            ops = ops.replica_ops[replica]  # this replica's rank of the in-process group
         if not isinstance(ops, P2PFusedAllReduce):
             if self.strategy.num_workers != 1:
                 raise RuntimeError("a multi-process GPU group must be created through MirroredStrategy / "
@@ -126,7 +132,7 @@ class NativeCnnEngine:
         self.ops = ops
         opt = model.optimizer
         self.state: FusedState = ops.fused_state(arena.params, arena.grads, momentum=bool(opt.momentum))
-        if opt.momentum:
+        if opt.momentum and self.strategy.num_local_replicas == 1:
             opt._slots = {"momentum": [self.state.mom]}  # the optimizer's slot IS the kernel's buffer
         # Gradient buckets (reverse layer order, like the reference's backward): the dense layers' gradients
         # - 91% of the arena - are final right after the fused dense block, so their all-reduce + update runs
@@ -310,7 +316,8 @@ class NativeCnnEngine:
             _lib.check(self.lib.tfdl_cnn_program_run_ptrs(self._prog, px, py, k, self.host_out.data_ptr(),
                                                           self.stream.cuda_stream), "cnn_program_run_ptrs")
         self._ptr_keep[r] = (px, py, xs, ys)  # the executor returns before the copies ran: keep the views alive
-        self.model.optimizer.iterations += k
+        if self.replica == 0:
+            self.model.optimizer.iterations += k
 
     def _pack(self, xs: List[np.ndarray], ys: List[np.ndarray]) -> None:
         """Stage a chunk of batches in the pinned ring: one multi-threaded C++ call when the arrays are plain
@@ -333,7 +340,8 @@ class NativeCnnEngine:
         with nvtx_range(f"tfdl/native_chunk[{n_steps}]"):
             _lib.check(self.lib.tfdl_cnn_program_run(self._prog, records.data_ptr(), records.shape[0], n_steps, out_ptr,
                                                      self.stream.cuda_stream), "cnn_program_run")
-        self.model.optimizer.iterations += n_steps
+        if self.replica == 0:
+            self.model.optimizer.iterations += n_steps
 
     def run_device(self, records: torch.Tensor, n_steps: int) -> None:
         """Drive n_steps steps from records already on the device ([n_records, rec_bytes] uint8)."""
@@ -342,7 +350,8 @@ class NativeCnnEngine:
         self.stream.wait_stream(torch.cuda.current_stream(self.device))
         _lib.check(self.lib.tfdl_cnn_program_run_device(self._prog, records.data_ptr(), records.shape[0], n_steps,
                                                         self.stream.cuda_stream), "cnn_program_run_device")
-        self.model.optimizer.iterations += n_steps
+        if self.replica == 0:
+            self.model.optimizer.iterations += n_steps
 
     def prepare(self, batch_size: int) -> None:
         """Build (or rebuild) the step program for a per-replica batch size."""
@@ -460,7 +469,7 @@ class NativeCnnEngine:
             i += k
 
     # ---- epoch totals without stopping the device ----------------------------------------------------------------
-    def epoch_mark(self) -> Tuple[int, Any]:
+    def epoch_mark(self, reduce: bool = True) -> Tuple[int, Any]:
         """Close an epoch on the device: stream-ordered after the epoch's last step, the (loss sum, correct, examples)
         counters are summed over replicas (NVLink kernel), copied to a pinned slot and cleared. Returns a handle for
         epoch_read(); the host does not wait here, so the next epoch's batches can be staged while this one runs."""
@@ -472,7 +481,7 @@ class NativeCnnEngine:
         tm = time.perf_counter()
         with torch.cuda.stream(self.stream):
             tot = self.metrics_dev.double()
-            if self.ops.world > 1:
+            if self.ops.world > 1 and reduce:
                 tot = self.ops.allreduce_scalars_device(tot)
             self._ep_pinned[slot].copy_(tot, non_blocking=True)
             self.metrics_dev.zero_()
@@ -505,9 +514,9 @@ class NativeCnnEngine:
         if float(m[2]) == 0.0:
             return
         self.metrics_dev.zero_()
-        self.model.loss_tracker.add(0, float(m[0]), float(m[2]))
+        self.model.loss_tracker.add(self.replica, float(m[0]), float(m[2]))
         for met in self.model.compiled_metrics:
-            met.add(0, float(m[1]), float(m[2]))
+            met.add(self.replica, float(m[1]), float(m[2]))
 
     def _torch(self) -> Any:
         if self._torch_engine is None:
@@ -542,3 +551,141 @@ class NativeCnnEngine:
                     self.lib.tfdl_host_unregister(C.c_void_p(key))
         except Exception:
             pass
+
+
+class MirroredNativeEngine:
+    """MirroredStrategy() in ONE process over several GPUs (tf_dist_example.py:13; README.md:15-19): one native step
+    program per GPU, all driven from this thread. Each program is the one the one-process-per-GPU launch runs - its
+    all-reduce kernels push gradient packets into the other GPUs' inboxes over NVLink (peer access instead of
+    symmetric memory) - so the replicas stay bit-identical. A step's per-worker batch is split in replica order."""
+
+    CHUNK = NativeCnnEngine.CHUNK
+
+    def __init__(self, model: Any, shape: Tuple[int, int, int, int, int, int]) -> None:
+        self.model, self.strategy, self.shape = model, model.strategy, shape
+        self.devices = list(self.strategy.local_devices)
+        self.replicas: List[NativeCnnEngine] = []
+        for r, d in enumerate(self.devices):
+            with torch.cuda.device(d):
+                self.replicas.append(NativeCnnEngine(model, shape, replica=r))
+        if model.optimizer.momentum:
+            model.optimizer._slots = {"momentum": [rep.state.mom for rep in self.replicas]}
+        self._torch_engine: Any = None
+        self.prof = self.replicas[0].prof
+
+    # ---- facts ----------------------------------------------------------------------------------------------
+    @property
+    def algo_name(self) -> str:
+        return self.replicas[0].algo_name
+
+    @property
+    def launches_per_step(self) -> int:
+        return sum(rep.launches_per_step for rep in self.replicas)
+
+    @property
+    def stream(self) -> Any:
+        return self.replicas[0].stream
+
+    def _each(self, fn) -> list:
+        out = []
+        for rep in self.replicas:
+            with torch.cuda.device(rep.device):
+                out.append(fn(rep))
+        return out
+
+    def hyperparams_changed(self) -> None:
+        self._each(lambda rep: rep.hyperparams_changed())
+
+    def weights_changed(self) -> None:
+        self._each(lambda rep: rep.weights_changed())
+
+    def prepare(self, batch_size: int) -> None:
+        self._each(lambda rep: rep.prepare(batch_size))
+
+    # ---- training -------------------------------------------------------------------------------------------
+    def train_chunk(self, batches: List[PerReplica]) -> None:
+        """batches[i][r] is replica r's batch of step i. Every replica's executor gets the whole chunk before the next
+        replica's is queued: the launches are asynchronous, and a replica whose kernels wait for a peer's packets is
+        served as soon as that peer's launches follow."""
+        sizes = {int(np.asarray(b[r][0]).shape[0]) for b in batches for r in range(len(self.replicas))}
+        if len(sizes) != 1 or next(iter(sizes)) % 16 != 0:
+            for b in batches:  # ragged or uneven step: the portable engine, then resynchronise the native state
+                self._fallback_step(b)
+            return
+        for r, rep in enumerate(self.replicas):
+            with torch.cuda.device(rep.device):
+                rep.train_chunk([PerReplica([b[r]]) for b in batches])
+
+    def train_step(self, batches: PerReplica) -> None:
+        self.train_chunk([batches])
+
+    def index_arrays(self, base: Any) -> Any:
+        return self.replicas[0].index_arrays(base)
+
+    def train_index_chunk(self, x: np.ndarray, y: np.ndarray, idxs: List[np.ndarray]) -> None:
+        W = len(self.replicas)
+        if any(i.size % W or (i.size // W) % 16 for i in idxs):
+            for i in idxs:  # ragged last step
+                parts = np.array_split(i, W)
+                self._fallback_step(PerReplica([(x[p], y[p]) for p in parts]))
+            return
+        for r, rep in enumerate(self.replicas):
+            with torch.cuda.device(rep.device):
+                rep.train_index_chunk(x, y, [i[r * (i.size // W):(r + 1) * (i.size // W)] for i in idxs])
+
+    def run_device(self, records: List[torch.Tensor], n_steps: int) -> None:
+        """Benchmark path: records[r] is replica r's device-resident pool."""
+        for rep, rec in zip(self.replicas, records):
+            with torch.cuda.device(rep.device):
+                rep.run_device(rec, n_steps)
+
+    @property
+    def rec_bytes(self) -> int:
+        return self.replicas[0].rec_bytes
+
+    # ---- metrics --------------------------------------------------------------------------------------------
+    def epoch_mark(self) -> Any:
+        return self._each(lambda rep: rep.epoch_mark(reduce=False))
+
+    def epoch_read(self, handles: Any) -> Tuple[float, float, float]:
+        tot = [0.0, 0.0, 0.0]
+        for rep, h in zip(self.replicas, handles):
+            with torch.cuda.device(rep.device):
+                vals = rep.epoch_read(h)
+            tot = [a + b for a, b in zip(tot, vals)]
+        return tot[0], tot[1], tot[2]
+
+    def flush_metrics(self) -> None:
+        self._each(lambda rep: rep.flush_metrics())
+
+    def last_step_out(self) -> Tuple[float, float]:
+        outs = self._each(lambda rep: rep.last_step_out())
+        return float(np.mean([o[0] for o in outs])), float(np.mean([o[1] for o in outs]))
+
+    # ---- everything that has no native program --------------------------------------------------------------
+    def _torch(self) -> Any:
+        if self._torch_engine is None:
+            from .engine import TorchEngine
+
+            self._torch_engine = TorchEngine(self.model)
+        return self._torch_engine
+
+    def _fallback_step(self, batches: PerReplica) -> None:
+        self.flush_metrics()
+        self._each(lambda rep: rep.stream.synchronize())
+        self._torch().train_step(batches)
+
+        def resync(rep: NativeCnnEngine) -> None:
+            torch.cuda.current_stream(rep.device).synchronize()
+            for g in rep.state.grads:
+                g.tensor.zero_()
+            rep.state.refresh_shadow()
+
+        self._each(resync)
+        self._each(lambda rep: torch.cuda.synchronize(rep.device))
+
+    def test_step(self, batches: PerReplica) -> None:
+        self._torch().test_step(batches)
+
+    def predict_step(self, x: np.ndarray) -> np.ndarray:
+        return self._torch().predict_step(x)

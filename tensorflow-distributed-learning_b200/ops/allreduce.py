@@ -126,9 +126,19 @@ class P2PFusedAllReduce(CrossDeviceOps):
         self._fused_states: List["FusedState"] = []  # every updating state / bucket (sync_optimizer_slots)
         self._scalars: Optional[list] = None
 
+    def make_buffer(self, numel: int, dtype: torch.dtype) -> SymmetricBuffer:
+        """One peer-mapped buffer per rank (collective: every rank makes the same sequence of calls)."""
+        return SymmetricBuffer(numel, dtype, self.device, self.world, self.rank)
+
+    def group_barrier(self) -> None:
+        """Host-side rendezvous of the group's ranks (before a collective that reads what peers wrote eagerly)."""
+        torch.cuda.synchronize(self.device)
+        if self.dist is not None:
+            self.dist.barrier()
+
     # ---- arena allocation hook used by parallel.values.ParamArena -----------------------------
     def alloc_arena(self, numel: int, device: torch.device) -> torch.Tensor:
-        buf = SymmetricBuffer(numel, torch.float32, device, self.world, self.rank)
+        buf = self.make_buffer(numel, torch.float32)
         self._arenas.append(buf)
         return buf.tensor
 
@@ -168,7 +178,7 @@ class P2PFusedAllReduce(CrossDeviceOps):
             self.dist.all_reduce(t)
             return t.cpu().numpy().reshape(np.shape(vals))
         if self._scalars is None:
-            buf = SymmetricBuffer(512, torch.float64, self.device, self.world, self.rank)
+            buf = self.make_buffer(512, torch.float64)
             st = FusedState(self, None, buf, False, plain=True)
             self._scalars = [buf, st, torch.zeros(256, dtype=torch.float64, device=self.device), 0]
         buf, st, out, calls = self._scalars
@@ -190,7 +200,7 @@ class P2PFusedAllReduce(CrossDeviceOps):
         n = int(vals.numel())
         assert n <= 256 and vals.dtype == torch.float64 and vals.is_cuda
         if self._scalars is None:
-            buf = SymmetricBuffer(512, torch.float64, self.device, self.world, self.rank)
+            buf = self.make_buffer(512, torch.float64)
             st = FusedState(self, None, buf, False, plain=True)
             self._scalars = [buf, st, torch.zeros(256, dtype=torch.float64, device=self.device), 0]
         buf, st, out, calls = self._scalars
@@ -215,14 +225,13 @@ class P2PFusedAllReduce(CrossDeviceOps):
             per = (((n + 3) // 4 + self.world - 1) // self.world) * 4
             lo, hi = min(n, per * self.rank), min(n, per * (self.rank + 1))
             if st._gather_tmp is None:
-                buf = SymmetricBuffer(n, torch.float32, self.device, self.world, self.rank)
+                buf = self.make_buffer(n, torch.float32)
                 st._gather_tmp = (buf, FusedState(self, None, buf, False, plain=True))
             buf, plain = st._gather_tmp
             view = st.mom[st.offset:st.offset + n]
             buf.tensor.zero_()
             buf.tensor[lo:hi].copy_(view[lo:hi])
-            torch.cuda.synchronize(self.device)
-            self.dist.barrier()
+            self.group_barrier()
             plain.allreduce_sum()
             view.copy_(buf.tensor)
         torch.cuda.synchronize(self.device)
@@ -281,11 +290,11 @@ class FusedState:
         self.params, self.grads = params, [grads0]
         self.shadow: Optional[SymmetricBuffer] = None
         if not plain:
-            self.grads.append(SymmetricBuffer(n, torch.float32, dev, W, R))
-            self.shadow = SymmetricBuffer(n, torch.bfloat16, dev, W, R)
+            self.grads.append(ops.make_buffer(n, torch.float32))
+            self.shadow = ops.make_buffer(n, torch.bfloat16)
         self.mom = torch.zeros(n, dtype=torch.float32, device=dev) if momentum else None
         self.pad_stride = MAX_BLOCKS * max(W, 1)
-        self.flags = SymmetricBuffer(3 * self.pad_stride, torch.int32, dev, W, R) if W > 1 else None
+        self.flags = ops.make_buffer(3 * self.pad_stride, torch.int32) if W > 1 else None
         self.counters = torch.zeros(4, dtype=torch.int32, device=dev)  # epoch, done, abort, pad
         self.hyper = torch.zeros(4, dtype=torch.float32, device=dev)
         self.has_multicast = bool(W > 1 and grads0.multicast_ptr and (plain or (
@@ -315,7 +324,7 @@ class FusedState:
         b.params, b.grads, b.shadow, b.mom = self.params, self.grads, self.shadow, self.mom
         dev, W, R = self.ops.device, self.ops.world, self.ops.rank
         b.pad_stride = self.pad_stride
-        b.flags = SymmetricBuffer(3 * b.pad_stride, torch.int32, dev, W, R) if W > 1 else None
+        b.flags = self.ops.make_buffer(3 * b.pad_stride, torch.int32) if W > 1 else None
         b.counters = torch.zeros(4, dtype=torch.int32, device=dev)
         b.hyper = torch.zeros(4, dtype=torch.float32, device=dev)
         b.has_multicast = self.has_multicast
@@ -342,7 +351,7 @@ class FusedState:
         if self.inbox is not None and self.inbox.numel * 4 >= need:
             return
         torch.cuda.synchronize(self.ops.device)
-        self.inbox = SymmetricBuffer((need + 3) // 4, torch.int32, self.ops.device, W, self.ops.rank)
+        self.inbox = self.ops.make_buffer((need + 3) // 4, torch.int32)
         self.inbox.barrier()  # nobody's first packet can land in memory that is zeroed afterwards
         self._structs = [self._make_struct(par) for par in (0, 1)]
 
@@ -410,3 +419,134 @@ class FusedState:
     @property
     def algo_name(self) -> str:
         return AR_NAMES[self.algo]
+
+
+# ---- single process, several GPUs (MirroredStrategy() in a plain python process; tf_dist_example.py:13, README.md:15-19) ----
+class PeerBuffer:
+    """One rank's view of a buffer that exists once per GPU of an in-process group: the same fields a SymmetricBuffer
+    has, with plain cudaMalloc'ed tensors and peer access between the devices instead of symmetric memory (one
+    process sees every device's pointers directly; there is no multicast mapping)."""
+
+    def __init__(self, tensors: List[torch.Tensor], rank: int) -> None:
+        self.tensor = tensors[rank]
+        self.numel, self.dtype, self.device = self.tensor.numel(), self.tensor.dtype, self.tensor.device
+        self.world, self.rank = len(tensors), rank
+        self.ptrs = [t.data_ptr() for t in tensors]
+        self.multicast_ptr = 0
+        self.handle = None
+        self._devices = [t.device for t in tensors]
+
+    def barrier(self) -> None:
+        for d in self._devices:
+            torch.cuda.synchronize(d)
+
+
+class _PeerPool:
+    """Allocations shared by the per-device ops objects of one in-process group: request number k of every rank names
+    the same logical buffer (every rank makes the same sequence of requests)."""
+
+    def __init__(self, devices: Sequence[torch.device]) -> None:
+        self.devices = list(devices)
+        self.bufs: Dict[int, List[torch.Tensor]] = {}
+        lib = _lib.kernels()
+        for a in self.devices:
+            for b in self.devices:
+                if a != b:
+                    _lib.check(lib.tfdl_enable_peer_access(a.index, b.index), "enable_peer_access")
+
+    def get(self, rank: int, seq: int, numel: int, dtype: torch.dtype) -> PeerBuffer:
+        if seq not in self.bufs:
+            self.bufs[seq] = [torch.zeros(numel, dtype=dtype, device=d) for d in self.devices]
+            for d in self.devices:
+                torch.cuda.synchronize(d)
+        ts = self.bufs[seq]
+        assert ts[0].numel() == numel and ts[0].dtype == dtype, "ranks of an in-process group diverged in their allocations"
+        return PeerBuffer(ts, rank)
+
+
+class InProcessPeerOps(P2PFusedAllReduce):
+    """Rank `rank` of a group whose ranks are the GPUs of ONE process. Same fused kernels and the same FusedState as the
+    one-process-per-GPU path; only allocation (peer access instead of symmetric memory) and the host rendezvous differ."""
+
+    name = "p2p-fused(in-process)"
+
+    def __init__(self, pool: _PeerPool, rank: int) -> None:
+        self.device = pool.devices[rank]
+        self.control, self.dist = None, None
+        self.world, self.rank = len(pool.devices), rank
+        self.pool, self._seq = pool, 0
+        self._abort = torch.zeros(1, dtype=torch.int32).pin_memory()
+        self._arenas, self._states, self._plain, self._fused_states, self._scalars = [], {}, {}, [], None
+
+    def make_buffer(self, numel: int, dtype: torch.dtype) -> PeerBuffer:  # type: ignore[override]
+        seq = self._seq
+        self._seq += 1
+        with torch.cuda.device(self.device):
+            return self.pool.get(self.rank, seq, numel, dtype)
+
+    def group_barrier(self) -> None:
+        for d in self.pool.devices:
+            torch.cuda.synchronize(d)
+
+    def barrier(self) -> None:
+        self.group_barrier()
+
+    def close(self) -> None:
+        pass
+
+
+class MirroredPeerAllReduce(CrossDeviceOps):
+    """Cross-device ops of a single-process MirroredStrategy over several GPUs: every parameter / gradient arena is
+    allocated through the matching per-device InProcessPeerOps so that the native step programs of the replicas can push
+    gradients into each other's memory. Generic engines (torch ops) reduce with a local sum."""
+
+    name = "p2p-fused(in-process)"
+
+    def __init__(self, devices: Sequence[torch.device]) -> None:
+        self.devices = list(devices)
+        self.pool = _PeerPool(self.devices)
+        self.replica_ops = [InProcessPeerOps(self.pool, r) for r in range(len(self.devices))]
+
+    @staticmethod
+    def possible(devices: Sequence[torch.device]) -> bool:
+        if len(devices) < 2 or len(devices) > MAX_RANKS or any(d.type != "cuda" for d in devices):
+            return False
+        if len({d.index for d in devices}) != len(devices) or not _lib.kernels_available():
+            return False
+        return all(torch.cuda.can_device_access_peer(a.index, b.index) for a in devices for b in devices if a != b)
+
+    def alloc_arena(self, numel: int, device: torch.device) -> torch.Tensor:
+        r = [d.index for d in self.devices].index(device.index)
+        return self.replica_ops[r].alloc_arena(numel, device)
+
+    def allreduce_grads(self, grads: Sequence[torch.Tensor]) -> None:
+        if len(grads) == 1:
+            return
+        acc = grads[0]
+        for g in grads[1:]:
+            acc.add_(g.to(acc.device, non_blocking=True))
+        for g in grads[1:]:
+            g.copy_(acc, non_blocking=True)
+
+    def barrier(self) -> None:
+        for d in self.devices:
+            torch.cuda.synchronize(d)
+
+    def sync_optimizer_slots(self) -> None:
+        """Momentum of a sliced bucket lives on the slice's owner: copy every owner's slice to the other replicas."""
+        self.barrier()
+        W = len(self.devices)
+        per_rank = [ops._fused_states for ops in self.replica_ops]
+        for i, st0 in enumerate(per_rank[0]):
+            if st0.mom is None or st0.last_algo not in (AR_TWOSHOT, AR_MULTIMEM, AR_PUSH2):
+                continue
+            n = st0.n
+            per = (((n + 3) // 4 + W - 1) // W) * 4
+            for r in range(W):
+                lo, hi = min(n, per * r), min(n, per * (r + 1))
+                src = per_rank[r][i]
+                for q in range(W):
+                    if q != r and hi > lo:
+                        dst = per_rank[q][i]
+                        dst.mom[dst.offset + lo:dst.offset + hi].copy_(src.mom[src.offset + lo:src.offset + hi])
+        self.barrier()

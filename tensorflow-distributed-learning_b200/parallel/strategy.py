@@ -103,9 +103,22 @@ class DistributedDataset:
     def index_stream(self):
         """(element store, iterator of per-step row numbers) for a single local replica over an indexable pipeline,
         else None. Lets an engine gather its batches itself (data/dataset.py:index_stream)."""
-        if self.num_local != 1:
-            return None
-        return _ds.index_stream(self.dataset)
+        st = _ds.index_stream(self.dataset)
+        if st is None or self.num_local == 1:
+            return st
+        base, it = st
+
+        def grouped():  # one step = one per-replica batch for each local replica, in replica order
+            buf = []
+            for idx in it:
+                buf.append(idx)
+                if len(buf) == self.num_local:
+                    yield np.concatenate(buf)
+                    buf = []
+            if buf:
+                yield np.concatenate(buf)
+
+        return base, grouped()
 
 
 class Strategy:
@@ -316,7 +329,16 @@ class MirroredStrategy(Strategy):
             super().__init__([dev], TFConfigClusterResolver.single_worker(), ops, world, rank)
             return
         devs = _parse_devices(devices)
-        super().__init__(devs, TFConfigClusterResolver.single_worker(), cross_device_ops or LocalAllReduce(), 1, 0)
+        ops = cross_device_ops
+        if ops is None and len(devs) > 1 and all(d.type == "cuda" for d in devs) and \
+                os.environ.get("TFDL_MIRRORED_NATIVE", "1") == "1":
+            # one process driving several GPUs (the form the reference names, tf_dist_example.py:13): the replicas' native
+            # step programs exchange gradients over NVLink peer memory, like the one-process-per-GPU launch
+            from ..ops.allreduce import MirroredPeerAllReduce
+
+            if MirroredPeerAllReduce.possible(devs):
+                ops = MirroredPeerAllReduce(devs)
+        super().__init__(devs, TFConfigClusterResolver.single_worker(), ops or LocalAllReduce(), 1, 0)
 
 
 class MultiWorkerMirroredStrategy(Strategy):

@@ -66,3 +66,33 @@ def test_tf_config_workers_one_gpu_each():
     assert all(r["replicas"] == n and r["engine"] == "NativeCnnEngine" and r["ops"] == "P2PFusedAllReduce" for r in reps), reps
     assert reps[0]["wsum"] == reps[1]["wsum"] and reps[0]["wabs"] == reps[1]["wabs"]  # mirrored variables stay identical
     assert reps[0]["loss"] == reps[1]["loss"]
+
+
+def test_killed_gpu_worker():
+    """A GPU worker dies mid-run (README.md:65-68 only describes the happy path): the survivor's collective
+    kernel is released by the heartbeat's abort word and fit() raises, naming the dead rank, within seconds."""
+    if torch.cuda.device_count() < 2:
+        pytest.skip("needs 2 GPUs")
+    ports = free_ports(2)
+    cluster = {"worker": [f"127.0.0.1:{p}" for p in ports]}
+    procs = []
+    for i in range(2):
+        env = dict(os.environ, TF_CONFIG=json.dumps({"cluster": cluster, "task": {"type": "worker", "index": i}}))
+        for k in ("RANK", "WORLD_SIZE", "LOCAL_RANK", "MASTER_ADDR", "MASTER_PORT"):
+            env.pop(k, None)
+        procs.append(subprocess.Popen([sys.executable, os.path.join(HERE, "gpu_fault_worker.py")], env=env,
+                                      stdout=subprocess.PIPE, stderr=subprocess.STDOUT, text=True))
+    outs = []
+    for p in procs:
+        try:
+            outs.append(p.communicate(timeout=180)[0])
+        except subprocess.TimeoutExpired:
+            p.kill()
+            outs.append(p.communicate()[0] + "\nTIMEOUT")
+    assert procs[1].returncode == 43, outs[1][-2000:]  # the injected exit
+    line = [l for l in outs[0].splitlines() if l.startswith("FAULT_REPORT ")]
+    assert line, outs[0][-4000:]
+    rep = json.loads(line[-1][len("FAULT_REPORT "):])
+    assert rep["engine"] == "NativeCnnEngine"
+    assert rep["error"] and "rank 1" in rep["error"], rep
+    assert rep["seconds"] < 60, rep
