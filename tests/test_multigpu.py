@@ -96,3 +96,19 @@ def test_killed_gpu_worker():
     assert rep["engine"] == "NativeCnnEngine"
     assert rep["error"] and "rank 1" in rep["error"], rep
     assert rep["seconds"] < 60, rep
+
+
+def test_single_process_mirrored_strategy():
+    """MirroredStrategy() in a plain python process (no torchrun, no TF_CONFIG) over every visible GPU."""
+    n = torch.cuda.device_count()
+    if n < 2:
+        pytest.skip("needs 2 GPUs")
+    env = {k: v for k, v in os.environ.items() if k not in ("RANK", "WORLD_SIZE", "LOCAL_RANK", "MASTER_ADDR", "MASTER_PORT")}
+    r = subprocess.run([sys.executable, os.path.join(HERE, "mirrored_single_process_worker.py")], env=env,
+                       stdout=subprocess.PIPE, stderr=subprocess.STDOUT, text=True, timeout=600)
+    assert r.returncode == 0, r.stdout[-6000:]
+    line = [l for l in r.stdout.splitlines() if l.startswith("MIRRORED_REPORT ")]
+    assert line, r.stdout[-3000:]
+    rep = json.loads(line[-1][len("MIRRORED_REPORT "):])
+    assert rep["gpus"] == n and rep["engine"] == "MirroredNativeEngine" and rep["ops"] == "MirroredPeerAllReduce", rep
+    assert rep["replicas_identical"] and rep["momentum_gathered"], rep
