@@ -61,8 +61,11 @@ __device__ __forceinline__ void pixel_coords(const ConvGeom& g, int m, int32_t& 
   h = g.lower_h + p * g.stride_h;
 }
 
+// 224 threads: warp 0 = activation (A) producer, warp 6 = weight / second-operand (B) producer, warp 1 = MMA issuer,
+// warps 2-5 = epilogue. With 64-channel layers a K block is only 128 x BN x 64 of MMA work, and ONE thread issuing both
+// operands' TMA loads (~70 dependent instructions per block) was the kernel's limiter, not the tensor core or memory.
 template <int BN, int STAGES>
-__global__ void __launch_bounds__(192, 1)
+__global__ void __launch_bounds__(224, 1)
 conv_igemm_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ CUtensorMap tmB,
                   const __grid_constant__ CUtensorMap tmD, TmaGemmParams p, ConvGeom g) {
   extern __shared__ __align__(1024) uint8_t smem_raw[];
@@ -107,46 +110,80 @@ conv_igemm_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant
   const uint32_t tmem_base = tmem_slot;
   const uint32_t smem_base = smem_u32(smem);
 
-  if (warp == 0) {
-    // ------------------------------ TMA producer ------------------------------
+  if (warp == 0 || warp == 6) {
+    // ------------------------------ TMA producers ------------------------------
+    // warp 0 posts the stage's byte count and loads operand A, warp 6 loads operand B; both wait for the slot to be free.
+    const bool prodA = warp == 0;
     if (elect_one()) {
       uint32_t stage = 0, phase = 0;
       for (int u = blockIdx.x; u < num_units; u += gridDim.x) {
         const int t = u / p.ksplit, kb0 = (u % p.ksplit) * k_per, kb1 = min(k_blocks, kb0 + k_per);
         int mt, nt;
         tile_coords(t, p.m_tiles, p.n_tiles, 16, mt, nt);
+        // No division inside the K loop: tap / channel-block / pixel counters are decoded once per work unit and then
+        // advanced incrementally.
         int32_t w0 = 0, h0 = 0, n0 = 0;
-        if (!wgrad) pixel_coords(g, mt * BM, w0, h0, n0);
-        for (int kb = kb0; kb < kb1; ++kb) {
-          mbar_wait(&empty_bar[stage], phase ^ 1);
-          const uint32_t sa = smem_base + stage * STAGE_BYTES, sb = sa + A_BYTES;
-          if (!wgrad) {
-            mbar_expect_tx(&full_bar[stage], STAGE_BYTES);
-            const int tap = kb / g.cblocks, cb = kb - tap * g.cblocks;
-            const int r = tap / g.S, s = tap - r * g.S;
-            tma_load_im2col(sa, &tmA, cb * 64, w0, h0, n0, (uint16_t)s, (uint16_t)r, &full_bar[stage]);
-            if (g.mode == 0) {
+        if (!wgrad) {
+          if (prodA) pixel_coords(g, mt * BM, w0, h0, n0);
+          int tap = kb0 / g.cblocks, cb = kb0 - tap * g.cblocks;
+          int r = tap / g.S, sx = tap - r * g.S;
+          for (int kb = kb0; kb < kb1; ++kb) {
+            mbar_wait(&empty_bar[stage], phase ^ 1);
+            const uint32_t sa = smem_base + stage * STAGE_BYTES, sb = sa + A_BYTES;
+            if (prodA) {
+              mbar_expect_tx(&full_bar[stage], STAGE_BYTES);
+              tma_load_im2col(sa, &tmA, cb * 64, w0, h0, n0, (uint16_t)sx, (uint16_t)r, &full_bar[stage]);
+            } else if (g.mode == 0) {
               tma_load_2d(sb, &tmB, tap * g.w_tap_stride + cb * 64, nt * BN, &full_bar[stage]);
             } else {
-              const int wt = (g.R - 1 - r) * g.S + (g.S - 1 - s);
+              const int wt = (g.R - 1 - r) * g.S + (g.S - 1 - sx);
 #pragma unroll
               for (int b = 0; b < UNITS; ++b)
                 tma_load_2d(sb + b * 8192, &tmB, wt * g.w_tap_stride + nt * BN + b * 64, cb * 64, &full_bar[stage]);
             }
-          } else {
-            int valid = min(UNITS, n_units - nt * UNITS);
-            mbar_expect_tx(&full_bar[stage], A_BYTES + (uint32_t)valid * 8192u);
-#pragma unroll
-            for (int b = 0; b < BM / 64; ++b) tma_load_2d(sa + b * 8192, &tmA, mt * BM + b * 64, kb * BK, &full_bar[stage]);
-            pixel_coords(g, kb * BK, w0, h0, n0);
-            for (int b = 0; b < valid; ++b) {
-              const int un = nt * UNITS + b;
-              const int tap = un / g.cblocks, cb = un - tap * g.cblocks;
-              const int r = tap / g.S, s = tap - r * g.S;
-              tma_load_im2col(sb + b * 8192, &tmB, cb * 64, w0, h0, n0, (uint16_t)s, (uint16_t)r, &full_bar[stage]);
+            if (++cb == g.cblocks) {
+              cb = 0;
+              ++tap;
+              if (++sx == g.S) { sx = 0; ++r; }
             }
+            if (++stage == STAGES) { stage = 0; phase ^= 1; }
           }
-          if (++stage == STAGES) { stage = 0; phase ^= 1; }
+        } else {
+          const int valid = min(UNITS, n_units - nt * UNITS);
+          int u_r[UNITS], u_s[UNITS], u_c[UNITS];
+#pragma unroll
+          for (int b = 0; b < UNITS; ++b) {
+            const int un = min(nt * UNITS + b, n_units - 1);
+            const int tap = un / g.cblocks;
+            u_c[b] = (un - tap * g.cblocks) * 64;
+            u_r[b] = tap / g.S;
+            u_s[b] = tap - u_r[b] * g.S;
+          }
+          // output pixel (n, p, q) of the first row of K block kb0, advanced by BK pixels per block
+          int pn = (kb0 * BK) / g.PQ, rem = kb0 * BK - pn * g.PQ;
+          int pp = rem / g.Q, pq = rem - pp * g.Q;
+          for (int kb = kb0; kb < kb1; ++kb) {
+            mbar_wait(&empty_bar[stage], phase ^ 1);
+            const uint32_t sa = smem_base + stage * STAGE_BYTES, sb = sa + A_BYTES;
+            if (prodA) {
+              mbar_expect_tx(&full_bar[stage], A_BYTES + (uint32_t)valid * 8192u);
+#pragma unroll
+              for (int b = 0; b < BM / 64; ++b) tma_load_2d(sa + b * 8192, &tmA, mt * BM + b * 64, kb * BK, &full_bar[stage]);
+            } else {
+              w0 = g.lower_w + pq * g.stride_w;
+              h0 = g.lower_h + pp * g.stride_h;
+#pragma unroll
+              for (int b = 0; b < UNITS; ++b)
+                if (b < valid)
+                  tma_load_im2col(sb + b * 8192, &tmB, u_c[b], w0, h0, pn, (uint16_t)u_s[b], (uint16_t)u_r[b], &full_bar[stage]);
+              pq += BK;
+              while (pq >= g.Q) {
+                pq -= g.Q;
+                if (++pp == g.P) { pp = 0; ++pn; }
+              }
+            }
+            if (++stage == STAGES) { stage = 0; phase ^= 1; }
+          }
         }
       }
     }
@@ -155,6 +192,12 @@ conv_igemm_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant
     if (elect_one()) {
       const bool a_mn = wgrad, b_mn = g.mode != 0;
       const uint32_t idesc = umma_idesc_bf16(BM, BN, a_mn, b_mn);
+      // Descriptors differ from block to block only in their 14-bit start-address field: build them once for stage 0 and
+      // add (byte offset >> 4) per stage and per K step (the sum stays below 2^14: shared memory is < 256 KB).
+      const uint64_t a_desc0 = a_mn ? umma_smem_desc(smem_base, 8192, 1024, SWZ_128B) : umma_smem_desc(smem_base, 16, 1024, SWZ_128B);
+      const uint64_t b_desc0 = b_mn ? umma_smem_desc(smem_base + A_BYTES, 8192, 1024, SWZ_128B)
+                                    : umma_smem_desc(smem_base + A_BYTES, 16, 1024, SWZ_128B);
+      const uint32_t a_step = a_mn ? (2048u >> 4) : (32u >> 4), b_step = b_mn ? (2048u >> 4) : (32u >> 4);
       uint32_t stage = 0, phase = 0, as = 0, aphase = 0;
       for (int u = blockIdx.x; u < num_units; u += gridDim.x) {
         const int kb0 = (u % p.ksplit) * k_per, kb1 = min(k_blocks, kb0 + k_per);
@@ -164,16 +207,10 @@ conv_igemm_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant
         for (int kb = kb0; kb < kb1; ++kb) {
           mbar_wait(&full_bar[stage], phase);
           tc_fence_after_sync();
-          const uint32_t sa = smem_base + stage * STAGE_BYTES;
-          const uint32_t sb = sa + A_BYTES;
+          const uint32_t soff = (stage * STAGE_BYTES) >> 4;
+          const uint64_t ad = a_desc0 + soff, bd = b_desc0 + soff;
 #pragma unroll
-          for (int k = 0; k < BK / 16; ++k) {
-            uint64_t ad = a_mn ? umma_smem_desc(sa + k * 2048, 8192, 1024, SWZ_128B)
-                               : umma_smem_desc(sa + k * 32, 16, 1024, SWZ_128B);
-            uint64_t bd = b_mn ? umma_smem_desc(sb + k * 2048, 8192, 1024, SWZ_128B)
-                               : umma_smem_desc(sb + k * 32, 16, 1024, SWZ_128B);
-            umma_bf16(d_tmem, ad, bd, idesc, (kb > kb0) || (k != 0));
-          }
+          for (int k = 0; k < BK / 16; ++k) umma_bf16(d_tmem, ad + k * a_step, bd + k * b_step, idesc, (kb > kb0) || (k != 0));
           umma_commit(&empty_bar[stage]);
           if (++stage == STAGES) { stage = 0; phase ^= 1; }
         }
@@ -310,7 +347,7 @@ static int launch_conv(const CUtensorMap& tmA, const CUtensorMap& tmB, const CUt
   }
   const int units = p.m_tiles * p.n_tiles * p.ksplit;
   const int grid = units < sms ? units : sms;
-  kern<<<grid, 192, smem, s>>>(tmA, tmB, tmD, p, g);
+  kern<<<grid, 224, smem, s>>>(tmA, tmB, tmD, p, g);
   TFDL_CUDA_OK(cudaGetLastError());
   return 0;
 }
