@@ -421,13 +421,51 @@ __global__ void __launch_bounds__(256) fused_ar_push2_kernel(TfdlFusedArParams p
     for (int64_t i = tid; i < n4; i += nth) z4[i] = make_float4(0.f, 0.f, 0.f, 0.f);
   // ---- hop 1 in: everybody else's slices ----
   const uint4* in1 = reinterpret_cast<const uint4*>(p.inbox[rank]) + hop1;
-  for (int64_t i = tid; i < n4; i += nth) {
-    const int owner = (int)(i / per);
-    if (owner == rank) continue;
-    float4 w;
-    if (!poll_one(in1 + (int64_t)owner * region, i - owner * per, e, p.abort_word, w)) return;
-    w4[i] = w;
-    if (s2) s2[i] = to_bf16x4(w);
+  // Four elements per trip with all eight packet loads in flight together: a thread that polled its elements one after
+  // the other paid one L2 round trip each.
+  constexpr int U = 4;
+  for (int64_t i0 = tid; i0 < n4; i0 += nth * U) {
+    const uint4* src[U];
+    bool need[U];
+    float4 w[U];
+#pragma unroll
+    for (int u = 0; u < U; ++u) {
+      const int64_t i = i0 + u * nth;
+      need[u] = i < n4 && (int)(i / per) != rank;
+      if (need[u]) {
+        const int owner = (int)(i / per);
+        src[u] = in1 + (int64_t)owner * region + pkt_of(i - owner * per);
+      }
+    }
+    uint32_t spins = 0;
+    for (;;) {
+      uint4 a[U], b[U];
+#pragma unroll
+      for (int u = 0; u < U; ++u)
+        if (need[u]) {
+          a[u] = ld_packet(src[u]);
+          b[u] = ld_packet(src[u] + 32);
+        }
+      bool pending = false;
+#pragma unroll
+      for (int u = 0; u < U; ++u)
+        if (need[u]) {
+          if (a[u].y == e && a[u].w == e && b[u].y == e && b[u].w == e) {
+            w[u] = make_float4(__uint_as_float(a[u].x), __uint_as_float(a[u].z), __uint_as_float(b[u].x), __uint_as_float(b[u].z));
+            const int64_t i = i0 + u * nth;
+            w4[i] = w[u];
+            if (s2) s2[i] = to_bf16x4(w[u]);
+            need[u] = false;
+          } else {
+            pending = true;
+          }
+        }
+      if (!pending) break;
+      if ((++spins & 0x3FF) == 0) {
+        if (p.abort_word && ld_relaxed_sys(p.abort_word) != 0) return;
+        if (spins > TFDL_PUSH_SPIN_LIMIT) __trap();
+      }
+    }
   }
   finish_step(p, e);
 }
@@ -650,6 +688,25 @@ extern "C" int tfdl_allreduce_small_f64(const TfdlFusedArParams* p, double* out,
   TFDL_REQUIRE(p && p->world >= 2 && p->world <= TFDL_MAX_RANKS && out && n > 0 && n <= 256,
                "allreduce_small_f64: bad arguments (n = %d, at most 256 values)", n);
   allreduce_f64_kernel<<<1, 256, 0, (cudaStream_t)stream>>>(*p, out, n);
+  TFDL_CUDA_OK(cudaGetLastError());
+  return 0;
+}
+
+// Epoch totals without a host round trip: dst[i] = (double)metrics[i], optionally clearing the counters - dst is either a
+// mapped pinned host slot (one GPU: the host reads it after the event) or this rank's slot of the symmetric buffer that
+// tfdl_allreduce_small_f64 sums over the ranks (its `out` may itself be a mapped host pointer).
+namespace tfdl {
+__global__ void metrics_snapshot_kernel(float* metrics, int n, double* dst, int zero) {
+  const int i = threadIdx.x;
+  if (i < n) {
+    dst[i] = (double)metrics[i];
+    if (zero) metrics[i] = 0.f;
+  }
+}
+}  // namespace tfdl
+extern "C" int tfdl_metrics_snapshot(float* metrics, int n, double* dst, int zero, void* stream) {
+  TFDL_REQUIRE(metrics && dst && n > 0 && n <= 256, "metrics_snapshot: bad arguments");
+  tfdl::metrics_snapshot_kernel<<<1, 256, 0, (cudaStream_t)stream>>>(metrics, n, dst, zero);
   TFDL_CUDA_OK(cudaGetLastError());
   return 0;
 }

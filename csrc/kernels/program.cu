@@ -143,7 +143,7 @@ static int step_launch_impl(const TfdlCnnStep* s, const TfdlFusedArParams* early
   return 0;
 }
 
-#define TFDL_CHUNK_MAX 8
+#define TFDL_CHUNK_MAX 16
 struct TfdlStageTable {
   const void* x[TFDL_CHUNK_MAX + 1];  // [j], j = 1..K: images of step j of this chunk (K = first step of the next chunk)
   const void* y[TFDL_CHUNK_MAX + 1];
@@ -169,7 +169,7 @@ struct TfdlCnnProgram {
   int64_t steps_done = 0;
   int device = 0;
   // chunked launches (see launch_chunk)
-  int chunk_max = 8;
+  int chunk_max = 16;
   cudaGraphExec_t chunk_exec[TFDL_CHUNK_MAX + 1][2] = {};
   TfdlStageTable* table_dev = nullptr;
   cudaEvent_t ev_stage_fork = nullptr, ev_stage_join = nullptr;
@@ -241,9 +241,9 @@ extern "C" int tfdl_cnn_program_create2(const TfdlCnnStep steps[2], const TfdlFu
   TFDL_CUDA_OK(cudaEventCreateWithFlags(&p->ev_stage_join, cudaEventDisableTiming));
   TFDL_CUDA_OK(cudaMalloc(&p->table_dev, sizeof(TfdlStageTable)));
   TFDL_CUDA_OK(cudaMemset(p->table_dev, 0, sizeof(TfdlStageTable)));
-  if (const char* e = getenv("TFDL_STEPS_PER_GRAPH")) {  // 1, 2, 4 or 8 steps per graph launch
+  if (const char* e = getenv("TFDL_STEPS_PER_GRAPH")) {  // 1, 2, 4, 8 or 16 steps per graph launch
     int k = atoi(e);
-    p->chunk_max = k >= 8 ? 8 : k >= 4 ? 4 : k >= 2 ? 2 : 1;
+    p->chunk_max = k >= 16 ? 16 : k >= 8 ? 8 : k >= 4 ? 4 : k >= 2 ? 2 : 1;
   }
   for (int i = 0; i < 2; ++i) {
     TFDL_CUDA_OK(cudaEventCreateWithFlags(&p->ev_in[i], cudaEventDisableTiming));

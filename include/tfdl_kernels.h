@@ -210,6 +210,9 @@ int tfdl_broadcast_f32(const TfdlFusedArParams* p, int root, void* stream);
 /* Sum n <= 256 doubles across ranks (metric totals): grads[0][r] = rank r's slot buffer of 2 x 256 doubles, the caller
  * puts its values into slot [epoch & 1] of its own buffer before the call; every rank receives the same totals. */
 int tfdl_allreduce_small_f64(const TfdlFusedArParams* p, double* out, int n, void* stream);
+/* dst[i] = (double)metrics[i] for i < n <= 256, then metrics[i] = 0 if `zero`: closes an epoch's device-side counters
+ * (loss sum, correct, examples) in stream order. dst: device memory or mapped pinned host memory. */
+int tfdl_metrics_snapshot(float* metrics, int n, double* dst, int zero, void* stream);
 int tfdl_cast_f32_to_bf16(const float* src, void* dst_bf16, int64_t n, void* stream);
 int tfdl_enable_peer_access(int device, int peer);
 
@@ -327,7 +330,7 @@ int tfdl_cnn_program_create(const TfdlCnnStep steps[2], const TfdlFusedArParams 
 int tfdl_cnn_program_create2(const TfdlCnnStep steps[2], const TfdlFusedArParams ar[2], int algo,
                              const TfdlFusedArParams ar_early[2], int algo_early, int use_graph, TfdlCnnProgram** out);
 int tfdl_cnn_program_destroy(TfdlCnnProgram* p);
-/* The run entry points launch up to 8 steps per CUDA graph (TFDL_STEPS_PER_GRAPH=1|2|4|8): a graph boundary after
+/* The run entry points launch up to 16 steps per CUDA graph (TFDL_STEPS_PER_GRAPH=1|2|4|8|16): a graph boundary after
  * kernels that wrote peer memory costs ~3-4 us. Each step's batch is fetched by a copy kernel on a parallel branch of
  * the step before it (source pointers come from a device table rewritten before each launch), and the same kernel
  * writes the previous step's (loss, accuracy) into host_out through mapped pinned memory.

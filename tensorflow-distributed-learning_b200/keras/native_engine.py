@@ -141,7 +141,8 @@ class NativeCnnEngine:
         self.overlap = os.environ.get("TFDL_AR_OVERLAP", "1") == "1"
         if self.overlap:
             cut = self.model.weights[4].spec.offset  # first dense variable
-            self.buckets = [self.state.bucket(0, cut), self.state.bucket(cut, self.state.n - cut, max_blocks=64)]
+            dense_blocks = int(os.environ.get("TFDL_DENSE_AR_BLOCKS", "64"))  # CTAs of the overlapped dense-bucket kernel
+            self.buckets = [self.state.bucket(0, cut), self.state.bucket(cut, self.state.n - cut, max_blocks=dense_blocks)]
         self.hyperparams_changed()
         self.state.refresh_shadow()
         torch.cuda.synchronize(self.device)
@@ -442,7 +443,8 @@ class NativeCnnEngine:
             self.prof["ring_wait"] += time.perf_counter() - tw
             k = 0
             # the first group of a call is short (8 steps): the device starts on it while the rest is being gathered
-            cap = 8 if i == 0 and len(idxs) > 8 else self.ring.shape[0]
+            # (only when the device has nothing queued - otherwise the split just costs an extra launch sequence)
+            cap = 8 if i == 0 and len(idxs) > 8 and self.stream.query() else self.ring.shape[0]
             while i + k < len(idxs) and k < cap and idxs[i + k].size == B:
                 k += 1
             t0 = time.perf_counter()
@@ -480,11 +482,13 @@ class NativeCnnEngine:
         self._ep_i = (self._ep_i + 1) % len(self._ep_pinned)
         tm = time.perf_counter()
         with torch.cuda.stream(self.stream):
-            tot = self.metrics_dev.double()
-            if self.ops.world > 1 and reduce:
-                tot = self.ops.allreduce_scalars_device(tot)
-            self._ep_pinned[slot].copy_(tot, non_blocking=True)
-            self.metrics_dev.zero_()
+            if self.ops.world > 1 and not reduce:  # in-process group: the caller adds the replicas' totals on the host
+                lib = self.lib
+                lib.tfdl_metrics_snapshot.argtypes = [C.c_void_p, C.c_int, C.c_void_p, C.c_int, C.c_void_p]
+                _lib.check(lib.tfdl_metrics_snapshot(_lib.ptr(self.metrics_dev), 3, _lib.ptr(self._ep_pinned[slot]), 1,
+                                                     _lib.cur_stream()), "metrics_snapshot")
+            else:
+                self.ops.snapshot_sum_to_host(self.metrics_dev, self._ep_pinned[slot])
             ev = torch.cuda.Event()
             ev.record(self.stream)
         self.prof["mark"] += time.perf_counter() - tm

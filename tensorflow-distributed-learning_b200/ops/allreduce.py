@@ -211,6 +211,29 @@ class P2PFusedAllReduce(CrossDeviceOps):
                    "allreduce_small_f64")
         return out[:n].clone()
 
+    def snapshot_sum_to_host(self, metrics: torch.Tensor, host_slot: torch.Tensor) -> None:
+        """Stream-ordered, no host wait: the fp32 device counters `metrics` are converted to float64, cleared, summed over
+        the ranks (NVLink kernel, rank order: identical totals everywhere) and written into `host_slot`, a pinned float64
+        tensor the device writes through its mapped address. Two launches (one on a single GPU)."""
+        n = int(metrics.numel())
+        lib = _lib.kernels()
+        lib.tfdl_metrics_snapshot.argtypes = [C.c_void_p, C.c_int, C.c_void_p, C.c_int, C.c_void_p]
+        if self.world == 1:
+            _lib.check(lib.tfdl_metrics_snapshot(_lib.ptr(metrics), n, _lib.ptr(host_slot), 1, _lib.cur_stream()),
+                       "metrics_snapshot")
+            return
+        if self._scalars is None:
+            buf = self.make_buffer(512, torch.float64)
+            st = FusedState(self, None, buf, False, plain=True)
+            self._scalars = [buf, st, torch.zeros(256, dtype=torch.float64, device=self.device), 0]
+        buf, st, _out, calls = self._scalars
+        par = calls & 1
+        self._scalars[3] = calls + 1
+        _lib.check(lib.tfdl_metrics_snapshot(_lib.ptr(metrics), n, C.c_void_p(buf.tensor.data_ptr() + par * 256 * 8), 1,
+                                             _lib.cur_stream()), "metrics_snapshot")
+        _lib.check(lib.tfdl_allreduce_small_f64(C.byref(st.struct(0)), _lib.ptr(host_slot), n, _lib.cur_stream()),
+                   "allreduce_small_f64")
+
     def sync_optimizer_slots(self) -> None:
         """Make every rank's momentum buffer complete (collective: every rank calls it, e.g. before a checkpoint).
         The sliced paths (two-shot, multimem, push2) update the momentum of a slice only on the rank that owns the
