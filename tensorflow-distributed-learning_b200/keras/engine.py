@@ -276,7 +276,10 @@ class Model:
             self.build(tuple(np.asarray(xb).shape[1:]))
         engine = self._make_engine()
         history = History()
-        cbs = _cb.CallbackList([history] + list(callbacks or []), model=self, verbose=verbose, epochs=epochs,
+        callbacks = list(callbacks or [])
+        if os.environ.get("TFDL_FAULT") and not any(isinstance(c, _cb.FaultInjection) for c in callbacks):
+            callbacks.append(_cb.FaultInjection())  # fault injection by environment alone
+        cbs = _cb.CallbackList([history] + callbacks, model=self, verbose=verbose, epochs=epochs,
                                steps=steps_per_epoch)
         self.stop_training = False
         logs: Dict[str, float] = {}
@@ -311,6 +314,7 @@ class Model:
 
         it: Any = None
         self.reset_metrics()
+        t_loop = time.time()
         for epoch in range(initial_epoch, epochs):
             if not lag and epoch > initial_epoch:
                 self.reset_metrics()
@@ -394,7 +398,7 @@ class Model:
             logs = deliver(pending)
         if os.environ.get("TFDL_FIT_PROFILE") and hasattr(engine, "prof"):
             print("[tfdl fit profile, host ms] " + ", ".join(f"{k} {1e3 * v:.2f}" for k, v in engine.prof.items())
-                  + f", fit total {1e3 * (time.time() - t_fit):.2f}", file=sys.stderr)
+                  + f", setup {1e3 * (t_loop - t_fit):.2f}, fit total {1e3 * (time.time() - t_fit):.2f}", file=sys.stderr)
             for k in engine.prof:
                 engine.prof[k] = 0.0
         cbs.on_train_end(logs)

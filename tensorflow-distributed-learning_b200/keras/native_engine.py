@@ -147,6 +147,7 @@ class NativeCnnEngine:
         self.state.refresh_shadow()
         torch.cuda.synchronize(self.device)
         self.metrics_dev = torch.zeros(3, dtype=torch.float32, device=self.device)
+        self._metrics_dirty = False  # steps have run since the counters were last read or closed
         lib = self.lib
         lib.tfdl_cnn_program_run.argtypes = [C.c_void_p, C.c_void_p, C.c_int64, C.c_int64, C.c_void_p, C.c_void_p]
         lib.tfdl_cnn_program_steps_done.restype = C.c_int64
@@ -316,6 +317,7 @@ class NativeCnnEngine:
         with nvtx_range(f"tfdl/native_chunk[{k}]"):
             _lib.check(self.lib.tfdl_cnn_program_run_ptrs(self._prog, px, py, k, self.host_out.data_ptr(),
                                                           self.stream.cuda_stream), "cnn_program_run_ptrs")
+        self._metrics_dirty = True
         self._ptr_keep[r] = (px, py, xs, ys)  # the executor returns before the copies ran: keep the views alive
         if self.replica == 0:
             self.model.optimizer.iterations += k
@@ -341,6 +343,7 @@ class NativeCnnEngine:
         with nvtx_range(f"tfdl/native_chunk[{n_steps}]"):
             _lib.check(self.lib.tfdl_cnn_program_run(self._prog, records.data_ptr(), records.shape[0], n_steps, out_ptr,
                                                      self.stream.cuda_stream), "cnn_program_run")
+        self._metrics_dirty = True
         if self.replica == 0:
             self.model.optimizer.iterations += n_steps
 
@@ -351,6 +354,7 @@ class NativeCnnEngine:
         self.stream.wait_stream(torch.cuda.current_stream(self.device))
         _lib.check(self.lib.tfdl_cnn_program_run_device(self._prog, records.data_ptr(), records.shape[0], n_steps,
                                                         self.stream.cuda_stream), "cnn_program_run_device")
+        self._metrics_dirty = True
         if self.replica == 0:
             self.model.optimizer.iterations += n_steps
 
@@ -424,6 +428,7 @@ class NativeCnnEngine:
         """Train on len(idxs) consecutive batches given as row numbers into (x, y): ONE multi-threaded gather builds the
         records in the pinned ring (shuffle + batch + staging in a single pass), one executor call runs them."""
         i = 0
+        ramping = False
         while i < len(idxs):
             B = int(idxs[i].size)
             if B == 0:
@@ -442,9 +447,15 @@ class NativeCnnEngine:
             self.ring_done[r].synchronize()
             self.prof["ring_wait"] += time.perf_counter() - tw
             k = 0
-            # the first group of a call is short (8 steps): the device starts on it while the rest is being gathered
+            # the first group of a call is short (4 steps): the device starts on it while the rest is being gathered
             # (only when the device has nothing queued - otherwise the split just costs an extra launch sequence)
-            cap = 8 if i == 0 and len(idxs) > 8 and self.stream.query() else self.ring.shape[0]
+            # and the second is 8 (gathered while the first runs); everything after that is gathered behind running steps
+            if i == 0 and len(idxs) > 4 and self.stream.query():
+                cap, ramping = 4, True
+            elif i == 4 and ramping:
+                cap, ramping = 8, False
+            else:
+                cap = self.ring.shape[0]
             while i + k < len(idxs) and k < cap and idxs[i + k].size == B:
                 k += 1
             t0 = time.perf_counter()
@@ -461,7 +472,7 @@ class NativeCnnEngine:
                     i += k
                     continue
             flat = np.ascontiguousarray(np.concatenate(group), dtype=np.int64)
-            _rt.gather_records(x, y, flat, k, B, self.ring.data_ptr(), self.rec_bytes)
+            _rt.gather_records(x, y, flat, k, B, self.ring.data_ptr(), self.rec_bytes, threads=8)
             t1 = time.perf_counter()
             self.run_pinned(self.ring, k, self.host_out)
             self.prof["gather"] += t1 - t0
@@ -491,6 +502,7 @@ class NativeCnnEngine:
                 self.ops.snapshot_sum_to_host(self.metrics_dev, self._ep_pinned[slot])
             ev = torch.cuda.Event()
             ev.record(self.stream)
+        self._metrics_dirty = False
         self.prof["mark"] += time.perf_counter() - tm
         return slot, ev
 
@@ -512,6 +524,9 @@ class NativeCnnEngine:
     # ------------------------------------------------------------------------------------------
     def flush_metrics(self) -> None:
         """Fold the device-side (loss sum, correct, examples) counters into the Keras metric objects."""
+        if not self._metrics_dirty:
+            return
+        self._metrics_dirty = False
         self.stream.synchronize()
         self.ops.check_abort()
         m = self.metrics_dev.cpu()
