@@ -323,13 +323,13 @@ __global__ void __launch_bounds__(256) stage_inputs_kernel(const TfdlStageTable*
     const uint4* a = reinterpret_cast<const uint4*>(sx);
     uint4* d = reinterpret_cast<uint4*>(dst);
     const unsigned nx = x_bytes >> 4, ny = y_bytes >> 4;
-    for (unsigned i = tid; i < nx; i += nth * 4) {  // four 16-byte loads in flight per thread (PCIe latency)
-      uint4 v[4];
+    for (unsigned i = tid; i < nx; i += nth * 8) {  // eight 16-byte loads in flight per thread (PCIe latency) ...
+      uint4 v[8];
 #pragma unroll
-      for (int u = 0; u < 4; ++u)
+      for (int u = 0; u < 8; ++u)
         if (i + u * nth < nx) v[u] = __ldcs(a + i + u * nth);
 #pragma unroll
-      for (int u = 0; u < 4; ++u)
+      for (int u = 0; u < 8; ++u)
         if (i + u * nth < nx) d[i + u * nth] = v[u];
     }
     const uint4* b = reinterpret_cast<const uint4*>(sy);
@@ -351,7 +351,9 @@ static int enqueue_chunk(TfdlCnnProgram* p, int K, int par0, cudaStream_t st) {
     // branch: fetch the batch of step j+1 (other parity's input record), export the result of step j-1
     TFDL_CUDA_OK(cudaEventRecord(p->ev_stage_fork, st));
     TFDL_CUDA_OK(cudaStreamWaitEvent(p->copy, p->ev_stage_fork, 0));
-    stage_inputs_kernel<<<24, 256, 0, p->copy>>>(p->table_dev, j + 1,
+    // ... from only 8 CTAs: the branch runs next to the step's compute kernels (the dense block needs its 25 CTAs
+    // co-resident) and must not take SMs from them; 8 x 256 x 8 x 16 B = 256 KB in flight covers a 200 KB batch.
+    stage_inputs_kernel<<<8, 256, 0, p->copy>>>(p->table_dev, j + 1,
                                                  reinterpret_cast<char*>(const_cast<float*>(p->steps[par ^ 1].x)), x_bytes,
                                                  y_bytes, p->steps[par ^ 1].step_out, j - 1);
     TFDL_CUDA_OK(cudaGetLastError());
