@@ -323,6 +323,14 @@ extern "C" int tfdl_rt_gather_records(const void* x_src, int64_t num_rows, int64
       int32_t* yl = reinterpret_cast<int32_t*>(rec + B * x_row_bytes);
       for (int64_t b = 0; b < B; ++b) {
         const int64_t j = idx[r * B + b];
+        // rows are scattered over a dataset far larger than the caches: start the DRAM fetch of a row a few rows ahead
+        // (the hardware prefetcher continues it) so the copy below is not one latency stall per row
+        if (b + 4 < B) {
+          const char* nxt = xs + idx[r * B + b + 4] * x_row_bytes;
+          __builtin_prefetch(nxt);
+          __builtin_prefetch(nxt + 64);
+          __builtin_prefetch(nxt + 128);
+        }
         std::memcpy(rec + b * x_row_bytes, xs + j * x_row_bytes, (size_t)x_row_bytes);
         yl[b] = label_bytes == 8 ? (int32_t) static_cast<const int64_t*>(y_src)[j]
                 : label_bytes == 4 ? static_cast<const int32_t*>(y_src)[j]
