@@ -230,13 +230,19 @@ class NativeCnnEngine:
         ars = (FusedArParams * 2)(last.struct(0), last.struct(1))
         prog = C.c_void_p()
         use_graph = int(os.environ.get("TFDL_USE_GRAPH", "1"))
+        # which states the C++ executor steps (sync_optimizer_slots gathers momentum slices of the sliced ones only)
+        for st_ in [self.state] + list(self.buckets):
+            st_.last_algo = None
         if len(self.buckets) == 2 and steps[0].use_dense_block:
+            for b_ in self.buckets:
+                b_.last_algo = b_.algo
             early = self.buckets[1]
             ars_early = (FusedArParams * 2)(early.struct(0), early.struct(1))
             _lib.check(self.lib.tfdl_cnn_program_create2(steps, ars, last.algo, ars_early, early.algo, use_graph,
                                                          C.byref(prog)), "cnn_program_create2")
         else:
             full = self.state
+            full.last_algo = full.algo
             ars = (FusedArParams * 2)(full.struct(0), full.struct(1))
             ars_early = None
             _lib.check(self.lib.tfdl_cnn_program_create(steps, ars, full.algo, use_graph, C.byref(prog)),
