@@ -78,6 +78,7 @@ struct Group {
   std::vector<int> hb;    // same indexing
   std::thread hb_thread;
   std::atomic<int> failed_rank{-1};
+  uint64_t ring_seq = 0;  // collectives issued on the ring so far (header check in ring_allreduce)
   // host-visible word that device kernels poll inside their spin loops (pinned, device-mapped memory owned by the
   // caller): the heartbeat thread stores failed_rank + 1 there the moment a peer is declared dead, which releases every
   // kernel waiting for that peer's gradients instead of letting it spin into its trap limit
@@ -456,9 +457,25 @@ static int ring_allreduce(Group* g, T* buf, int64_t n) {
   size_t maxseg = 0;
   for (int i = 0; i < W; ++i) maxseg = std::max<size_t>(maxseg, (off[i + 1] - off[i]) * sizeof(T));
   if (g->scratch.size() < maxseg) g->scratch.resize(maxseg);
+  const int prev = (R + W - 1) % W, next = (R + 1) % W;
+  // Every ring collective starts with a header {magic, element size, count, sequence number} to the next rank, checked
+  // against the previous rank's: workers that fell out of step (one left its epoch early and started the float64 metric
+  // reduction while its peers are still in the float32 gradient reduction) fail here with a message instead of consuming
+  // each other's bytes as data.
+  {
+    struct Hdr { uint32_t magic, elem; int64_t n; uint64_t seq; } mine{0x52444654u, (uint32_t)sizeof(T), n, g->ring_seq++}, theirs{};
+    if (int hrc = g->io_all(g->ring_send, &mine, sizeof(mine), true, next, "ring all-reduce header")) return hrc;
+    if (int hrc = g->io_all(g->ring_recv, &theirs, sizeof(theirs), false, prev, "ring all-reduce header")) return hrc;
+    if (theirs.magic != mine.magic || theirs.elem != mine.elem || theirs.n != mine.n || theirs.seq != mine.seq) {
+      set_error("ring all-reduce out of step: this rank (%d) is in collective #%llu (%lld elements of %u bytes) but rank %d "
+                "sent the header of collective #%llu (%lld elements of %u bytes) - the workers ran different numbers of steps",
+                R, (unsigned long long)mine.seq, (long long)mine.n, mine.elem, prev, (unsigned long long)theirs.seq,
+                (long long)theirs.n, theirs.elem);
+      return -4;
+    }
+  }
   set_nonblock(g->ring_send, true);
   set_nonblock(g->ring_recv, true);
-  const int prev = (R + W - 1) % W, next = (R + 1) % W;
   int rc = 0;
   for (int phase = 0; phase < 2 && rc == 0; ++phase) {
     for (int s = 0; s < W - 1 && rc == 0; ++s) {

@@ -8,7 +8,20 @@ if ROOT not in sys.path:
     sys.path.insert(0, ROOT)
 
 
+def _strict_fp32_oracles():
+    """Torch stays the second oracle in several GPU tests: keep its fp32 convolutions / matmuls at full precision (no TF32),
+    so that a comparison 'against fp32' means fp32."""
+    try:
+        import torch
+
+        torch.backends.cudnn.allow_tf32 = False
+        torch.backends.cuda.matmul.allow_tf32 = False
+    except Exception:  # pragma: no cover
+        pass
+
+
 def pytest_configure(config):
+    _strict_fp32_oracles()
     config.addinivalue_line("markers", "gpu: needs a CUDA device (run on the B200 box with -m gpu)")
     config.addinivalue_line("markers", "multigpu: needs >= 2 CUDA devices")
 

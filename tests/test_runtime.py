@@ -147,3 +147,26 @@ def test_pack_records_matches_numpy(ydt):
         np.testing.assert_array_equal(ring[i, :B * 784 * 4].view(np.float32), xs[i].reshape(-1))
         np.testing.assert_array_equal(ring[i, B * 784 * 4:].view(np.int32), ys[i].astype(np.int32))
     assert not ring[k].any()
+
+
+def _w_desync(rank, addrs):
+    """Workers that fell out of step: rank 0 reduces 10 float32 gradients while rank 1 already reduces 4 float64 metric
+    totals (what happens when one worker's data runs out a step early)."""
+    from tfdl.runtime import native
+
+    g = native.Group(rank, addrs, timeout_s=10, hb_timeout_s=5)
+    try:
+        if rank == 0:
+            g.allreduce_(np.ones(10, np.float32))
+        else:
+            g.allreduce_(np.ones(4, np.float64))
+    except Exception as e:  # noqa: BLE001
+        return f"{type(e).__name__}: {e}"
+    finally:
+        g.close()
+    return "no error"
+
+
+def test_ring_collectives_out_of_step_fail_with_a_message():
+    res = run_workers(_w_desync, 2, timeout=60)
+    assert all("out of step" in v[1] for v in res.values()), res
