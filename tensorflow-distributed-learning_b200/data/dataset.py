@@ -942,7 +942,14 @@ def auto_shard(ds: Dataset, num_workers: int, worker_index: int,
     if use_file:
         sharded: Dataset = _FileShardDataset(target, num_workers, worker_index)
     else:
-        sharded = _ShardDataset(target, num_workers, worker_index)
+        # Every worker must run the same number of steps per epoch: a worker whose shard is one element longer would
+        # enter one more gradient collective than its peers. With a known element count the tail that does not divide
+        # by the number of workers (at most num_workers - 1 elements) is left out of the epoch, so all shards are equal.
+        c = target.cardinality()
+        even: Dataset = target
+        if c >= 0 and c % num_workers:
+            even = _TakeSkipDataset(target, c - c % num_workers, True)
+        sharded = _ShardDataset(even, num_workers, worker_index)
     if batch is None:
         return sharded
     return _rebuild_above(ds, target, sharded)
