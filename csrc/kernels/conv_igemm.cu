@@ -408,7 +408,7 @@ extern "C" int tfdl_conv2d_dgrad(const void* dy, const void* w, void* dx, int N,
   const long M = (long)N * H * W;
   TFDL_REQUIRE(M < (1l << 31), "conv2d_dgrad: too many pixels");
   if (int rc = make_tmap_out(&tmD, dx, M, C, C, false)) return rc;
-  const int BN = C <= 64 ? 64 : 128;
+  const int BN = C <= 64 ? 64 : ((C >= 256 && (long)((M + 127) / 128) * ((C + 255) / 256) >= 120) ? 256 : 128);
   TmaGemmParams p{};
   p.Dh = (__nv_bfloat16*)dx; p.M = (int)M; p.N = C; p.K = R * S * K; p.ldd = C; p.act = 0; p.ksplit = 1; p.tma_store = 1;
   p.m_tiles = (p.M + BM - 1) / BM; p.n_tiles = (C + BN - 1) / BN;
@@ -416,7 +416,8 @@ extern "C" int tfdl_conv2d_dgrad(const void* dy, const void* w, void* dx, int N,
   fill_geom(g, H, W, lh, lw, 1, 1, R, S, K, C, 1);
   cudaStream_t s = (cudaStream_t)stream;
   if (BN == 64) return launch_conv<64, 8>(tmA, tmB, tmD, p, g, s);
-  return launch_conv<128, 6>(tmA, tmB, tmD, p, g, s);
+  if (BN == 128) return launch_conv<128, 6>(tmA, tmB, tmD, p, g, s);
+  return launch_conv<256, 4>(tmA, tmB, tmD, p, g, s);
 }
 
 // dw[K][R][S][C] (fp32, ACCUMULATED: zero it first - or point it at a cleared gradient arena) += dy^T * im2col(x).
@@ -442,9 +443,16 @@ extern "C" int tfdl_conv2d_wgrad(const void* x, const void* dy, float* dw, int N
   p.Df = dw; p.M = K; p.N = n_units * 64; p.K = (int)M; p.ldd = R * S * C; p.act = 0; p.tma_store = 1;
   p.m_tiles = (K + BM - 1) / BM; p.n_tiles = (n_units + BN / 64 - 1) / (BN / 64);
   const int k_blocks = (int)((M + BK - 1) / BK), tiles = p.m_tiles * p.n_tiles;
-  int ks = (2 * 148 + tiles - 1) / tiles;           // about two waves of work units
-  if (ks > k_blocks / 4) ks = k_blocks / 4;         // but at least four pixel blocks per unit
-  if (ks < 1) ks = 1;
+  // Split factor: the kernel's time is (waves of work units over 148 SMs) x (K blocks per unit + a fixed per-unit cost of
+  // about six blocks for the accumulator hand-over and the reduce-add epilogue); take the split that minimises it, with
+  // at least four pixel blocks per unit.
+  int ks = 1;
+  long best = -1;
+  for (int c = 1; c <= 64 && c <= (k_blocks + 3) / 4; ++c) {
+    const long waves = ((long)tiles * c + 147) / 148;
+    const long cost = waves * ((k_blocks + c - 1) / c + 6);
+    if (best < 0 || cost < best) { best = cost; ks = c; }
+  }
   const int k_per = (k_blocks + ks - 1) / ks;
   p.ksplit = (k_blocks + k_per - 1) / k_per;        // no empty split
   return launch_conv<BN, 6>(tmA, tmB, tmD, p, g, (cudaStream_t)stream);
