@@ -105,6 +105,41 @@ __device__ __forceinline__ float4 sgd_update(float4 w, float4 g, float4* v, cons
   return w;
 }
 
+// Adam (tf.keras.optimizers.Adam: m = b1 m + (1-b1) g, v = b2 v + (1-b2) g^2, w -= lr_t m / (sqrt(v) + eps) with the bias
+// correction folded into lr_t = lr sqrt(1 - b2^t) / (1 - b1^t)). Selected by hyper.beta2 > 0; `m` and `v` are the two slot
+// arenas; the step number t is the kernel's own epoch counter plus hyper.t_offset (restored runs), so LR schedules and
+// the bias correction need no re-capture of a step graph.
+struct OptStep {
+  bool adam;
+  float lr_t;
+};
+__device__ __forceinline__ OptStep opt_step(const TfdlHyper& h, uint32_t e) {
+  OptStep o;
+  o.adam = h.beta2 > 0.f;
+  o.lr_t = h.lr;
+  if (o.adam) {
+    const float t = (float)e + h.t_offset;
+    o.lr_t = h.lr * sqrtf(1.f - powf(h.beta2, t)) / (1.f - powf(h.beta1, t));
+  }
+  return o;
+}
+__device__ __forceinline__ float adam1(float w, float g, float& m, float& v, const TfdlHyper& h, float lr_t) {
+  m = h.beta1 * m + (1.f - h.beta1) * g;
+  v = h.beta2 * v + (1.f - h.beta2) * g * g;
+  return w - lr_t * m / (sqrtf(v) + h.eps);
+}
+__device__ __forceinline__ float4 opt_update(float4 w, float4 g, float4* mp, float4* vp, const TfdlHyper& h, const OptStep& o) {
+  if (!o.adam) return sgd_update(w, g, mp, h);
+  float4 m = *mp, v = *vp;
+  w.x = adam1(w.x, g.x, m.x, v.x, h, o.lr_t);
+  w.y = adam1(w.y, g.y, m.y, v.y, h, o.lr_t);
+  w.z = adam1(w.z, g.z, m.z, v.z, h, o.lr_t);
+  w.w = adam1(w.w, g.w, m.w, v.w, h, o.lr_t);
+  *mp = m;
+  *vp = v;
+  return w;
+}
+
 // Scalar tail for element counts that are not a multiple of 4 (the vector loops cover [0, n & ~3)).
 __device__ __forceinline__ float ld_peer_f1(const float* p) {
   float v;
@@ -151,12 +186,14 @@ __global__ void __launch_bounds__(512) fused_ar_oneshot_kernel(TfdlFusedArParams
   const int W = p.world;
   float4* w4 = reinterpret_cast<float4*>(p.params[p.rank]);
   float4* v4 = reinterpret_cast<float4*>(p.mom);
+  float4* u4 = reinterpret_cast<float4*>(p.mom2);
+  const OptStep os = opt_step(h, e);
   uint2* s2 = reinterpret_cast<uint2*>(p.shadow[p.rank]);
   float4* z4 = reinterpret_cast<float4*>(p.grads[par ^ 1][p.rank]);
   for (int64_t i = (int64_t)blockIdx.x * blockDim.x + threadIdx.x; i < n4; i += (int64_t)gridDim.x * blockDim.x) {
     float4 g = gather_sum(p.grads[par], i, W, p.rank);
     g.x *= h.scale; g.y *= h.scale; g.z *= h.scale; g.w *= h.scale;
-    float4 w = sgd_update(w4[i], g, v4 ? v4 + i : nullptr, h);
+    float4 w = opt_update(w4[i], g, v4 ? v4 + i : nullptr, u4 ? u4 + i : nullptr, h, os);
     w4[i] = w;
     if (s2) s2[i] = to_bf16x4(w);
     if (z4) z4[i] = make_float4(0.f, 0.f, 0.f, 0.f);
@@ -165,8 +202,10 @@ __global__ void __launch_bounds__(512) fused_ar_oneshot_kernel(TfdlFusedArParams
     for (int64_t i = n4 * 4; i < p.n; ++i) {
       float4 g = make_float4(gather_sum1(p.grads[par], i, W, p.rank) * h.scale, 0.f, 0.f, 0.f);
       float4 m = p.mom ? make_float4(p.mom[i], 0.f, 0.f, 0.f) : g;
-      float4 w = sgd_update(make_float4(p.params[p.rank][i], 0.f, 0.f, 0.f), g, p.mom ? &m : nullptr, h);
+      float4 v2 = p.mom2 ? make_float4(p.mom2[i], 1.f, 1.f, 1.f) : g;
+      float4 w = opt_update(make_float4(p.params[p.rank][i], 0.f, 0.f, 0.f), g, p.mom ? &m : nullptr, p.mom2 ? &v2 : nullptr, h, os);
       if (p.mom) p.mom[i] = m.x;
+      if (p.mom2) p.mom2[i] = v2.x;
       p.params[p.rank][i] = w.x;
       if (p.shadow[p.rank]) reinterpret_cast<__nv_bfloat16*>(p.shadow[p.rank])[i] = __float2bfloat16(w.x);
       if (p.grads[par ^ 1][p.rank]) p.grads[par ^ 1][p.rank][i] = 0.f;
@@ -206,6 +245,8 @@ __global__ void __launch_bounds__(512) fused_ar_sliced_kernel(TfdlFusedArParams 
   const int64_t lo = per * p.rank, hi = min(n4, lo + per);
   const int64_t tid = (int64_t)blockIdx.x * blockDim.x + threadIdx.x, nth = (int64_t)gridDim.x * blockDim.x;
   float4* v4 = reinterpret_cast<float4*>(p.mom);
+  float4* u4 = reinterpret_cast<float4*>(p.mom2);
+  const OptStep os = opt_step(h, e);
   const float4* w_own = reinterpret_cast<const float4*>(p.params[p.rank]);
   for (int64_t i0 = lo + tid; i0 < hi; i0 += nth * U) {
     float4 g[U];
@@ -221,7 +262,7 @@ __global__ void __launch_bounds__(512) fused_ar_sliced_kernel(TfdlFusedArParams 
       if (i >= hi) continue;
       float4 gg = g[u];
       gg.x *= h.scale; gg.y *= h.scale; gg.z *= h.scale; gg.w *= h.scale;
-      const float4 w = sgd_update(w_own[i], gg, v4 ? v4 + i : nullptr, h);
+      const float4 w = opt_update(w_own[i], gg, v4 ? v4 + i : nullptr, u4 ? u4 + i : nullptr, h, os);
       if (MC) {
         mc_st_f4(reinterpret_cast<float4*>(p.mc_params) + i, w);
       } else {
@@ -364,13 +405,15 @@ __global__ void __launch_bounds__(256) fused_ar_push_kernel(TfdlFusedArParams p)
   const uint4* mine = reinterpret_cast<const uint4*>(p.inbox[rank]) + (int64_t)ipar * W * region;
   float4* w4 = reinterpret_cast<float4*>(p.params[rank]);
   float4* v4 = reinterpret_cast<float4*>(p.mom);
+  float4* u4 = reinterpret_cast<float4*>(p.mom2);
+  const OptStep os = opt_step(h, e);
   uint2* s2 = reinterpret_cast<uint2*>(p.shadow[rank]);
   float4* z4 = reinterpret_cast<float4*>(p.grads[par ^ 1][rank]);
   for (int64_t i = tid; i < n4; i += nth) {
     float4 g;
     if (!poll_sum(mine, region, i, W, rank, e, g4[i], p.abort_word, g)) return;
     g.x *= h.scale; g.y *= h.scale; g.z *= h.scale; g.w *= h.scale;
-    float4 w = sgd_update(w4[i], g, v4 ? v4 + i : nullptr, h);
+    float4 w = opt_update(w4[i], g, v4 ? v4 + i : nullptr, u4 ? u4 + i : nullptr, h, os);
     w4[i] = w;
     if (s2) s2[i] = to_bf16x4(w);
     if (z4) z4[i] = make_float4(0.f, 0.f, 0.f, 0.f);
@@ -392,6 +435,8 @@ __global__ void __launch_bounds__(256) fused_ar_push2_kernel(TfdlFusedArParams p
   const float4* g4 = reinterpret_cast<const float4*>(p.grads[par][rank]);
   float4* w4 = reinterpret_cast<float4*>(p.params[rank]);
   float4* v4 = reinterpret_cast<float4*>(p.mom);
+  float4* u4 = reinterpret_cast<float4*>(p.mom2);
+  const OptStep os = opt_step(h, e);
   uint2* s2 = reinterpret_cast<uint2*>(p.shadow[rank]);
   const int64_t tid = (int64_t)blockIdx.x * blockDim.x + threadIdx.x, nth = (int64_t)gridDim.x * blockDim.x;
   const int64_t hop0 = ((int64_t)ipar * 2 + 0) * W * region, hop1 = ((int64_t)ipar * 2 + 1) * W * region;
@@ -407,7 +452,7 @@ __global__ void __launch_bounds__(256) fused_ar_push2_kernel(TfdlFusedArParams p
     float4 g;
     if (!poll_sum(in0, region, i - lo, W, rank, e, g4[i], p.abort_word, g)) return;
     g.x *= h.scale; g.y *= h.scale; g.z *= h.scale; g.w *= h.scale;
-    float4 w = sgd_update(w4[i], g, v4 ? v4 + i : nullptr, h);
+    float4 w = opt_update(w4[i], g, v4 ? v4 + i : nullptr, u4 ? u4 + i : nullptr, h, os);
     w4[i] = w;
     if (s2) s2[i] = to_bf16x4(w);
 #pragma unroll
@@ -599,6 +644,7 @@ extern "C" int tfdl_fused_allreduce_sgd(const TfdlFusedArParams* p, int algo, vo
                "fused_allreduce_sgd: n=%lld is not a multiple of 4: only the one-shot path takes a ragged tail "
                "(parameter arenas are padded to 16 bytes)", (long long)p->n);
   TFDL_REQUIRE(p->epoch && p->done && p->hyper, "fused_allreduce_sgd: epoch/done/hyper pointers are required");
+  // (Adam, hyper.beta2 > 0, needs both slot arenas; the kernels cannot check device memory here, the Python side does)
   TFDL_REQUIRE(p->world == 1 || p->flags[p->rank], "fused_allreduce_sgd: flag pads missing");
   cudaStream_t s = (cudaStream_t)stream;
   const int threads = 256;

@@ -174,6 +174,7 @@ enum { TFDL_AR_ONESHOT = 0, TFDL_AR_TWOSHOT = 1, TFDL_AR_MULTIMEM = 2, TFDL_AR_P
 
 typedef struct {
   float lr, momentum, nesterov, scale; /* read on the device each step: LR schedules need no re-capture */
+  float beta1, beta2, eps, t_offset;   /* Adam when beta2 > 0 (slots mom = m, mom2 = v); step number = epoch counter + t_offset */
 } TfdlHyper;
 
 typedef struct {
@@ -196,6 +197,7 @@ typedef struct {
   int parity;                           /* gradient buffer of this step: 0/1 fixed by the host, -1 = (epoch & 1) */
   void* inbox[TFDL_MAX_RANKS];          /* push / push2 only: every rank's packet inbox (peer-mapped, zeroed once) */
   int64_t inbox_bytes;                  /* size of each inbox, >= tfdl_fused_ar_inbox_bytes(algo, world, n) */
+  float* mom2;                          /* second slot arena (Adam's v) or NULL */
 } TfdlFusedArParams;
 
 /* TFDL_AR_PUSH / TFDL_AR_PUSH2 move 16-byte {value, epoch, value, epoch} packets into the peers' inboxes instead of

@@ -561,15 +561,26 @@ class TorchEngine:
         self._comm_stream: Any = None
         self.launches_per_step = 0
         ops = self.strategy.cross_device_ops
-        if (type(ops).__name__ == "P2PFusedAllReduce" and isinstance(model.optimizer, _optimizers.SGD)
+        opt0 = model.optimizer
+        fusable = isinstance(opt0, _optimizers.SGD) or (isinstance(opt0, _optimizers.Adam) and not opt0.weight_decay)
+        if (type(ops).__name__ == "P2PFusedAllReduce" and fusable
                 and len(self.devices) == 1 and os.environ.get("TFDL_TORCH_FUSED_AR", "1") == "1"):
             # GPU process group + SGD: the gradient all-reduce, 1/N scale and the (momentum) update are ONE
             # NVLink kernel over the arena (ops/allreduce.py) even though forward/backward run on torch ops.
             # A single gradient buffer is used here, so only the variants with an end barrier are legal.
             arena = model.arenas[0]
-            st = ops.fused_state(arena.params, arena.grads, momentum=bool(model.optimizer.momentum))
-            if model.optimizer.momentum:
-                model.optimizer._slots = {"momentum": [st.mom]}
+            is_adam = isinstance(opt0, _optimizers.Adam)
+            st = ops.fused_state(arena.params, arena.grads, momentum=bool(getattr(opt0, "momentum", 0.0)), adam=is_adam)
+            if is_adam:
+                # the optimizer's slots ARE the kernel's arenas (values restored from a checkpoint before this point move in)
+                old = dict(opt0._slots) if opt0._slots else {}
+                for name, buf in (("m", st.mom), ("v", st.mom2)):
+                    if old.get(name):
+                        buf.copy_(old[name][0])
+                opt0._slots = {"m": [st.mom], "v": [st.mom2]}
+                self._adam_steps0 = int(opt0.iterations)  # Adam's t before this state's first kernel
+            elif opt0.momentum:
+                opt0._slots = {"momentum": [st.mom]}
             from ..ops.structs import AR_MULTIMEM, AR_ONESHOT, AR_TWOSHOT
 
             st.torch_algo = AR_ONESHOT if ops.world == 1 else (AR_MULTIMEM if st.has_multicast else AR_TWOSHOT)
@@ -721,7 +732,9 @@ class TorchEngine:
     def _graph_eligible(self) -> bool:
         if self._graph_off or len(self.devices) != 1 or self.devices[0].type != "cuda":
             return False
-        if not isinstance(self.model.optimizer, _optimizers.SGD) or callable(getattr(self.model.optimizer, "_lr", None)):
+        opt = self.model.optimizer
+        ok_opt = isinstance(opt, _optimizers.SGD) or (isinstance(opt, _optimizers.Adam) and self._fused is not None)
+        if not ok_opt or callable(getattr(opt, "_lr", None)):
             return False
         return os.environ.get("TFDL_TORCH_GRAPH", "1") == "1"
 
@@ -731,11 +744,16 @@ class TorchEngine:
             if self._fused_lr != opt.learning_rate:
                 self._fused_lr = opt.learning_rate
                 for st in [self._fused] + [b for b, _ in self._buckets]:
-                    st.set_hyper(opt.learning_rate, opt.momentum, opt.nesterov, 1.0)
+                    if isinstance(opt, _optimizers.Adam):
+                        st.set_hyper(opt.learning_rate, 0.0, False, 1.0, opt.beta_1, opt.beta_2, opt.epsilon,
+                                     float(self._adam_steps0))
+                    else:
+                        st.set_hyper(opt.learning_rate, opt.momentum, opt.nesterov, 1.0)
 
     def _train_step_graphed(self, xt: torch.Tensor, yt: torch.Tensor) -> None:
         opt = self.model.optimizer
-        key = (tuple(xt.shape), xt.dtype, tuple(yt.shape), yt.dtype, float(opt.learning_rate), opt.momentum, opt.nesterov)
+        key = (tuple(xt.shape), xt.dtype, tuple(yt.shape), yt.dtype, float(opt.learning_rate),
+               getattr(opt, "momentum", 0.0), getattr(opt, "nesterov", False))
         self._sync_hyper()
         ent = self._graphs.get(key)
         if ent is None:

@@ -149,11 +149,18 @@ class P2PFusedAllReduce(CrossDeviceOps):
         raise RuntimeError("tensor was not allocated through P2PFusedAllReduce.alloc_arena")
 
     # ---- fused state for a (params, grads) pair ---------------------------------------------
-    def fused_state(self, params: torch.Tensor, grads: torch.Tensor, momentum: bool) -> "FusedState":
+    def fused_state(self, params: torch.Tensor, grads: torch.Tensor, momentum: bool, adam: bool = False) -> "FusedState":
         key = params.data_ptr()
         if key not in self._states:
-            self._states[key] = FusedState(self, self._find(params), self._find(grads), momentum)
-        return self._states[key]
+            self._states[key] = FusedState(self, self._find(params), self._find(grads), momentum or adam, adam=adam)
+        st = self._states[key]
+        if (momentum or adam) and st.mom is None:
+            st.mom = torch.zeros(st.n, dtype=torch.float32, device=self.device)
+        if adam and st.mom2 is None:
+            st.mom2 = torch.zeros(st.n, dtype=torch.float32, device=self.device)
+        if (momentum or adam) and st._structs[0].mom is None or (adam and st._structs[0].mom2 is None):
+            st._structs = [st._make_struct(par) for par in (0, 1)]
+        return st
 
     # ---- CrossDeviceOps interface (used by the torch engine on GPU and by tests) ----------------
     def allreduce_grads(self, grads: Sequence[torch.Tensor]) -> None:
@@ -251,12 +258,16 @@ class P2PFusedAllReduce(CrossDeviceOps):
                 buf = self.make_buffer(n, torch.float32)
                 st._gather_tmp = (buf, FusedState(self, None, buf, False, plain=True))
             buf, plain = st._gather_tmp
-            view = st.mom[st.offset:st.offset + n]
-            buf.tensor.zero_()
-            buf.tensor[lo:hi].copy_(view[lo:hi])
-            self.group_barrier()
-            plain.allreduce_sum()
-            view.copy_(buf.tensor)
+            for slot in (st.mom, st.mom2):
+                if slot is None:
+                    continue
+                view = slot[st.offset:st.offset + n]
+                buf.tensor.zero_()
+                buf.tensor[lo:hi].copy_(view[lo:hi])
+                self.group_barrier()
+                plain.allreduce_sum()
+                view.copy_(buf.tensor)
+                torch.cuda.synchronize(self.device)
         torch.cuda.synchronize(self.device)
 
     def broadcast_params(self, params: Sequence[torch.Tensor]) -> None:
@@ -304,7 +315,7 @@ class FusedState:
     """Everything the fused kernel needs for one arena: extra buffers, counters, the C struct."""
 
     def __init__(self, ops: P2PFusedAllReduce, params: Optional[SymmetricBuffer], grads0: SymmetricBuffer,
-                 momentum: bool, plain: bool = False) -> None:
+                 momentum: bool, plain: bool = False, adam: bool = False) -> None:
         self.ops = ops
         dev, W, R = ops.device, ops.world, ops.rank
         n = grads0.numel
@@ -316,10 +327,11 @@ class FusedState:
             self.grads.append(ops.make_buffer(n, torch.float32))
             self.shadow = ops.make_buffer(n, torch.bfloat16)
         self.mom = torch.zeros(n, dtype=torch.float32, device=dev) if momentum else None
+        self.mom2 = torch.zeros(n, dtype=torch.float32, device=dev) if adam else None  # Adam's second-moment slot
         self.pad_stride = MAX_BLOCKS * max(W, 1)
         self.flags = ops.make_buffer(3 * self.pad_stride, torch.int32) if W > 1 else None
         self.counters = torch.zeros(4, dtype=torch.int32, device=dev)  # epoch, done, abort, pad
-        self.hyper = torch.zeros(4, dtype=torch.float32, device=dev)
+        self.hyper = torch.zeros(8, dtype=torch.float32, device=dev)
         self.has_multicast = bool(W > 1 and grads0.multicast_ptr and (plain or (
             params is not None and params.multicast_ptr and self.grads[1].multicast_ptr)))
         self.algo = pick_algo(n * 4, W, self.has_multicast) if not plain else (
@@ -344,12 +356,12 @@ class FusedState:
         assert offset % 4 == 0 and length % 4 == 0 and offset + length <= self.n
         b = FusedState.__new__(FusedState)
         b.ops, b.n, b.offset, b.max_blocks = self.ops, length, offset, max_blocks
-        b.params, b.grads, b.shadow, b.mom = self.params, self.grads, self.shadow, self.mom
+        b.params, b.grads, b.shadow, b.mom, b.mom2 = self.params, self.grads, self.shadow, self.mom, self.mom2
         dev, W, R = self.ops.device, self.ops.world, self.ops.rank
         b.pad_stride = self.pad_stride
         b.flags = self.ops.make_buffer(3 * b.pad_stride, torch.int32) if W > 1 else None
         b.counters = torch.zeros(4, dtype=torch.int32, device=dev)
-        b.hyper = torch.zeros(4, dtype=torch.float32, device=dev)
+        b.hyper = torch.zeros(8, dtype=torch.float32, device=dev)
         b.has_multicast = self.has_multicast
         b.algo = pick_algo(length * 4, W, b.has_multicast)
         b.inbox = None
@@ -393,6 +405,7 @@ class FusedState:
             if self.flags is not None:
                 p.flags[r] = self.flags.ptrs[r]
         p.mom = self.mom.data_ptr() + o4 if self.mom is not None else None
+        p.mom2 = self.mom2.data_ptr() + o4 if self.mom2 is not None else None
         p.pad_stride = self.pad_stride
         p.max_blocks = self.max_blocks
         if self.has_multicast:
@@ -415,8 +428,13 @@ class FusedState:
     def struct(self, parity: int) -> FusedArParams:
         return self._structs[parity]
 
-    def set_hyper(self, lr: float, momentum: float = 0.0, nesterov: bool = False, scale: float = 1.0) -> None:
-        self.hyper.copy_(torch.tensor([lr, momentum, 1.0 if nesterov else 0.0, scale], dtype=torch.float32))
+    def set_hyper(self, lr: float, momentum: float = 0.0, nesterov: bool = False, scale: float = 1.0, beta1: float = 0.0,
+                  beta2: float = 0.0, eps: float = 0.0, t_offset: float = 0.0) -> None:
+        """SGD / momentum / Nesterov, or - with beta2 > 0 - Adam (both slot arenas must exist). t_offset: optimizer steps
+        taken before this state's first kernel (the kernel's own step counter supplies the rest of Adam's t)."""
+        assert beta2 == 0.0 or (self.mom is not None and self.mom2 is not None), "Adam needs the m and v slot arenas"
+        self.hyper.copy_(torch.tensor([lr, momentum, 1.0 if nesterov else 0.0, scale, beta1, beta2, eps, t_offset],
+                                      dtype=torch.float32))
 
     def refresh_shadow(self) -> None:
         """fp32 master -> bf16 shadow (after set_weights / load_weights / broadcast)."""
@@ -572,4 +590,6 @@ class MirroredPeerAllReduce(CrossDeviceOps):
                     if q != r and hi > lo:
                         dst = per_rank[q][i]
                         dst.mom[dst.offset + lo:dst.offset + hi].copy_(src.mom[src.offset + lo:src.offset + hi])
+                        if src.mom2 is not None:
+                            dst.mom2[dst.offset + lo:dst.offset + hi].copy_(src.mom2[src.offset + lo:src.offset + hi])
         self.barrier()

@@ -9,7 +9,8 @@ AR_NAMES = {AR_ONESHOT: "oneshot", AR_TWOSHOT: "twoshot", AR_MULTIMEM: "multimem
 
 
 class Hyper(C.Structure):
-    _fields_ = [("lr", C.c_float), ("momentum", C.c_float), ("nesterov", C.c_float), ("scale", C.c_float)]
+    _fields_ = [("lr", C.c_float), ("momentum", C.c_float), ("nesterov", C.c_float), ("scale", C.c_float),
+                ("beta1", C.c_float), ("beta2", C.c_float), ("eps", C.c_float), ("t_offset", C.c_float)]
 
 
 class FusedArParams(C.Structure):
@@ -33,6 +34,7 @@ class FusedArParams(C.Structure):
         ("parity", C.c_int),
         ("inbox", C.c_void_p * MAX_RANKS),
         ("inbox_bytes", C.c_int64),
+        ("mom2", C.c_void_p),
     ]
 
 

@@ -84,6 +84,48 @@ def main() -> None:
                 assert torch.equal(gathered[0], gathered[r]), f"rank {r} diverged ({AR_NAMES[algo]}, n={n})"
             report[f"fused_{AR_NAMES[algo]}_{n}"] = "ok"
 
+    # ---- fused Adam (both slot arenas, bias correction from the kernel's own step counter) on every kind of path -------
+    n = 225280
+    params, grads = ops.alloc_arena(n, dev), ops.alloc_arena(n, dev)
+    st = ops.fused_state(params, grads, momentum=False, adam=True)
+    for algo in [AR_PUSH, AR_PUSH2, AR_TWOSHOT]:
+        torch.manual_seed(2)
+        w0 = torch.randn(n, device=dev)
+        params.copy_(w0)
+        st.mom.zero_()
+        st.mom2.zero_()
+        st.counters[0:1].zero_()  # Adam's t restarts at 1 (every rank, same point of its stream)
+        for g in st.grads:
+            g.tensor.zero_()
+        lr, b1, b2, eps = 1e-2, 0.9, 0.999, 1e-7
+        st.set_hyper(lr, 0.0, False, 1.0 / world, b1, b2, eps, 0.0)
+        torch.cuda.synchronize(dev)
+        dist.barrier()
+        w_ref, m_ref, v_ref = w0.clone(), torch.zeros(n, device=dev), torch.zeros(n, device=dev)
+        for s in range(5):
+            par = s & 1
+            gs = [torch.randn(n, generator=torch.Generator(device="cpu").manual_seed(1000 * s + r)).to(dev) for r in range(world)]
+            st.grads[par].tensor.copy_(gs[rank])
+            st.step(par, algo)
+            gsum = gs[0].clone()
+            for r in range(1, world):
+                gsum += gs[r]
+            gsum *= 1.0 / world
+            m_ref = b1 * m_ref + (1 - b1) * gsum
+            v_ref = b2 * v_ref + (1 - b2) * gsum * gsum
+            t = s + 1
+            w_ref = w_ref - lr * (1 - b2 ** t) ** 0.5 / (1 - b1 ** t) * m_ref / (v_ref.sqrt() + eps)
+        torch.cuda.synchronize(dev)
+        torch.testing.assert_close(params, w_ref, rtol=2e-4, atol=2e-5)
+        ops.sync_optimizer_slots()
+        torch.testing.assert_close(st.mom, m_ref, rtol=1e-4, atol=1e-6)
+        torch.testing.assert_close(st.mom2, v_ref, rtol=1e-4, atol=1e-7)
+        gathered = [torch.empty_like(params) for _ in range(world)]
+        dist.all_gather(gathered, params)
+        for r in range(1, world):
+            assert torch.equal(gathered[0], gathered[r]), f"rank {r} diverged (adam, {AR_NAMES[algo]})"
+        report[f"fused_adam_{AR_NAMES[algo]}"] = "ok"
+
     # ---- plain in-place sum (odd sizes) --------------------------------------------------------------
     for n in (4, 7, 1001, (1 << 20) + 3):  # element counts that are not multiples of 4: the kernels finish the tail
         buf = ops.alloc_arena(n, dev)

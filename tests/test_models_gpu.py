@@ -99,3 +99,27 @@ def test_modified_reference_cnn_stays_on_native_kernels(monkeypatch):
     assert calls["small"] >= 1 and calls["conv"] >= 1 and calls["pool"] >= 2, calls
     ref, _ = _train(build, batches, "float32", monkeypatch, {"TFDL_TORCH_GRAPH": "0", "TFDL_NATIVE_OPS": "0"})
     np.testing.assert_allclose(native, ref, rtol=3e-2, atol=3e-2)
+
+
+def test_fused_adam_matches_unfused_adam(monkeypatch):
+    """Adam inside the fused all-reduce + update kernel (csrc/kernels/allreduce.cu:opt_update; bias correction from the
+    kernel's own step counter) against the optimizer's plain tensor-op implementation, same model, same batches."""
+    from tfdl import keras
+
+    def build():
+        m = keras.Sequential([
+            keras.layers.Conv2D(16, 3, activation="relu", padding="same", input_shape=(12, 12, 8)),
+            keras.layers.MaxPooling2D(), keras.layers.Flatten(), keras.layers.Dense(64, activation="relu"),
+            keras.layers.Dense(16)])
+        m.compile(loss=keras.losses.SparseCategoricalCrossentropy(from_logits=True),
+                  optimizer=keras.optimizers.Adam(learning_rate=3e-3))
+        return m
+
+    rng = np.random.default_rng(21)
+    batches = [(rng.random((32, 12, 12, 8), dtype=np.float32), rng.integers(0, 16, size=32)) for _ in range(8)]
+    fused, eng = _train(build, batches, "float32", monkeypatch, {"TFDL_NATIVE_OPS": "0"})
+    plain, _ = _train(build, batches, "float32", monkeypatch, {"TFDL_NATIVE_OPS": "0", "TFDL_TORCH_FUSED_AR": "0",
+                                                                "TFDL_TORCH_GRAPH": "0"})
+    assert eng == "TorchEngine"
+    assert fused[-1] < fused[0]  # it trains
+    np.testing.assert_allclose(fused, plain, rtol=2e-4, atol=2e-4)  # fp32 both ways: only the update's operation order differs
