@@ -94,11 +94,12 @@ def main() -> None:
         params.copy_(w0)
         st.mom.zero_()
         st.mom2.zero_()
-        st.counters[0:1].zero_()  # Adam's t restarts at 1 (every rank, same point of its stream)
         for g in st.grads:
             g.tensor.zero_()
         lr, b1, b2, eps = 1e-2, 0.9, 0.999, 1e-7
-        st.set_hyper(lr, 0.0, False, 1.0 / world, b1, b2, eps, 0.0)
+        torch.cuda.synchronize(dev)
+        done = int(st.counters[0])  # steps this state has already run: Adam's t must restart at 1 for this algorithm
+        st.set_hyper(lr, 0.0, False, 1.0 / world, b1, b2, eps, -float(done))
         torch.cuda.synchronize(dev)
         dist.barrier()
         w_ref, m_ref, v_ref = w0.clone(), torch.zeros(n, device=dev), torch.zeros(n, device=dev)
