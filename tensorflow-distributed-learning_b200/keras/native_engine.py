@@ -64,8 +64,9 @@ def _match(model: Any) -> Optional[Tuple[int, int, int, int, int, int]]:
     if not isinstance(model.loss, _losses.SparseCategoricalCrossentropy) or not model.loss.from_logits \
             or model.loss.ignore_class is not None:
         return None
-    if not isinstance(model.optimizer, _optimizers.SGD):
-        return None
+    opt = model.optimizer
+    if not (isinstance(opt, _optimizers.SGD) or (isinstance(opt, _optimizers.Adam) and not opt.weight_decay)):
+        return None  # SGD / momentum / Nesterov and Adam are fused into the all-reduce kernels
     for m in model.compiled_metrics:
         if not isinstance(m, _metrics.SparseCategoricalAccuracy):
             return None
@@ -131,9 +132,19 @@ class NativeCnnEngine:
                 ops._arenas.append(b)
         self.ops = ops
         opt = model.optimizer
-        self.state: FusedState = ops.fused_state(arena.params, arena.grads, momentum=bool(opt.momentum))
-        if opt.momentum and self.strategy.num_local_replicas == 1:
-            opt._slots = {"momentum": [self.state.mom]}  # the optimizer's slot IS the kernel's buffer
+        self._adam = isinstance(opt, _optimizers.Adam)
+        self.state: FusedState = ops.fused_state(arena.params, arena.grads, momentum=bool(getattr(opt, "momentum", 0.0)),
+                                                 adam=self._adam)
+        self._adam_steps0 = int(opt.iterations)  # Adam's t before this state's first kernel
+        if self.strategy.num_local_replicas == 1:  # the optimizer's slots ARE the kernel's buffers
+            if self._adam:
+                old = dict(opt._slots) if opt._slots else {}
+                for name, buf in (("m", self.state.mom), ("v", self.state.mom2)):
+                    if old.get(name):
+                        buf.copy_(old[name][0])
+                opt._slots = {"m": [self.state.mom], "v": [self.state.mom2]}
+            elif opt.momentum:
+                opt._slots = {"momentum": [self.state.mom]}
         # Gradient buckets (reverse layer order, like the reference's backward): the dense layers' gradients
         # - 91% of the arena - are final right after the fused dense block, so their all-reduce + update runs
         # on its own stream while the conv backward kernels execute; the conv bucket follows at the end.
@@ -172,7 +183,10 @@ class NativeCnnEngine:
         self._lr = opt.learning_rate
         # the whole-arena state is what the unbucketed program (batch sizes the fused dense block does not take) steps
         for b in list(getattr(self, "buckets", [])) + [self.state]:
-            b.set_hyper(self._lr, opt.momentum, opt.nesterov, 1.0)
+            if self._adam:
+                b.set_hyper(self._lr, 0.0, False, 1.0, opt.beta_1, opt.beta_2, opt.epsilon, float(self._adam_steps0))
+            else:
+                b.set_hyper(self._lr, opt.momentum, opt.nesterov, 1.0)
 
     def weights_changed(self) -> None:
         self.state.refresh_shadow()
@@ -593,7 +607,10 @@ class MirroredNativeEngine:
         for r, d in enumerate(self.devices):
             with torch.cuda.device(d):
                 self.replicas.append(NativeCnnEngine(model, shape, replica=r))
-        if model.optimizer.momentum:
+        if isinstance(model.optimizer, _optimizers.Adam):
+            model.optimizer._slots = {"m": [rep.state.mom for rep in self.replicas],
+                                      "v": [rep.state.mom2 for rep in self.replicas]}
+        elif model.optimizer.momentum:
             model.optimizer._slots = {"momentum": [rep.state.mom for rep in self.replicas]}
         self._torch_engine: Any = None
         self.prof = self.replicas[0].prof

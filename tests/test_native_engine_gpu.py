@@ -147,3 +147,31 @@ def test_torch_engine_whole_step_cuda_graph_matches_eager(monkeypatch):
     np.testing.assert_allclose(out["1"][0], out["0"][0], rtol=2e-3)
     for a, b in zip(out["1"][1], out["0"][1]):  # same kernels; library atomics make the two runs differ in the last bits
         np.testing.assert_allclose(a, b, rtol=0, atol=1e-3)
+
+
+def test_native_program_with_adam_tracks_torch_engine():
+    """Adam runs inside the native step program too (fused into the all-reduce + update kernels)."""
+    import tfdl
+    from tfdl import keras
+    from tfdl.models import build_and_compile_cnn_model
+
+    def model(engine):
+        keras.layers.set_init_seed(3)
+        keras.clear_session()
+        s = tfdl.distribute.MirroredStrategy(devices=["gpu:0"])
+        with s.scope():
+            m = build_and_compile_cnn_model(learning_rate=1e-3)
+            m.compile(loss=keras.losses.SparseCategoricalCrossentropy(from_logits=True),
+                      optimizer=keras.optimizers.Adam(learning_rate=2e-3),
+                      metrics=[keras.metrics.SparseCategoricalAccuracy()])
+        m._engine_pref = engine
+        return m
+
+    x, y = _data(64 * 6, seed=8)
+    native, ref = model("native"), model("torch")
+    for i in range(6):
+        xb, yb = x[i * 64:(i + 1) * 64], y[i * 64:(i + 1) * 64]
+        ln, lr_ = native.train_on_batch(xb, yb, return_dict=True), ref.train_on_batch(xb, yb, return_dict=True)
+        assert abs(ln["loss"] - lr_["loss"]) < 3e-2, (i, ln, lr_)
+    assert native.engine_name == "NativeCnnEngine" and ref.engine_name == "TorchEngine"
+    assert ln["loss"] < 2.30  # six Adam steps move the loss
