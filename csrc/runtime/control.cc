@@ -169,7 +169,20 @@ int connect_retry(Group* g, int peer, Channel ch) {
     if (getaddrinfo(host.c_str(), ps, &hints, &res) == 0 && res) {
       int fd = socket(AF_INET, SOCK_STREAM, 0);
       if (fd >= 0) {
-        if (connect(fd, res->ai_addr, res->ai_addrlen) == 0) {
+        // non-blocking connect bounded by the rendezvous deadline: a blocking connect() to an unroutable peer can
+        // sit in the kernel for minutes, far past timeout_ms
+        set_nonblock(fd, true);
+        int cr = connect(fd, res->ai_addr, res->ai_addrlen);
+        if (cr != 0 && errno == EINPROGRESS) {
+          int64_t left = deadline - now_ms();
+          pollfd pf{fd, POLLOUT, 0};
+          int pr = poll(&pf, 1, (int)std::max<int64_t>(1, std::min<int64_t>(left, 1000)));
+          int soerr = 0;
+          socklen_t sl = sizeof(soerr);
+          if (pr > 0 && getsockopt(fd, SOL_SOCKET, SO_ERROR, &soerr, &sl) == 0 && soerr == 0) cr = 0;
+        }
+        if (cr == 0) {
+          set_nonblock(fd, false);
           freeaddrinfo(res);
           set_nodelay(fd);
           Hello h{kMagic, (uint32_t)g->rank, (uint32_t)ch, (uint32_t)g->world};
@@ -236,13 +249,13 @@ void heartbeat_loop(Group* g) {
         if (r > 0) {
           last[peer] = now_ms();
           for (ssize_t k = 0; k < r; ++k) {
-            if (want_rank[peer]) {  // second byte of a failure notice whose 'F' ended the previous recv
+            if (want_rank[peer]) {  // rank byte of a failure notice whose 'F' ended the previous recv
               want_rank[peer] = false;
               if (g->failed_rank.load() < 0) g->failed_rank = (unsigned char)buf[k];
               continue;
             }
             if (buf[k] == 'Q') quit[peer] = true;  // graceful goodbye
-            if (buf[k] == 'F') {                   // failure notice from the leader: next byte = rank
+            if (buf[k] == 'F') {                   // failure notice from the leader: next byte = rank (groups are <= 255 ranks)
               if (k + 1 < r) {
                 if (g->failed_rank.load() < 0) g->failed_rank = (unsigned char)buf[k + 1];
                 ++k;
@@ -285,6 +298,10 @@ void heartbeat_loop(Group* g) {
 extern "C" void* tfdl_rt_group_create(int rank, int world, const char* const* addrs, int timeout_ms,
                                       int hb_interval_ms, int hb_timeout_ms) {
   signal(SIGPIPE, SIG_IGN);
+  if (world > 255) {  // the heartbeat's failure notice carries the rank in one byte
+    set_error("a control group holds at most 255 tasks, got %d", world);
+    return nullptr;
+  }
   if (world < 1 || rank < 0 || rank >= world) {
     set_error("group_create: rank %d out of range for world %d", rank, world);
     return nullptr;
