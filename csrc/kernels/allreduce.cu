@@ -248,6 +248,10 @@ __global__ void __launch_bounds__(512) fused_ar_sliced_kernel(TfdlFusedArParams 
   float4* u4 = reinterpret_cast<float4*>(p.mom2);
   const OptStep os = opt_step(h, e);
   const float4* w_own = reinterpret_cast<const float4*>(p.params[p.rank]);
+  // The other-parity gradient buffer (whole local arena, n4 float4) is cleared INSIDE the reduction loop: the thread
+  // that handles element j of its slice also zeroes elements [j*W, j*W + W) while its NVLink loads are in flight, so
+  // this HBM work hides under the transfer instead of following it (per * W >= n4 covers the arena).
+  float4* z4 = reinterpret_cast<float4*>(p.grads[par ^ 1][p.rank]);
   for (int64_t i0 = lo + tid; i0 < hi; i0 += nth * U) {
     float4 g[U];
 #pragma unroll
@@ -255,6 +259,14 @@ __global__ void __launch_bounds__(512) fused_ar_sliced_kernel(TfdlFusedArParams 
       const int64_t i = i0 + u * nth;
       if (i < hi) g[u] = MC ? mc_ld_reduce_f4(reinterpret_cast<const float4*>(p.mc_grads[par]) + i)
                             : gather_sum(p.grads[par], i, W, p.rank);
+    }
+    if (z4) {
+#pragma unroll
+      for (int u = 0; u < U; ++u) {
+        const int64_t j = i0 + u * nth - lo;
+        if (i0 + u * nth < hi)
+          for (int64_t z = j * W; z < min(n4, j * W + W); ++z) z4[z] = make_float4(0.f, 0.f, 0.f, 0.f);
+      }
     }
 #pragma unroll
     for (int u = 0; u < U; ++u) {
@@ -275,10 +287,9 @@ __global__ void __launch_bounds__(512) fused_ar_sliced_kernel(TfdlFusedArParams 
       }
     }
   }
-  // clear the other-parity gradient buffer (whole local arena)
-  float4* z4 = reinterpret_cast<float4*>(p.grads[par ^ 1][p.rank]);
+  // (a last rank with a short slice leaves a tail of the arena to clear: elements >= (hi - lo) * W)
   if (z4)
-    for (int64_t i = tid; i < n4; i += nth) z4[i] = make_float4(0.f, 0.f, 0.f, 0.f);
+    for (int64_t i = (hi - lo) * W + tid; i < n4; i += nth) z4[i] = make_float4(0.f, 0.f, 0.f, 0.f);
   // end barrier: block b of every peer has stored its part of every slice into my arena
   if (!block_barrier(p, p.pad_stride, e)) return;
   // bf16 shadow of the WHOLE arena, cast locally (the weights travel over NVLink once, as fp32; the shadow never

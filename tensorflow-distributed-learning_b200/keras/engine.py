@@ -583,7 +583,10 @@ class TorchEngine:
                 opt0._slots = {"momentum": [st.mom]}
             from ..ops.structs import AR_MULTIMEM, AR_ONESHOT, AR_TWOSHOT
 
-            st.torch_algo = AR_ONESHOT if ops.world == 1 else (AR_MULTIMEM if st.has_multicast else AR_TWOSHOT)
+            from ..ops.allreduce import MULTIMEM_MIN_WORLD
+
+            st.torch_algo = AR_ONESHOT if ops.world == 1 else (
+                AR_MULTIMEM if (st.has_multicast and ops.world >= MULTIMEM_MIN_WORLD) else AR_TWOSHOT)
             self._fused = st
             st.refresh_shadow()
             self._make_buckets(ops)
@@ -627,7 +630,7 @@ class TorchEngine:
             b = self._fused.bucket(lo, hi - lo)
             algo = pick_algo((hi - lo) * 4, ops.world, b.has_multicast)
             if algo not in (AR_PUSH, AR_PUSH2, AR_MULTIMEM, AR_TWOSHOT):  # one gradient buffer: no barrier-less pull
-                algo = AR_MULTIMEM if b.has_multicast else AR_TWOSHOT
+                algo = self._fused.torch_algo
             b.ensure_inbox(algo)
             self._buckets.append((b, algo))
             need = 0
@@ -636,7 +639,11 @@ class TorchEngine:
                     self._bucket_of[id(w)] = k
                     need += 1
             self._bucket_need.append(need)
-        self._comm_stream = torch.cuda.Stream(self.devices[0])
+        # ONE communication stream on purpose: two bucket kernels in flight at once could each hold the SM slots the
+        # other one's not-yet-resident blocks need on a different GPU (every block waits for its peers' matching block),
+        # a cross-GPU cycle; a single kernel at a time only ever waits for compute kernels, which always finish.
+        self._comm_streams = [torch.cuda.Stream(self.devices[0])]
+        self._comm_stream = self._comm_streams[0]
         self.bucket_info = [{"elements": hi - lo, "algo": int(a)} for (lo, hi), (_, a) in zip(cuts, self._buckets)]
 
     def _fire_bucket(self, k: int) -> None:
@@ -644,8 +651,9 @@ class TorchEngine:
         cur = torch.cuda.current_stream(self.devices[0])
         ev = torch.cuda.Event()
         ev.record(cur)
-        self._comm_stream.wait_event(ev)
-        with torch.cuda.stream(self._comm_stream):
+        cs = self._comm_streams[k % len(self._comm_streams)]
+        cs.wait_event(ev)
+        with torch.cuda.stream(cs):
             b.step(0, algo)
         self._bucket_left[k] = -1
 
@@ -818,7 +826,8 @@ class TorchEngine:
                     for k in range(len(self._buckets)):  # buckets whose variables saw no gradient this step
                         if self._bucket_left[k] >= 0:
                             self._fire_bucket(k)
-                    torch.cuda.current_stream(self.devices[0]).wait_stream(self._comm_stream)
+                    for cs in self._comm_streams:
+                        torch.cuda.current_stream(self.devices[0]).wait_stream(cs)
                     self._bucket_left = []
                 else:
                     self._fused.step(0, self._fused.torch_algo)

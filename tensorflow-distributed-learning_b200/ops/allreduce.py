@@ -37,6 +37,9 @@ MAX_BLOCKS = 148
 ONESHOT_MAX_BYTES = int(os.environ.get("TFDL_AR_ONESHOT_MAX", 4 * 1024 * 1024))  # pull one-shot vs sliced crossover
 PUSH_MAX_BYTES = int(os.environ.get("TFDL_AR_PUSH_MAX", 2 * 1024 * 1024))        # bytes x (W-1) sent per rank, one hop
 PUSH2_MAX_BYTES = int(os.environ.get("TFDL_AR_PUSH2_MAX", 8 * 1024 * 1024))      # arena bytes, two hops
+# NVLS pays off from 4 GPUs up: with two ranks the in-switch reduction saves nothing and the two-shot kernel's plain peer
+# loads / stores are faster (256 MB, 2 GPUs: fused 483 vs 318 GB/s, plain sum 635 vs 385; 4 GPUs: on par; 8: multimem ahead)
+MULTIMEM_MIN_WORLD = int(os.environ.get("TFDL_AR_MULTIMEM_MIN_WORLD", "4"))
 _ALGOS = {"oneshot": AR_ONESHOT, "twoshot": AR_TWOSHOT, "multimem": AR_MULTIMEM, "push": AR_PUSH, "push2": AR_PUSH2}
 
 
@@ -56,7 +59,7 @@ def pick_algo(nbytes: int, world: int, has_multicast: bool) -> int:
         return AR_PUSH
     if nbytes <= PUSH2_MAX_BYTES:
         return AR_PUSH2
-    return AR_MULTIMEM if has_multicast else AR_TWOSHOT
+    return AR_MULTIMEM if (has_multicast and world >= MULTIMEM_MIN_WORLD) else AR_TWOSHOT
 
 
 class SymmetricBuffer:
@@ -335,7 +338,7 @@ class FusedState:
         self.has_multicast = bool(W > 1 and grads0.multicast_ptr and (plain or (
             params is not None and params.multicast_ptr and self.grads[1].multicast_ptr)))
         self.algo = pick_algo(n * 4, W, self.has_multicast) if not plain else (
-            AR_MULTIMEM if self.has_multicast else AR_TWOSHOT)
+            AR_MULTIMEM if (self.has_multicast and W >= MULTIMEM_MIN_WORLD) else AR_TWOSHOT)
         self.offset = 0
         self.max_blocks = MAX_BLOCKS
         self.inbox: Optional[SymmetricBuffer] = None
@@ -454,7 +457,7 @@ class FusedState:
     def allreduce_sum(self, algo: Optional[int] = None) -> None:
         a = self.algo if algo is None else algo
         if a not in (AR_MULTIMEM, AR_TWOSHOT):
-            a = AR_MULTIMEM if self.has_multicast else AR_TWOSHOT
+            a = AR_MULTIMEM if (self.has_multicast and self.ops.world >= MULTIMEM_MIN_WORLD) else AR_TWOSHOT
         _lib.check(_lib.kernels().tfdl_allreduce_sum(C.byref(self._structs[0]), a, _lib.cur_stream()), "allreduce_sum")
 
     @property

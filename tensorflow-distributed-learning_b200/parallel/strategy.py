@@ -407,7 +407,7 @@ def _launcher_control_group(rank: int, world: int, dev: torch.device) -> Any:
         host = os.environ.get("MASTER_ADDR", "127.0.0.1")
         base = int(os.environ.get("MASTER_PORT", "29500")) + 17
         addrs = [f"{host}:{base + r}" for r in range(world)]
-        return native.Group(rank, addrs, timeout_s=float(os.environ.get("TFDL_HEARTBEAT_CONNECT_S", "60")),
+        return native.Group(rank, addrs, timeout_s=float(os.environ.get("TFDL_HEARTBEAT_CONNECT_S", "20")),
                             hb_timeout_s=float(os.environ.get("TFDL_HEARTBEAT_TIMEOUT_S", "10")))
     except Exception as e:  # noqa: BLE001
         import sys

@@ -70,6 +70,8 @@ def main() -> None:
                 v_ref = 0.9 * v_ref - 0.1 * gsum
                 w_ref = w_ref + v_ref
             torch.cuda.synchronize(dev)
+            # every kernel also clears the OTHER parity's gradient buffer for the next step's backward pass
+            assert float(st.grads[par ^ 1].tensor.abs().max()) == 0.0, f"other-parity gradients not cleared ({AR_NAMES[algo]})"
             if algo in (AR_ONESHOT, AR_PUSH, AR_PUSH2):  # rank-ordered fp32 sums: the host order exactly
                 torch.testing.assert_close(params, w_ref, rtol=1e-5, atol=1e-5)
             else:
