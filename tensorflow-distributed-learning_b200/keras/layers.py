@@ -6,9 +6,11 @@ OHWI and dense kernels [out, in] so that the forward GEMM operands are K-major f
 that torch's channels_last conv can use them without a copy; `get_weights()` / checkpoints convert
 back to the Keras layout.
 
-`call()` here is the portable torch implementation (CPU tests, stand-in baseline, layers that have no
-native kernel yet). On a B200 the supported stacks are executed by the native step program instead
-(keras/native_engine.py), which never calls these functions.
+`call()` dispatches per layer: on CUDA replicas (CallContext.native) Conv2D, MaxPooling2D, GlobalAveragePooling2D, Dense,
+BatchNormalization and LayerNormalization run on this library's sm_100a kernels (ops/conv.py, ops/pool.py, ops/gemm.py,
+ops/batchnorm.py, ops/layernorm.py); the torch implementation below each dispatch is the portable path (CPU tests, the
+independent reference of the GPU tests, shapes a kernel does not take). The reference CNN's exact stack is executed by the
+native step program instead (keras/native_engine.py), which never calls these functions.
 """
 from __future__ import annotations
 

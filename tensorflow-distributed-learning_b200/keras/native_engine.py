@@ -2,15 +2,19 @@
 
 `try_build(model)` recognises the layer stack of /root/reference/tf_dist_example.py:40-52
     Conv2D(C1,3,relu) - MaxPooling2D() - Conv2D(C2,3,relu) - MaxPooling2D() - Flatten - Dense(D1,relu) - Dense(NC)
-compiled with SparseCategoricalCrossentropy(from_logits=True) + SGD (any lr / momentum / nesterov),
-and returns an engine whose training step is ONE CUDA-graph launch: nine hand-written kernels
-(csrc/kernels/cnn.cu, tcgen05 for every GEMM-shaped op) plus the fused NVLink all-reduce + SGD kernel
-(csrc/kernels/allreduce.cu). Steps are driven by the C++ executor (csrc/kernels/program.cu): Python
-hands it a ring of pinned batches and does not run again until the chunk is done.
+compiled with SparseCategoricalCrossentropy(from_logits=True) + SGD (any lr / momentum / nesterov) or Adam, and returns an
+engine whose training step is seven kernels of this library - input staging, conv1+conv2 forward, the fused dense block,
+conv2 wgrad, conv2 dgrad + conv1 wgrad (csrc/kernels/cnn_tma.cu, dense_block.cu; tcgen05 for every GEMM-shaped op) and the
+two buckets' fused NVLink all-reduce + update kernels (csrc/kernels/allreduce.cu) - launched up to 16 steps per CUDA graph
+by the C++ executor (csrc/kernels/program.cu): Python hands it a ring of pinned batches (or row numbers into the dataset
+arrays, gathered by one C++ call) and does not run again until the chunk is queued.
 
-Anything else (other topologies, evaluate/predict, a ragged last batch) runs on the portable
-TorchEngine, which shares the same parameter arena. On a machine with CUDA devices the native library
-must be present: a missing .so is an error, never a silent fallback.
+`NativeCnnEngine` drives ONE replica (one GPU of a one-process-per-GPU launch, or replica r of an in-process group);
+`MirroredNativeEngine` drives all GPUs of a single-process MirroredStrategy() through one NativeCnnEngine per GPU.
+
+Anything else (other topologies, evaluate/predict, a ragged last batch) runs on the TorchEngine, which shares the same
+parameter arena and calls the same library's layer kernels (implicit-GEMM Conv2D, pooling, GEMM). On a machine with CUDA
+devices the native library must be present: a missing .so is an error, never a silent fallback.
 """
 from __future__ import annotations
 

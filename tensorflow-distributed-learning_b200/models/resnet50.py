@@ -2,10 +2,11 @@
 batch 256/GPU"). Same topology, layer names and parameter count as tf.keras.applications.ResNet50
 (25,636,712 parameters, 53,120 of them non-trainable BatchNorm statistics), NHWC.
 
-Execution: this model runs on the TorchEngine. Convolutions go through cuDNN (channels_last); BatchNorm, ReLU and
-the residual add are the native streaming kernels of ops/batchnorm.py (half of the eager step time was BatchNorm),
-the classifier Dense layer uses the tcgen05 GEMM under the mixed_bfloat16 policy, and the per-step gradient
-all-reduce + SGD/momentum update over the ~102 MB arena is ONE fused NVLink kernel (ops/allreduce.py).
+Execution: this model runs on the TorchEngine with every layer op on this library's kernels: the 3x3 / strided / 7x7
+convolutions on the tcgen05 implicit-GEMM kernel (TMA im2col loads; the 3-channel stem through a patch matrix + GEMM),
+1x1 convolutions and the classifier on the TMA + tcgen05 GEMM, max-pool and global average pool on streaming kernels,
+BatchNorm + ReLU + the residual add fused in the kernels of ops/batchnorm.py, and the ~102 MB gradient arena reduced in
+buckets by the fused NVLink all-reduce + SGD/momentum kernels while backward is still running (ops/allreduce.py).
 """
 from __future__ import annotations
 

@@ -9,13 +9,15 @@ csrc/kernels/allreduce.cu.
 Buffers per rank (all symmetric when world > 1):
     params   fp32 master weights            grads[0], grads[1]   fp32 gradient arenas (parity double buffer)
     shadow   bf16 copy of params            flags                3 barrier pads of MAX_BLOCKS*world u32
-Device-local: epoch / done counters, hyper-parameters {lr, momentum, nesterov, scale}, abort word.
+    inbox    packet inboxes of the push paths (2 parities x world regions)
+Device-local: epoch / done counters, hyper-parameters {lr, momentum, nesterov, scale, beta1, beta2, eps, t_offset},
+momentum / Adam slot arenas. Host (pinned, device-mapped): the abort word the heartbeat thread sets when a peer dies.
 
 Algorithm choice (`AUTO`, `pick_algo`): small buckets are PUSHED - every rank writes {value, epoch} packets into
 its peers' inboxes and polls its own, one NVLink one-way trip and no barrier; mid-size buckets take the same
 packets in two hops (slices to their owner, new weights back: push2); large arenas go through the NVSwitch
-(multimem: in-switch reduction, one multicast store of the fp32 weights, bf16 shadow cast locally) or, without a
-multicast mapping, two-shot peer loads/stores. The pull-style one-shot kernel (one barrier, then peer loads)
+(multimem: in-switch reduction, one multicast store of the fp32 weights, bf16 shadow cast locally) from 4 GPUs up or,
+on 2 GPUs and without a multicast mapping, two-shot peer loads/stores. The pull-style one-shot kernel (one barrier, then peer loads)
 remains for ragged element counts and for comparison. Override with
 TFDL_AR_ALGO=oneshot|twoshot|multimem|push|push2; thresholds TFDL_AR_PUSH_MAX / TFDL_AR_PUSH2_MAX (bytes).
 """

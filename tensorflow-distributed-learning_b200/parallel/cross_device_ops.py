@@ -8,8 +8,9 @@ size); MirroredStrategy defaults to NcclAllReduce. Here:
   NCCL  -> P2PFusedAllReduce: hand-written sm_100a kernels over NVLink peer memory that fuse the
            reduction with the 1/N scale and the SGD/momentum update (ops/allreduce.py) - this is
            the "NCCL slot", but no NCCL call runs on it
-  AUTO  -> P2PFused when every replica is a CUDA device with peer access, else RING; inside
-           P2PFused the one-shot / two-shot / multimem variant is picked per message size.
+  AUTO  -> P2PFused when every worker drives one CUDA device of the SAME host, else RING; inside
+           P2PFused the push / push2 / two-shot / multimem variant is picked per message size and group size.
+  (single-process MirroredStrategy over several GPUs: ops/allreduce.py:MirroredPeerAllReduce, same kernels)
 
 Every implementation reduces the *flat gradient arena* in place (values.ParamArena.grads), so
 there is no packing step, and every implementation produces bit-identical results on all replicas.

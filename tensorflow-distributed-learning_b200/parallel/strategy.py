@@ -12,11 +12,12 @@ inside scope() are mirrored and start from the chief's initial values; the datas
 GLOBAL batch size and each replica consumes global/num_replicas_in_sync; gradients are summed over
 all replicas every step before anyone applies them (README.md:67).
 
-Execution model (B200-first, differs from TF): the native GPU path runs ONE PROCESS PER GPU and
-the fused all-reduce+update kernel reads peers' gradient arenas over NVLink. A MirroredStrategy
-constructed inside a torchrun-style launch (WORLD_SIZE/RANK/LOCAL_RANK in the environment) is one
-replica of such a process group. Constructed in a plain process it drives its `devices` from one
-Python thread (this is also what the CPU tests use: devices=["cpu:0","cpu:1"]).
+Execution model (B200-first, differs from TF): the fused all-reduce + update kernels exchange gradients between the
+replicas' arenas over NVLink in both launch forms. A MirroredStrategy constructed inside a torchrun-style launch
+(WORLD_SIZE/RANK/LOCAL_RANK in the environment) is one replica of a one-process-per-GPU group (symmetric memory).
+Constructed in a plain process it drives all its `devices` from one Python thread: several GPUs form an in-process
+peer group (peer access) running one native step program each; CPU devices (devices=["cpu:0","cpu:1"], the CPU tests)
+and GPUs without peer access reduce with a local sum.
 """
 from __future__ import annotations
 
