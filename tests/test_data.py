@@ -151,3 +151,34 @@ def test_idx_reader_roundtrip(tmp_path):
     assert not info.synthetic and info.splits["train"].num_examples == 30
     x, y = next(iter(ds["train"].batch(30)))
     assert x.shape == (30, 28, 28, 1) and x.dtype == np.uint8 and y.dtype == np.int64
+
+
+def test_index_stream_matches_the_materialised_batches():
+    """The native executor gathers its batches itself from the dataset arrays; the row numbers it is handed must describe
+    exactly the batches that iterating the dataset yields (tf_dist_example.py:31-33: map -> cache -> shuffle -> batch),
+    also when a step is split over several local replicas."""
+    import tfdl
+    from tfdl.data import dataset as D
+
+    x = np.arange(200 * 4, dtype=np.float32).reshape(200, 4)
+    y = np.arange(200, dtype=np.int64)
+    ds = tfdl.data.Dataset.from_tensor_slices((x, y)).map(lambda a, b: (a * 2, b)).cache().shuffle(50, seed=7).batch(16)
+    base, it = D.index_stream(ds)
+    idx_batches = list(it)
+    xs, ys = base.arrays
+    ds2 = tfdl.data.Dataset.from_tensor_slices((x, y)).map(lambda a, b: (a * 2, b)).cache().shuffle(50, seed=7).batch(16)
+    real = list(ds2)
+    assert len(idx_batches) == len(real) == 13
+    for idx, (bx, by) in zip(idx_batches, real):
+        np.testing.assert_array_equal(xs[idx], bx)
+        np.testing.assert_array_equal(ys[idx], by)
+    # two local replicas: one step = two consecutive per-replica batches, concatenated in replica order
+    s = tfdl.distribute.MirroredStrategy(devices=["cpu:0", "cpu:1"])
+    ds3 = tfdl.data.Dataset.from_tensor_slices((x, y)).batch(16)
+    dist = s.experimental_distribute_dataset(ds3)
+    base3, steps = dist.index_stream()
+    steps = list(steps)
+    assert [len(i) for i in steps] == [16] * 12 + [8]
+    np.testing.assert_array_equal(steps[0], np.arange(16))
+    for st, per in zip(steps, dist):
+        np.testing.assert_array_equal(np.concatenate([np.asarray(b[1]) for b in per]), y[st])

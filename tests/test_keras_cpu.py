@@ -155,3 +155,24 @@ def test_callbacks_lr_schedule_and_early_stopping():
           keras.callbacks.EarlyStopping(monitor="loss", patience=0, min_delta=10.0)]
     h = m.fit(x, y, batch_size=64, epochs=5, verbose=0, callbacks=cb)
     assert lrs[:2] == [0.05, 0.025] and len(h.history["loss"]) == 2  # stopped: no 10.0 improvement
+
+
+def test_fault_injection_is_installed_from_the_environment(monkeypatch):
+    """TFDL_FAULT alone arms the fault hook: no callback has to be passed to fit()."""
+    import tfdl
+    from tfdl import keras
+
+    seen = []
+    orig = keras.callbacks.FaultInjection.on_train_batch_end
+
+    def spy(self, batch, logs=None):
+        seen.append((self.spec, batch))
+        return orig(self, batch, logs)
+
+    monkeypatch.setattr(keras.callbacks.FaultInjection, "on_train_batch_end", spy)
+    monkeypatch.setenv("TFDL_FAULT", "stall:7:1000:0.0")  # rank 7 does not exist here: armed but never fires
+    m = keras.Sequential([keras.layers.Dense(4, input_shape=(3,))])
+    m.compile(optimizer="sgd", loss="mse")
+    x, y = np.random.rand(16, 3).astype(np.float32), np.random.rand(16, 4).astype(np.float32)
+    m.fit(x, y, batch_size=8, epochs=1, verbose=0)
+    assert seen and seen[0][0] == "stall:7:1000:0.0"
