@@ -6,8 +6,13 @@
 // into a (pinned) staging buffer, optionally fusing the uint8 -> float32 /255 scale of
 // tf_dist_example.py:22-25.
 #include <algorithm>
+#include <atomic>
+#include <chrono>
 #include <cstdlib>
 #include <condition_variable>
+#include <deque>
+#include <memory>
+#include <vector>
 #include <functional>
 #include <mutex>
 #include <thread>
@@ -123,10 +128,51 @@ extern "C" int tfdl_rt_shuffle_indices(const int64_t* src, int64_t n, int64_t bu
 
 // A small persistent worker pool: the input pipeline calls into here once per chunk of steps (every ~0.8 ms of
 // device time for the reference CNN), and creating + joining threads per call costs more than the copy they do.
+//
+// Jobs are split into many small parts that any thread claims with one atomic add. The posting thread never waits
+// for a worker to wake up: in run() (and in the wait of an asynchronous job) it claims parts itself, so a job costs
+// at most its single-threaded time and workers that wake late simply find nothing left. After a job the workers
+// poll for the next one for a short while before they sleep: fit() posts its gathers back to back, and a
+// condition-variable wake-up (30-60 us) is as long as the gather of four MNIST batches.
 namespace {
+inline void cpu_relax() {
+#if defined(__x86_64__)
+  __builtin_ia32_pause();
+#else
+  std::this_thread::yield();
+#endif
+}
+inline int64_t now_us() {
+  return std::chrono::duration_cast<std::chrono::microseconds>(std::chrono::steady_clock::now().time_since_epoch()).count();
+}
+
+struct Job {
+  std::function<void(int)> fn;  // owned: a worker may look at a job after its poster has returned
+  int parts = 0;
+  std::atomic<int> next{0}, pending{0};
+  void help() {
+    for (;;) {
+      const int part = next.fetch_add(1, std::memory_order_relaxed);
+      if (part >= parts) return;
+      fn(part);
+      pending.fetch_sub(1, std::memory_order_acq_rel);
+    }
+  }
+  bool claimed() const { return next.load(std::memory_order_relaxed) >= parts; }
+  bool done() const { return pending.load(std::memory_order_acquire) == 0; }
+  void wait_done() {  // parts are short: spin, then start yielding
+    const int64_t t0 = now_us();
+    while (!done()) {
+      if (now_us() - t0 < 200) cpu_relax();
+      else std::this_thread::yield();
+    }
+  }
+};
+
 class Pool {
  public:
   explicit Pool(int n) {
+    if (const char* e = getenv("TFDL_IO_SPIN_US")) spin_us_ = std::max(0, atoi(e));
     for (int i = 0; i < n; ++i) workers_.emplace_back([this] { loop(); });
   }
   ~Pool() {
@@ -138,60 +184,63 @@ class Pool {
     for (auto& t : workers_) t.join();
   }
   int size() const { return (int)workers_.size(); }
+  // hands the job to the workers and returns at once; the poster joins in with job->help()
+  void post(const std::shared_ptr<Job>& job) {
+    job->pending.store(job->parts, std::memory_order_relaxed);
+    {
+      std::lock_guard<std::mutex> g(mu_);
+      jobs_.push_back(job);
+      posted_.fetch_add(1, std::memory_order_release);
+    }
+    cv_.notify_all();
+  }
   // runs fn(part) for part in [0, parts) on the workers + the calling thread; returns when all are done
-  void run(int parts, const std::function<void(int)>& fn) {
+  void run(int parts, std::function<void(int)> fn) {
     if (parts <= 1) {
       if (parts == 1) fn(0);
       return;
     }
-    std::unique_lock<std::mutex> g(mu_);
-    fn_ = &fn;
-    next_ = 0;
-    parts_ = parts;
-    pending_ = parts;
-    ++gen_;
-    g.unlock();
-    cv_.notify_all();
-    work();
-    g.lock();
-    done_cv_.wait(g, [this] { return pending_ == 0; });
-    fn_ = nullptr;
+    auto job = std::make_shared<Job>();
+    job->fn = std::move(fn);
+    job->parts = parts;
+    post(job);
+    job->help();
+    job->wait_done();
   }
 
  private:
-  void work() {
-    for (;;) {
-      int part;
-      const std::function<void(int)>* f;
-      {
-        std::lock_guard<std::mutex> g(mu_);
-        if (!fn_ || next_ >= parts_) return;
-        part = next_++;
-        f = fn_;
-      }
-      (*f)(part);
-      std::lock_guard<std::mutex> g(mu_);
-      if (--pending_ == 0) done_cv_.notify_all();
-    }
+  std::shared_ptr<Job> take() {
+    std::lock_guard<std::mutex> g(mu_);
+    while (!jobs_.empty() && jobs_.front()->claimed()) jobs_.pop_front();
+    return jobs_.empty() ? nullptr : jobs_.front();
   }
   void loop() {
-    uint64_t seen = 0;
     for (;;) {
-      {
-        std::unique_lock<std::mutex> g(mu_);
-        cv_.wait(g, [&] { return stop_ || gen_ != seen; });
-        if (stop_) return;
-        seen = gen_;
+      const uint64_t seen = posted_.load(std::memory_order_acquire);
+      if (auto job = take()) {
+        job->help();
+        continue;
       }
-      work();
+      bool again = false;
+      for (const int64_t t0 = now_us(); spin_us_ > 0 && now_us() - t0 < spin_us_;) {
+        if (posted_.load(std::memory_order_acquire) != seen) {
+          again = true;
+          break;
+        }
+        cpu_relax();
+      }
+      if (again) continue;
+      std::unique_lock<std::mutex> g(mu_);
+      cv_.wait(g, [&] { return stop_ || posted_.load(std::memory_order_acquire) != seen; });
+      if (stop_) return;
     }
   }
   std::vector<std::thread> workers_;
   std::mutex mu_;
-  std::condition_variable cv_, done_cv_;
-  const std::function<void(int)>* fn_ = nullptr;
-  int next_ = 0, parts_ = 0, pending_ = 0;
-  uint64_t gen_ = 0;
+  std::condition_variable cv_;
+  std::deque<std::shared_ptr<Job>> jobs_;
+  std::atomic<uint64_t> posted_{0};
+  int spin_us_ = 150;
   bool stop_ = false;
 };
 Pool& pool() {
@@ -207,7 +256,6 @@ Pool& pool() {
   }();
   return *p;
 }
-std::mutex g_pool_mu;  // one parallel region at a time (callers are the per-process input pipeline)
 }  // namespace
 
 template <class F>
@@ -218,12 +266,10 @@ static void parallel_ranges(int64_t n, int parts, F fn) {
   }
   parts = (int)std::min<int64_t>(parts, n);
   const int64_t per = (n + parts - 1) / parts;
-  std::lock_guard<std::mutex> g(g_pool_mu);
-  std::function<void(int)> job = [&](int t) {
+  pool().run(parts, [=](int t) {
     const int64_t lo = t * per, hi = std::min(n, lo + per);
     if (lo < hi) fn(lo, hi);
-  };
-  pool().run(parts, job);
+  });
 }
 
 template <class F>
@@ -302,45 +348,134 @@ extern "C" int tfdl_rt_pack_records(const void* const* xs, const void* const* ys
 // Builds k records straight from the (cached) dataset arrays: record r = [x[idx[r*B + b]] for b < B | labels as int32].
 // This is `.shuffle(...).batch(...)` of tf_dist_example.py:31-33 done as ONE gather into the executor's pinned ring -
 // no per-batch arrays, no second staging copy (shuffle / batch / rebatch kernels).
-extern "C" int tfdl_rt_gather_records(const void* x_src, int64_t num_rows, int64_t x_row_bytes, const void* y_src,
-                                      int label_bytes, const int64_t* idx, int64_t k, int64_t B, void* ring,
-                                      int64_t rec_bytes, int threads) {
+//
+// The work is cut into parts of GATHER_ROWS rows of one record, claimed in record order, so the first records are
+// complete first. The asynchronous form (begin / ready / wait / end) is tf.data's prefetch for this path: fit() starts
+// the gather of a whole chunk, launches the first steps as soon as their records are in the ring and keeps launching
+// while the pool fills the rest behind the running steps.
+namespace {
+constexpr int64_t GATHER_ROWS = 16;
+struct GatherJob {
+  const char* xs = nullptr;
+  const void* ys = nullptr;
+  int label_bytes = 4;
+  int64_t k = 0, B = 0, x_row_bytes = 0, rec_bytes = 0, ppr = 1;  // ppr: parts per record
+  char* ring = nullptr;
+  std::vector<int64_t> idx;                       // owned copy: the caller's array may go away
+  std::unique_ptr<std::atomic<int>[]> left;       // parts of record r still to be copied
+  std::atomic<int64_t> prefix{0};                 // records [0, prefix) are known to be complete
+  std::shared_ptr<Job> job;
+  void copy_part(int part) {
+    const int64_t r = part / ppr, b0 = (part % ppr) * GATHER_ROWS, b1 = std::min(B, b0 + GATHER_ROWS);
+    char* rec = ring + r * rec_bytes;
+    int32_t* yl = reinterpret_cast<int32_t*>(rec + B * x_row_bytes);
+    const int64_t* id = idx.data() + r * B;
+    for (int64_t b = b0; b < b1; ++b) {
+      const int64_t j = id[b];
+      // rows are scattered over a dataset far larger than the caches: start the DRAM fetch of a row a few rows ahead
+      // (the hardware prefetcher continues it) so the copy below is not one latency stall per row
+      if (b + 4 < B) {  // also across the end of this part: whoever copies the next part finds its first rows on the way
+        const char* nxt = xs + id[b + 4] * x_row_bytes;
+        __builtin_prefetch(nxt);
+        __builtin_prefetch(nxt + 64);
+        __builtin_prefetch(nxt + 128);
+      }
+      std::memcpy(rec + b * x_row_bytes, xs + j * x_row_bytes, (size_t)x_row_bytes);
+      yl[b] = label_bytes == 8 ? (int32_t) static_cast<const int64_t*>(ys)[j]
+              : label_bytes == 4 ? static_cast<const int32_t*>(ys)[j]
+                                 : (int32_t) static_cast<const uint8_t*>(ys)[j];
+    }
+    left[r].fetch_sub(1, std::memory_order_release);
+  }
+  int64_t ready() {
+    int64_t p = prefix.load(std::memory_order_relaxed);
+    while (p < k && left[p].load(std::memory_order_acquire) == 0) ++p;
+    prefix.store(p, std::memory_order_relaxed);
+    return p;
+  }
+};
+
+GatherJob* make_gather(const void* x_src, int64_t num_rows, int64_t x_row_bytes, const void* y_src, int label_bytes,
+                       const int64_t* idx, int64_t k, int64_t B, void* ring, int64_t rec_bytes) {
   if (!x_src || !y_src || !idx || !ring || k < 0 || B < 1 || (label_bytes != 1 && label_bytes != 4 && label_bytes != 8) ||
-      rec_bytes < B * x_row_bytes + B * 4) {
+      rec_bytes < B * x_row_bytes + B * 4 || k * ((B + GATHER_ROWS - 1) / GATHER_ROWS) > (int64_t)1 << 30) {
     set_error("gather_records: bad arguments (k=%lld B=%lld row=%lld label_bytes=%d rec=%lld)", (long long)k, (long long)B,
               (long long)x_row_bytes, label_bytes, (long long)rec_bytes);
-    return -1;
+    return nullptr;
   }
   for (int64_t i = 0; i < k * B; ++i)
     if (idx[i] < 0 || idx[i] >= num_rows) {
       set_error("gather_records: index %lld out of range [0,%lld)", (long long)idx[i], (long long)num_rows);
-      return -1;
+      return nullptr;
     }
-  const char* xs = static_cast<const char*>(x_src);
-  auto work = [=](int64_t lo, int64_t hi) {
-    for (int64_t r = lo; r < hi; ++r) {
-      char* rec = static_cast<char*>(ring) + r * rec_bytes;
-      int32_t* yl = reinterpret_cast<int32_t*>(rec + B * x_row_bytes);
-      for (int64_t b = 0; b < B; ++b) {
-        const int64_t j = idx[r * B + b];
-        // rows are scattered over a dataset far larger than the caches: start the DRAM fetch of a row a few rows ahead
-        // (the hardware prefetcher continues it) so the copy below is not one latency stall per row
-        if (b + 4 < B) {
-          const char* nxt = xs + idx[r * B + b + 4] * x_row_bytes;
-          __builtin_prefetch(nxt);
-          __builtin_prefetch(nxt + 64);
-          __builtin_prefetch(nxt + 128);
-        }
-        std::memcpy(rec + b * x_row_bytes, xs + j * x_row_bytes, (size_t)x_row_bytes);
-        yl[b] = label_bytes == 8 ? (int32_t) static_cast<const int64_t*>(y_src)[j]
-                : label_bytes == 4 ? static_cast<const int32_t*>(y_src)[j]
-                                   : (int32_t) static_cast<const uint8_t*>(y_src)[j];
-      }
-    }
-  };
-  const int64_t nt = std::min<int64_t>(std::min<int64_t>(threads, k), (k * B * x_row_bytes) >> 18);
-  parallel_ranges(k, (int)nt, work);
+  auto* g = new GatherJob;
+  g->xs = static_cast<const char*>(x_src);
+  g->ys = y_src;
+  g->label_bytes = label_bytes;
+  g->k = k;
+  g->B = B;
+  g->x_row_bytes = x_row_bytes;
+  g->rec_bytes = rec_bytes;
+  g->ring = static_cast<char*>(ring);
+  g->ppr = (B + GATHER_ROWS - 1) / GATHER_ROWS;
+  g->idx.assign(idx, idx + k * B);
+  g->left.reset(new std::atomic<int>[std::max<int64_t>(k, 1)]);
+  for (int64_t r = 0; r < k; ++r) g->left[r].store((int)g->ppr, std::memory_order_relaxed);
+  g->job = std::make_shared<Job>();
+  g->job->parts = (int)(k * g->ppr);
+  g->job->fn = [g](int part) { g->copy_part(part); };
+  return g;
+}
+}  // namespace
+
+extern "C" int tfdl_rt_gather_records(const void* x_src, int64_t num_rows, int64_t x_row_bytes, const void* y_src,
+                                      int label_bytes, const int64_t* idx, int64_t k, int64_t B, void* ring,
+                                      int64_t rec_bytes, int threads) {
+  GatherJob* g = make_gather(x_src, num_rows, x_row_bytes, y_src, label_bytes, idx, k, B, ring, rec_bytes);
+  if (!g) return -1;
+  if (threads > 1 && k * B * x_row_bytes >= (1 << 18)) pool().post(g->job);  // small jobs: not worth waking anyone
+  else g->job->pending.store(g->job->parts, std::memory_order_relaxed);
+  g->job->help();
+  g->job->wait_done();
+  delete g;
   return 0;
+}
+
+// Asynchronous form. begin() validates, hands the job to the pool and returns; the caller must keep x_src, y_src and
+// ring alive until end(). Returns NULL on bad arguments (tfdl_rt_last_error()).
+extern "C" void* tfdl_rt_gather_records_begin(const void* x_src, int64_t num_rows, int64_t x_row_bytes, const void* y_src,
+                                              int label_bytes, const int64_t* idx, int64_t k, int64_t B, void* ring,
+                                              int64_t rec_bytes) {
+  GatherJob* g = make_gather(x_src, num_rows, x_row_bytes, y_src, label_bytes, idx, k, B, ring, rec_bytes);
+  if (!g) return nullptr;
+  pool().post(g->job);
+  return g;
+}
+// How many leading records are complete right now (does not block).
+extern "C" int64_t tfdl_rt_gather_records_ready(void* h) { return static_cast<GatherJob*>(h)->ready(); }
+// Returns once records [0, n) are complete. The caller does not sleep: it copies parts itself while any are
+// unclaimed, so the wait costs at most the single-threaded time of what is left.
+extern "C" int tfdl_rt_gather_records_wait(void* h, int64_t n) {
+  auto* g = static_cast<GatherJob*>(h);
+  n = std::min(n, g->k);
+  while (g->ready() < n) {
+    const int part = g->job->next.fetch_add(1, std::memory_order_relaxed);
+    if (part < g->job->parts) {
+      g->job->fn(part);
+      g->job->pending.fetch_sub(1, std::memory_order_acq_rel);
+    } else {
+      cpu_relax();  // everything is claimed: the last parts are in flight on the workers (a few microseconds each)
+    }
+  }
+  return 0;
+}
+// Completes the job (helping like wait) and frees it.
+extern "C" void tfdl_rt_gather_records_end(void* h) {
+  auto* g = static_cast<GatherJob*>(h);
+  if (!g) return;
+  g->job->help();
+  g->job->wait_done();
+  delete g;
 }
 
 // Streaming form of the shuffle buffer: the same algorithm as tfdl_rt_shuffle_indices, producing its output on

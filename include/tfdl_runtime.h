@@ -37,6 +37,15 @@ int tfdl_rt_pack_records(const void* const* xs, const void* const* ys, int64_t k
  * (labels stored as uint8, int32 or int64: label_bytes 1, 4, 8). shuffle + batch + staging in one pass. */
 int tfdl_rt_gather_records(const void* x_src, int64_t num_rows, int64_t x_row_bytes, const void* y_src, int label_bytes,
                            const int64_t* idx, int64_t k, int64_t B, void* ring, int64_t rec_bytes, int threads);
+/* the same gather, asynchronous (the prefetch of this input path): begin() posts the job to the worker pool and returns;
+ * ready() = number of leading records complete; wait(n) returns once records [0, n) are complete (the caller copies
+ * unclaimed parts itself instead of sleeping); end() completes and frees the job. x_src, y_src and ring must stay alive
+ * until end(); idx is copied. */
+void* tfdl_rt_gather_records_begin(const void* x_src, int64_t num_rows, int64_t x_row_bytes, const void* y_src,
+                                   int label_bytes, const int64_t* idx, int64_t k, int64_t B, void* ring, int64_t rec_bytes);
+int64_t tfdl_rt_gather_records_ready(void* job);
+int tfdl_rt_gather_records_wait(void* job, int64_t n);
+void tfdl_rt_gather_records_end(void* job);
 
 /* ---- TCP control plane + RING collective (ref: README.md:21-23,65-68) -------------------- */
 /* Binds the port of addrs[rank], connects ring/control/heartbeat channels, returns once every

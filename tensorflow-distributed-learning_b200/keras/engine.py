@@ -313,7 +313,13 @@ class Model:
             return out
 
         it: Any = None
-        self.reset_metrics()
+        if lag:
+            # epoch totals come from the engine's device counters (epoch_mark), never from the Keras accumulators: only
+            # those counters have to be clean - zeroing the accumulators would be four kernel launches in front of the
+            # first step of every fit()
+            engine.flush_metrics()
+        else:
+            self.reset_metrics()
         t_loop = time.time()
         for epoch in range(initial_epoch, epochs):
             if not lag and epoch > initial_epoch:

@@ -274,6 +274,7 @@ class NativeCnnEngine:
         self.host_outs = [torch.zeros((n_rec, 2), dtype=torch.float32).pin_memory() for _ in range(2)]
         self.ring_done = [torch.cuda.Event(), torch.cuda.Event()]
         self._ring_i = 0
+        self._prefetch = os.environ.get("TFDL_FIT_PREFETCH", "1") == "1"
         self.ring, self.host_out = self.rings[0], self.host_outs[0]
         # the executor alternates parity with its own step counter, which restarts at 0: both gradient
         # buffers must be clean and the device epoch is only used for flag values
@@ -357,15 +358,18 @@ class NativeCnnEngine:
             for k, (xb, yb) in enumerate(zip(xs, ys)):
                 self.pack_record(k, xb, yb)
 
-    def run_pinned(self, records: torch.Tensor, n_steps: int, host_out: Optional[torch.Tensor] = None) -> None:
-        """Drive n_steps steps from a pinned [n_records, rec_bytes] uint8 tensor (asynchronous)."""
-        assert records.is_pinned() and records.shape[1] == self.rec_bytes
+    def run_pinned(self, records: torch.Tensor, n_steps: int, host_out: Optional[torch.Tensor] = None,
+                   first: int = 0) -> None:
+        """Drive n_steps steps from a pinned [n_records, rec_bytes] uint8 tensor (asynchronous), starting at record
+        `first`; their (loss, accuracy) pairs go to host_out[first:first + n_steps]."""
+        assert records.is_pinned() and records.shape[1] == self.rec_bytes and 0 <= first < records.shape[0]
         if self.model.optimizer.learning_rate != self._lr:
             self.hyperparams_changed()
-        out_ptr = host_out.data_ptr() if host_out is not None else None
+        out_ptr = host_out.data_ptr() + 8 * first if host_out is not None else None
         self.stream.wait_stream(torch.cuda.current_stream(self.device))
         with nvtx_range(f"tfdl/native_chunk[{n_steps}]"):
-            _lib.check(self.lib.tfdl_cnn_program_run(self._prog, records.data_ptr(), records.shape[0], n_steps, out_ptr,
+            _lib.check(self.lib.tfdl_cnn_program_run(self._prog, records.data_ptr() + first * self.rec_bytes,
+                                                     records.shape[0] - first, n_steps, out_ptr,
                                                      self.stream.cuda_stream), "cnn_program_run")
         self._metrics_dirty = True
         if self.replica == 0:
@@ -450,9 +454,13 @@ class NativeCnnEngine:
 
     def train_index_chunk(self, x: np.ndarray, y: np.ndarray, idxs: List[np.ndarray]) -> None:
         """Train on len(idxs) consecutive batches given as row numbers into (x, y): ONE multi-threaded gather builds the
-        records in the pinned ring (shuffle + batch + staging in a single pass), one executor call runs them."""
+        records in the pinned ring (shuffle + batch + staging in a single pass), the executor runs them.
+
+        When the device has nothing queued (the start of a fit) the gather runs as a background job on the runtime's
+        worker pool - the prefetch of this input path: the first two steps are launched as soon as their records are in
+        the ring, and every further launch takes whatever has been gathered by then, so the copy of the later batches
+        and the launch work of the earlier ones overlap each other and the running steps."""
         i = 0
-        ramping = False
         while i < len(idxs):
             B = int(idxs[i].size)
             if B == 0:
@@ -470,16 +478,7 @@ class NativeCnnEngine:
             tw = time.perf_counter()
             self.ring_done[r].synchronize()
             self.prof["ring_wait"] += time.perf_counter() - tw
-            k = 0
-            # the first group of a call is short (4 steps): the device starts on it while the rest is being gathered
-            # (only when the device has nothing queued - otherwise the split just costs an extra launch sequence)
-            # and the second is 8 (gathered while the first runs); everything after that is gathered behind running steps
-            if i == 0 and len(idxs) > 4 and self.stream.query():
-                cap, ramping = 4, True
-            elif i == 4 and ramping:
-                cap, ramping = 8, False
-            else:
-                cap = self.ring.shape[0]
+            k, cap = 0, self.ring.shape[0]
             while i + k < len(idxs) and k < cap and idxs[i + k].size == B:
                 k += 1
             t0 = time.perf_counter()
@@ -496,14 +495,44 @@ class NativeCnnEngine:
                     i += k
                     continue
             flat = np.ascontiguousarray(np.concatenate(group), dtype=np.int64)
-            _rt.gather_records(x, y, flat, k, B, self.ring.data_ptr(), self.rec_bytes, threads=8)
-            t1 = time.perf_counter()
-            self.run_pinned(self.ring, k, self.host_out)
-            self.prof["gather"] += t1 - t0
-            self.prof["enqueue"] += time.perf_counter() - t1
+            if k > 2 and self._prefetch and self.stream.query():
+                self._run_prefetched(x, y, flat, k, B, t0)
+            else:  # the device is busy anyway: gather everything behind the running steps, one launch sequence
+                _rt.gather_records(x, y, flat, k, B, self.ring.data_ptr(), self.rec_bytes, threads=8)
+                t1 = time.perf_counter()
+                self.run_pinned(self.ring, k, self.host_out)
+                self.prof["gather"] += t1 - t0
+                self.prof["enqueue"] += time.perf_counter() - t1
             self.ring_done[r].record(self.stream)
             self._last_k = k
             i += k
+
+    def _run_prefetched(self, x: np.ndarray, y: np.ndarray, flat: np.ndarray, k: int, B: int, t0: float) -> None:
+        """k steps whose records are gathered by a background job while the first ones are already being launched."""
+        job = _rt.GatherJob(x, y, flat, k, B, self.ring.data_ptr(), self.rec_bytes)
+        try:
+            done = 0
+            while done < k:
+                # the first launch is two steps (the device starts ~50 us after the gather began); later ones wait for
+                # at least four more records so that a slow gather does not turn into a launch per step
+                job.wait(min(k, done + (2 if done == 0 else 4)))
+                n = job.ready() - done
+                if done + n < k:
+                    if done == 0:
+                        n = 4 if n >= 4 else 2
+                    elif k - (done + n) <= 2:  # nearly everything: take the rest in the same launch sequence
+                        job.wait(k)
+                        n = k - done
+                    else:
+                        n = 1 << (n.bit_length() - 1)  # whole power-of-two graphs; the tail stays in one piece
+                t1 = time.perf_counter()
+                self.run_pinned(self.ring, n, self.host_out, first=done)
+                self.prof["gather"] += t1 - t0
+                t0 = time.perf_counter()
+                self.prof["enqueue"] += t0 - t1
+                done += n
+        finally:
+            job.end()
 
     # ---- epoch totals without stopping the device ----------------------------------------------------------------
     def epoch_mark(self, reduce: bool = True) -> Tuple[int, Any]:

@@ -37,6 +37,14 @@ def lib() -> C.CDLL:
         L.tfdl_rt_gather_rows_u8_to_f32.argtypes = [vp, C.c_int64, C.c_int64, vp, C.c_int64, C.c_float, vp, C.c_int]
         L.tfdl_rt_gather_records.argtypes = [vp, C.c_int64, C.c_int64, vp, C.c_int, vp, C.c_int64, C.c_int64, vp,
                                              C.c_int64, C.c_int]
+        L.tfdl_rt_gather_records_begin.restype = vp
+        L.tfdl_rt_gather_records_begin.argtypes = [vp, C.c_int64, C.c_int64, vp, C.c_int, vp, C.c_int64, C.c_int64, vp,
+                                                   C.c_int64]
+        L.tfdl_rt_gather_records_ready.restype = C.c_int64
+        L.tfdl_rt_gather_records_ready.argtypes = [vp]
+        L.tfdl_rt_gather_records_wait.argtypes = [vp, C.c_int64]
+        L.tfdl_rt_gather_records_end.restype = None
+        L.tfdl_rt_gather_records_end.argtypes = [vp]
         L.tfdl_rt_group_create.restype = vp
         L.tfdl_rt_group_create.argtypes = [C.c_int, C.c_int, C.POINTER(C.c_char_p), C.c_int, C.c_int, C.c_int]
         L.tfdl_rt_group_destroy.argtypes = [vp]
@@ -157,6 +165,40 @@ def gather_records(x: np.ndarray, y: np.ndarray, idx: np.ndarray, k: int, B: int
     row = int(np.prod(x.shape[1:], dtype=np.int64)) * x.itemsize
     _lib.check_rt(lib().tfdl_rt_gather_records(_np_ptr(x), x.shape[0], row, _np_ptr(y), y.dtype.itemsize, _np_ptr(idx),
                                               k, B, C.c_void_p(ring_ptr), rec_bytes, threads), "gather_records")
+
+
+class GatherJob:
+    """gather_records running on the runtime's worker pool while the caller does something else (the prefetch of the
+    index path of fit()). ``ready()``: leading records complete; ``wait(n)``: returns once records [0, n) are in the
+    ring (the calling thread copies unclaimed parts itself rather than sleep); ``end()``: complete and free. The job
+    holds references to x and y; the ring must outlive it."""
+
+    def __init__(self, x: np.ndarray, y: np.ndarray, idx: np.ndarray, k: int, B: int, ring_ptr: int, rec_bytes: int) -> None:
+        row = int(np.prod(x.shape[1:], dtype=np.int64)) * x.itemsize
+        self._keep = (x, y)
+        self.k = k
+        self._h = lib().tfdl_rt_gather_records_begin(_np_ptr(x), x.shape[0], row, _np_ptr(y), y.dtype.itemsize, _np_ptr(idx),
+                                                     k, B, C.c_void_p(ring_ptr), rec_bytes)
+        if not self._h:
+            raise RuntimeError("gather_records: " + lib().tfdl_rt_last_error().decode())
+
+    def ready(self) -> int:
+        return int(lib().tfdl_rt_gather_records_ready(self._h))
+
+    def wait(self, n: int) -> None:
+        lib().tfdl_rt_gather_records_wait(self._h, n)
+
+    def end(self) -> None:
+        if self._h:
+            lib().tfdl_rt_gather_records_end(self._h)
+            self._h = None
+            self._keep = ()
+
+    def __del__(self) -> None:  # pragma: no cover
+        try:
+            self.end()
+        except Exception:
+            pass
 
 
 def gather_rows_u8_to_f32(src: np.ndarray, idx: np.ndarray, scale: float, out_ptr: int, threads: int = 4) -> None:

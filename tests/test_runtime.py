@@ -170,3 +170,67 @@ def _w_desync(rank, addrs):
 def test_ring_collectives_out_of_step_fail_with_a_message():
     res = run_workers(_w_desync, 2, timeout=60)
     assert all("out of step" in v[1] for v in res.values()), res
+
+
+def _records_oracle(x, y, flat, k, B):
+    rows = int(np.prod(x.shape[1:])) * x.itemsize
+    out = np.zeros((k, B * rows + B * 4), dtype=np.uint8)
+    for r in range(k):
+        sel = flat[r * B:(r + 1) * B]
+        out[r, :B * rows] = np.ascontiguousarray(x[sel]).view(np.uint8).reshape(-1)
+        out[r, B * rows:] = y[sel].astype(np.int32).view(np.uint8)
+    return out
+
+
+@pytest.mark.parametrize("k,B,ydt", [(1, 64, np.int64), (7, 48, np.int32), (20, 64, np.int64), (3, 20, np.uint8)])
+def test_gather_records_sync_and_async_match_numpy(k, B, ydt):
+    """shuffle + batch + staging in one gather (tf_dist_example.py:31-33), in its blocking form and as the background
+    job that fit() starts its steps behind: same bytes, records complete in order, nothing written past the k-th record."""
+    from tfdl.runtime import native as rt
+
+    rng = np.random.default_rng(k * 100 + B)
+    x = rng.random((5000, 28, 28, 1), dtype=np.float32)
+    y = rng.integers(0, 10, size=5000).astype(ydt)
+    flat = rng.integers(0, 5000, size=k * B).astype(np.int64)
+    want = _records_oracle(x, y, flat, k, B)
+    rec = want.shape[1]
+    ring = np.full((k + 1, rec), 0xAB, dtype=np.uint8)
+    rt.gather_records(x, y, flat, k, B, ring.ctypes.data, rec, threads=8)
+    np.testing.assert_array_equal(ring[:k], want)
+    assert (ring[k] == 0xAB).all()
+    for first in (1, min(2, k), k):
+        ring[:] = 0xCD
+        job = rt.GatherJob(x, y, flat.copy(), k, B, ring.ctypes.data, rec)
+        job.wait(first)
+        got = job.ready()
+        assert first <= got <= k
+        np.testing.assert_array_equal(ring[:got], want[:got])  # whatever is reported ready is complete
+        job.wait(k)
+        assert job.ready() == k
+        job.end()
+        np.testing.assert_array_equal(ring[:k], want)
+        assert (ring[k] == 0xCD).all()
+
+
+def test_gather_jobs_queue_behind_each_other_and_reject_bad_rows():
+    from tfdl.runtime import native as rt
+
+    rng = np.random.default_rng(5)
+    x = rng.random((3000, 784), dtype=np.float32)
+    y = rng.integers(0, 10, size=3000).astype(np.int64)
+    k, B = 12, 64
+    flats = [rng.integers(0, 3000, size=k * B).astype(np.int64) for _ in range(4)]
+    rec = B * 784 * 4 + B * 4
+    rings = [np.zeros((k, rec), dtype=np.uint8) for _ in flats]
+    jobs = [rt.GatherJob(x, y, f, k, B, r.ctypes.data, rec) for f, r in zip(flats, rings)]  # four jobs in flight
+    rt.gather_rows(x, flats[0][:300])  # a blocking call on the same pool while they run
+    for j in reversed(jobs):
+        j.end()
+    for f, r in zip(flats, rings):
+        np.testing.assert_array_equal(r, _records_oracle(x, y, f, k, B))
+    bad = flats[0].copy()
+    bad[17] = 3000
+    with pytest.raises(RuntimeError, match="out of range"):
+        rt.GatherJob(x, y, bad, k, B, rings[0].ctypes.data, rec)
+    with pytest.raises(RuntimeError, match="out of range"):
+        rt.gather_records(x, y, bad, k, B, rings[0].ctypes.data, rec)
