@@ -244,13 +244,15 @@ class Pool {
   bool stop_ = false;
 };
 Pool& pool() {
-  // Workers per process: the host's cores shared between the worker processes of this node (one per GPU under
-  // torchrun / TF_CONFIG launches), minus the caller; TFDL_IO_THREADS overrides. Leaked on purpose: no
+  // Workers per process: from the host's cores shared between the worker processes of this node (one per GPU under
+  // torchrun / TF_CONFIG launches); TFDL_IO_THREADS overrides. Leaked on purpose: no
   // static-destruction order games at exit.
   static Pool* p = [] {
     int n = (int)std::thread::hardware_concurrency();
     if (const char* lw = getenv("LOCAL_WORLD_SIZE")) n /= std::max(1, atoi(lw));
-    n = std::max(1, std::min(7, n - 1));
+    // half of this process's share: the workers poll between jobs, and the training thread, the heartbeat thread and
+    // the driver's own threads must never have to wait for a core behind them
+    n = std::max(1, std::min(7, n / 2));
     if (const char* e = getenv("TFDL_IO_THREADS")) n = std::max(1, std::min(32, atoi(e)));
     return new Pool(n);
   }();

@@ -122,18 +122,20 @@ def shuffle_stream(src, buffer_size: int, seed: int, chunk: int = 8192):
         h = lib().tfdl_rt_shuffler_create(_np_ptr(src), src.size, int(buffer_size), C.c_uint64(seed & ((1 << 64) - 1)))
     if not h:
         raise RuntimeError(_lib.runtime_error() if hasattr(_lib, "runtime_error") else "shuffler_create failed")
+    # bound now: a generator that is still open at interpreter exit is finalised after this module's globals are gone
+    nxt, destroy, h = lib().tfdl_rt_shuffler_next, lib().tfdl_rt_shuffler_destroy, C.c_void_p(h)
     try:
         first = True
         while True:
             # a small first chunk: the consumer's first batches should not wait for 8192 draws
             out = np.empty(min(chunk, 2048) if first else chunk, dtype=np.int64)
             first = False
-            n = int(lib().tfdl_rt_shuffler_next(h, _np_ptr(out), out.size))
+            n = int(nxt(h, C.c_void_p(out.ctypes.data), out.size))
             if n == 0:
                 return
             yield out[:n]
     finally:
-        lib().tfdl_rt_shuffler_destroy(h)
+        destroy(h)
 
 
 def gather_rows(src: np.ndarray, idx: np.ndarray, out: Optional[np.ndarray] = None, threads: int = 4) -> np.ndarray:
