@@ -325,6 +325,10 @@ class MirroredStrategy(Strategy):
                 dev = torch.device("cuda", local_rank % torch.cuda.device_count())
             else:
                 dev = torch.device("cpu")
+            if dev.type == "cuda":
+                from ..utils.affinity import bind_to_device
+
+                bind_to_device(dev, int(os.environ.get("LOCAL_WORLD_SIZE", world)))  # before any helper thread exists
             _ensure_process_group(rank, world, dev)
             ops = cross_device_ops or _make_group_ops(dev, CollectiveCommunication.AUTO, _launcher_control_group(rank, world, dev))
             super().__init__([dev], TFConfigClusterResolver.single_worker(), ops, world, rank)
@@ -386,6 +390,9 @@ class MultiWorkerMirroredStrategy(Strategy):
                    "every worker must drive exactly one CUDA device")
             raise ValueError(f"CollectiveCommunication.NCCL is not possible here: {why}")
         if use_p2p:
+            from ..utils.affinity import bind_to_device
+
+            bind_to_device(devs[0], res.num_workers)  # all workers are on this host: share its sockets by GPU locality
             _ensure_process_group(res.id_in_cluster, res.num_workers, devs[0], master=res.leader_address)
             ops: CrossDeviceOps = _make_group_ops(devs[0], communication, group)
         else:
