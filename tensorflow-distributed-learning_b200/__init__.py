@@ -8,6 +8,7 @@ Public surface mirrors what /root/reference/tf_dist_example.py touches in Tensor
     tfdl.cluster      TF_CONFIG resolver
     tfdl.datasets     tfds-style loader (mnist: IDX files or synthetic)
     tfdl.ops          ctypes bindings of the sm_100a kernels
+    tfdl.config       set_random_seed, enable_op_determinism
 """
 __version__ = "0.1.0"
 
@@ -25,6 +26,7 @@ _LAZY = {
     "checkpoint": ".checkpoint",
     "runtime": ".runtime",
     "datasets": ".data.datasets",
+    "config": ".config",
 }
 
 

@@ -22,6 +22,7 @@ from typing import Any, Dict, Iterator, List, Optional, Sequence, Tuple, Union
 import numpy as np
 import torch
 
+from .. import config as _config
 from ..data import Dataset
 from ..parallel import strategy as _strat
 from ..parallel.strategy import DistributedDataset, Strategy, get_strategy
@@ -218,6 +219,8 @@ class Model:
         elif not self.optimizer.slot_names():
             self.optimizer._slots = {}
         pref = self._engine_pref
+        if _config.is_op_determinism_enabled():
+            pref = "torch"  # the native step programs accumulate with atomics (config.py)
         on_cuda = all(d.type == "cuda" for d in self.strategy.local_devices)
         engine = None
         if pref in ("auto", "native") and on_cuda:
@@ -589,10 +592,10 @@ class TorchEngine:
                 opt0._slots = {"momentum": [st.mom]}
             from ..ops.structs import AR_MULTIMEM, AR_ONESHOT, AR_TWOSHOT
 
-            from ..ops.allreduce import MULTIMEM_MIN_WORLD
+            from ..ops.allreduce import multimem_ok
 
             st.torch_algo = AR_ONESHOT if ops.world == 1 else (
-                AR_MULTIMEM if (st.has_multicast and ops.world >= MULTIMEM_MIN_WORLD) else AR_TWOSHOT)
+                AR_MULTIMEM if multimem_ok(ops.world, st.has_multicast) else AR_TWOSHOT)
             self._fused = st
             st.refresh_shadow()
             self._make_buckets(ops)
@@ -678,7 +681,7 @@ class TorchEngine:
         # asks for bf16 anyway - that is the independent reference the tests compare against.
         native = None
         if self.devices[r].type == "cuda" and self.model._engine_pref != "torch" and \
-                os.environ.get("TFDL_NATIVE_OPS", "1") == "1":
+                os.environ.get("TFDL_NATIVE_OPS", "1") == "1" and not _config.is_op_determinism_enabled():
             native = True
         ctx = CallContext(r, training, lambda v: leaves[id(v)], self.model.compute_dtype, native)
         if native and self._fused is not None and r == 0 and os.environ.get("TFDL_TORCH_INPLACE", "1") == "1":

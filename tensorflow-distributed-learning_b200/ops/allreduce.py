@@ -45,6 +45,15 @@ MULTIMEM_MIN_WORLD = int(os.environ.get("TFDL_AR_MULTIMEM_MIN_WORLD", "4"))
 _ALGOS = {"oneshot": AR_ONESHOT, "twoshot": AR_TWOSHOT, "multimem": AR_MULTIMEM, "push": AR_PUSH, "push2": AR_PUSH2}
 
 
+def multimem_ok(world: int, has_multicast: bool) -> bool:
+    """NVLS multicast reduction: needs the multicast mapping, pays off from MULTIMEM_MIN_WORLD GPUs, and is left out under
+    op determinism (the order in which the switch adds the ranks' values is not specified; every other kernel here adds
+    them in rank order)."""
+    from .. import config as _config
+
+    return bool(has_multicast and world >= MULTIMEM_MIN_WORLD and not _config.is_op_determinism_enabled())
+
+
 def pick_algo(nbytes: int, world: int, has_multicast: bool) -> int:
     """The reference's AUTO: choose by message size, world size and hardware (README.md:21)."""
     forced = os.environ.get("TFDL_AR_ALGO", "").lower()
@@ -61,7 +70,7 @@ def pick_algo(nbytes: int, world: int, has_multicast: bool) -> int:
         return AR_PUSH
     if nbytes <= PUSH2_MAX_BYTES:
         return AR_PUSH2
-    return AR_MULTIMEM if (has_multicast and world >= MULTIMEM_MIN_WORLD) else AR_TWOSHOT
+    return AR_MULTIMEM if multimem_ok(world, has_multicast) else AR_TWOSHOT
 
 
 class SymmetricBuffer:
@@ -340,7 +349,7 @@ class FusedState:
         self.has_multicast = bool(W > 1 and grads0.multicast_ptr and (plain or (
             params is not None and params.multicast_ptr and self.grads[1].multicast_ptr)))
         self.algo = pick_algo(n * 4, W, self.has_multicast) if not plain else (
-            AR_MULTIMEM if (self.has_multicast and W >= MULTIMEM_MIN_WORLD) else AR_TWOSHOT)
+            AR_MULTIMEM if multimem_ok(W, self.has_multicast) else AR_TWOSHOT)
         self.offset = 0
         self.max_blocks = MAX_BLOCKS
         self.inbox: Optional[SymmetricBuffer] = None
@@ -459,7 +468,7 @@ class FusedState:
     def allreduce_sum(self, algo: Optional[int] = None) -> None:
         a = self.algo if algo is None else algo
         if a not in (AR_MULTIMEM, AR_TWOSHOT):
-            a = AR_MULTIMEM if (self.has_multicast and self.ops.world >= MULTIMEM_MIN_WORLD) else AR_TWOSHOT
+            a = AR_MULTIMEM if multimem_ok(self.ops.world, self.has_multicast) else AR_TWOSHOT
         _lib.check(_lib.kernels().tfdl_allreduce_sum(C.byref(self._structs[0]), a, _lib.cur_stream()), "allreduce_sum")
 
     @property
