@@ -29,6 +29,7 @@ from ..parallel.strategy import DistributedDataset, Strategy, get_strategy
 from ..parallel.values import MirroredVariable, ParamArena, PerReplica
 from ..utils.trace import nvtx_range
 from . import callbacks as _cb
+from . import layers as _klayers
 from . import losses as _losses
 from . import metrics as _metrics
 from . import optimizers as _optimizers
@@ -543,8 +544,20 @@ class Sequential(Model):
         return (None,) + tuple(self._stack[-1].output_shape) if self.built else None
 
     def _forward(self, x: torch.Tensor, ctx: CallContext) -> torch.Tensor:
-        for l in self._stack:
+        stack, i = self._stack, 0
+        while i < len(stack):
+            l = stack[i]
+            if (not ctx.native and not x.is_cuda and type(l) is _klayers.Conv2D and l.activation == "relu"
+                    and i + 1 < len(stack) and type(stack[i + 1]) is _klayers.MaxPooling2D):
+                # CPU workers (library kernels, no fusion): ReLU and max-pool commute exactly - relu(max(w)) ==
+                # max(relu(w)) for every window, gradients included - so the ReLU runs after the pool, on a quarter of
+                # the elements (tf_dist_example.py:41-44: both convolutions of the reference model)
+                x = stack[i + 1].call(l.call(x, ctx, defer_relu=True), ctx)
+                x = torch.relu(x)
+                i += 2
+                continue
             x = l.call(x, ctx)
+            i += 1
         return x
 
 

@@ -258,9 +258,11 @@ class Conv2D(Layer):
             return ((h - kh) // sh + 1, (w - kw) // sw + 1, self.filters)
         return (-(-h // sh), -(-w // sw), self.filters)
 
-    def call(self, x: torch.Tensor, ctx: CallContext, add_bias: bool = True) -> torch.Tensor:
+    def call(self, x: torch.Tensor, ctx: CallContext, add_bias: bool = True, defer_relu: bool = False) -> torch.Tensor:
         """``add_bias=False``: leave the bias to a following BatchNormalization(in_bias=...), which absorbs it for
-        free (no extra pass over the activations, no bias-gradient reduction)."""
+        free (no extra pass over the activations, no bias-gradient reduction). ``defer_relu=True`` (library-kernel path
+        only): return the pre-activation; the caller applies the ReLU after the max-pool that follows (see
+        Sequential._forward)."""
         assert self.kernel is not None
         b = ctx.param(self.bias) if (self.bias is not None and add_bias) else None
         fused_act = self.activation if self.activation in (None, "linear", "relu") else None
@@ -310,7 +312,7 @@ class Conv2D(Layer):
         elif xin.dtype != w.dtype:  # bf16 activations from a native layer upstream
             xin = xin.to(w.dtype)
         y = F.conv2d(xin, w, b, stride=self.strides, padding=pad).permute(0, 2, 3, 1)
-        act = _ACTS[self.activation]
+        act = None if (defer_relu and self.activation == "relu") else _ACTS[self.activation]
         return act(y) if act else y
 
 

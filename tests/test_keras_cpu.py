@@ -176,3 +176,49 @@ def test_fault_injection_is_installed_from_the_environment(monkeypatch):
     x, y = np.random.rand(16, 3).astype(np.float32), np.random.rand(16, 4).astype(np.float32)
     m.fit(x, y, batch_size=8, epochs=1, verbose=0)
     assert seen and seen[0][0] == "stall:7:1000:0.0"
+
+
+def test_relu_after_pool_on_cpu_is_exactly_relu_before_pool():
+    """CPU workers run Conv2D(relu) -> MaxPooling2D as conv -> pool -> relu (keras/engine.py:Sequential._forward). The two
+    orders are the same function with the same gradients - also for windows that are all negative or hold ties."""
+    import torch
+
+    import tfdl
+    from tfdl.keras import layers as L
+    from tfdl.keras.layers import CallContext
+
+    tfdl.config.set_random_seed(3)
+    try:
+        model = tfdl.models.build_and_compile_cnn_model()
+        model.build((28, 28, 1))
+        model._finalize()
+    finally:
+        tfdl.config.set_random_seed(None)
+    rng = np.random.default_rng(0)
+    x = rng.standard_normal((8, 28, 28, 1)).astype(np.float32)
+    x[0] = -1.0       # whole images whose first-layer windows are all negative / all equal
+    x[1] = 0.25
+    x[2, :14] = 0.0
+    pools = [l for l in model._stack if type(l) is L.MaxPooling2D]
+    assert len(pools) == 2
+
+    class Plain(L.MaxPooling2D):  # a subclass is not fused: the layer-by-layer order
+        pass
+
+    def run(fused: bool):
+        for p in pools:
+            p.__class__ = L.MaxPooling2D if fused else Plain
+        leaves = {id(v): v.value(0).detach().clone().requires_grad_(True) for v in model.trainable_variables}
+        ctx = CallContext(0, True, lambda v: leaves[id(v)], torch.float32)
+        out = model._forward(torch.from_numpy(x), ctx)
+        out.square().sum().backward()
+        return out.detach(), [leaves[id(v)].grad for v in model.trainable_variables]
+
+    try:
+        (o1, g1), (o2, g2) = run(True), run(False)
+    finally:
+        for p in pools:
+            p.__class__ = L.MaxPooling2D
+    assert torch.equal(o1, o2)
+    for a, b in zip(g1, g2):
+        torch.testing.assert_close(a, b, rtol=1e-6, atol=1e-7)  # same terms; the library may add them in another order
