@@ -2,6 +2,7 @@
 from . import callbacks, layers, losses, metrics, optimizers
 from .engine import History, Model, Sequential, TorchEngine, mixed_precision
 from .layers import clear_session
+from . import models  # noqa: E402  (needs engine)
 
 
 class backend:  # tf.keras.backend look-alike
@@ -9,4 +10,4 @@ class backend:  # tf.keras.backend look-alike
 
 
 __all__ = ["callbacks", "layers", "losses", "metrics", "optimizers", "History", "Model", "Sequential", "TorchEngine",
-           "mixed_precision", "backend", "clear_session"]
+           "mixed_precision", "backend", "clear_session", "models"]

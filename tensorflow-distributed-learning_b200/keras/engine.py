@@ -80,6 +80,10 @@ def _as_dataset(x: Any, y: Any, batch_size: Optional[int], shuffle: bool = False
 class Model:
     """Base model: a stack (or custom graph) of layers with Keras-style training methods."""
 
+    def __init_subclass__(cls, **kw: Any) -> None:
+        super().__init_subclass__(**kw)
+        _klayers.capture_init_config(cls)  # constructor arguments -> get_config(), like the layers
+
     def __init__(self, name: Optional[str] = None) -> None:
         self.name = name or "model"
         self.strategy: Strategy = get_strategy()  # captured at construction: build under strategy.scope()
@@ -471,13 +475,15 @@ class Model:
             first = next(iter(ds))
             xb = first[0] if isinstance(first, (tuple, list)) else first
             self.build(tuple(np.asarray(xb).shape[1:]))
-        engine = self._make_engine()
+        # a model that was never compiled can still predict (as in Keras): eager forward on replica 0
+        engine = self._make_engine() if self.optimizer is not None else None
         outs = []
         for i, b in enumerate(ds):
             if steps is not None and i >= steps:
                 break
             xb = b[0] if isinstance(b, (tuple, list)) else b
-            outs.append(engine.predict_step(np.asarray(xb)))
+            outs.append(engine.predict_step(np.asarray(xb)) if engine is not None
+                        else self(np.asarray(xb)).float().cpu().numpy())
         return np.concatenate(outs) if outs else np.zeros((0,))
 
     def __call__(self, x: Any, training: bool = False) -> torch.Tensor:
@@ -505,6 +511,29 @@ class Model:
         load_model_weights(self, filepath)
         self._weights_changed()
 
+    # ---- whole-model save (architecture + compile arguments + variables) ----------------------------
+    def get_config(self) -> Dict[str, Any]:
+        """Constructor arguments of a subclassed model (Sequential overrides this with its layer list)."""
+        return _klayers.jsonable_config(getattr(self, "_init_config", {}))
+
+    @classmethod
+    def from_config(cls, config: Dict[str, Any], custom_objects: Optional[Dict[str, Any]] = None) -> "Model":
+        return cls(**config)
+
+    def to_json(self) -> str:
+        from . import models as _models
+
+        return _models.model_to_json(self)
+
+    def save(self, filepath: str, overwrite: bool = True, include_optimizer: bool = True) -> None:
+        """tf.keras.Model.save: a directory with the architecture and compile arguments (`model.json`) and the
+        variables as a TensorFlow-format checkpoint (`variables/variables.*`, optimizer slots included). Under a
+        multi-worker strategy every worker calls this and only the chief writes (README.md:51 of the reference).
+        `tfdl.keras.models.load_model` restores it."""
+        from . import models as _models
+
+        _models.save_model(self, filepath, overwrite=overwrite, include_optimizer=include_optimizer)
+
 
 class Sequential(Model):
     """tf.keras.Sequential (tf_dist_example.py:40-48)."""
@@ -527,6 +556,24 @@ class Sequential(Model):
 
     def _layers(self) -> List[Layer]:
         return self._stack
+
+    def get_config(self) -> Dict[str, Any]:
+        return {"name": self.name,
+                "layers": [{"class_name": type(l).__name__, "module": type(l).__module__, "config": l.get_config()}
+                           for l in self._stack],
+                "build_input_shape": list(self._input_shape) if self._input_shape else None}
+
+    @classmethod
+    def from_config(cls, config: Dict[str, Any], custom_objects: Optional[Dict[str, Any]] = None) -> "Sequential":
+        from . import models as _models
+
+        model = cls(name=config.get("name"))
+        for spec in config["layers"]:
+            layer_cls = _models.resolve_class(spec["class_name"], spec.get("module"), custom_objects, Layer)
+            model.add(layer_cls.from_config(dict(spec["config"])))
+        if not model.built and config.get("build_input_shape"):
+            model.build(tuple(config["build_input_shape"]))
+        return model
 
     def build(self, input_shape: Sequence[int]) -> None:
         shape = tuple(int(s) for s in input_shape)

@@ -14,6 +14,8 @@ native step program instead (keras/native_engine.py), which never calls these fu
 """
 from __future__ import annotations
 
+import functools
+import inspect
 import math
 import os
 from typing import Any, Callable, Dict, List, Optional, Sequence, Tuple, Union
@@ -135,8 +137,58 @@ class CallContext:
         return self.grad_sink(var) if (self.grad_sink is not None and self.training) else None
 
 
+def capture_init_config(cls: type) -> None:
+    """Wrap cls.__init__ so that the arguments of the OUTERMOST constructor call are remembered on the instance
+    (`_init_config`): that is what get_config() returns and from_config() feeds back (tf.keras layer / model configs)."""
+    init = cls.__dict__.get("__init__")
+    if init is None or getattr(init, "_captures_config", False):
+        return
+    sig = inspect.signature(init)
+
+    @functools.wraps(init)
+    def wrapped(self, *a: Any, **k: Any) -> None:
+        if not hasattr(self, "_init_config"):
+            cfg: Dict[str, Any] = {}
+            try:
+                bound = sig.bind(self, *a, **k)
+                for name, val in list(bound.arguments.items())[1:]:
+                    kind = sig.parameters[name].kind
+                    if kind is inspect.Parameter.VAR_KEYWORD:
+                        cfg.update(val)
+                    elif kind is not inspect.Parameter.VAR_POSITIONAL:
+                        cfg[name] = val
+            except TypeError:
+                pass  # the real call below raises the proper error
+            self._init_config = cfg
+        init(self, *a, **k)
+
+    wrapped._captures_config = True  # type: ignore[attr-defined]
+    cls.__init__ = wrapped  # type: ignore[assignment]
+
+
+def jsonable_config(cfg: Dict[str, Any]) -> Dict[str, Any]:
+    """Constructor arguments as JSON values: tuples become lists, callables (custom initialisers) are left out - a
+    restored model takes its values from the saved variables, not from an initialiser."""
+    out: Dict[str, Any] = {}
+    for k, v in cfg.items():
+        if callable(v):
+            continue
+        if isinstance(v, (tuple, list)):
+            v = [int(e) if isinstance(e, (int, np.integer)) else e for e in v]
+        elif isinstance(v, np.integer):
+            v = int(v)
+        elif isinstance(v, np.floating):
+            v = float(v)
+        out[k] = v
+    return out
+
+
 class Layer:
     """Base layer: lazily built from the input shape (excluding the batch dimension)."""
+
+    def __init_subclass__(cls, **kw: Any) -> None:
+        super().__init_subclass__(**kw)
+        capture_init_config(cls)
 
     def __init__(self, name: Optional[str] = None, input_shape: Optional[Sequence[int]] = None,
                  trainable: bool = True, **kw: Any) -> None:
@@ -204,7 +256,14 @@ class Layer:
         return x
 
     def get_config(self) -> Dict[str, Any]:
-        return {"name": self.name}
+        """The constructor arguments (tf.keras.layers.Layer.get_config); `from_config` rebuilds an unbuilt layer."""
+        cfg = jsonable_config(getattr(self, "_init_config", {}))
+        cfg["name"] = self.name
+        return cfg
+
+    @classmethod
+    def from_config(cls, config: Dict[str, Any]) -> "Layer":
+        return cls(**config)
 
     def __repr__(self) -> str:
         return f"<{type(self).__name__} {self.name}>"

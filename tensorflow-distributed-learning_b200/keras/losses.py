@@ -18,6 +18,13 @@ class Loss:
     def __call__(self, y_true: torch.Tensor, y_pred: torch.Tensor) -> torch.Tensor:
         return self.per_example(y_true, y_pred).mean()
 
+    def get_config(self) -> dict:
+        return {k: v for k, v in vars(self).items() if not k.startswith("_")}
+
+    @classmethod
+    def from_config(cls, config: dict) -> "Loss":
+        return cls(**config)
+
 
 class SparseCategoricalCrossentropy(Loss):
     name = "sparse_categorical_crossentropy"

@@ -90,6 +90,10 @@ class Adam(Optimizer):
         super().__init__(learning_rate)
         self.beta_1, self.beta_2, self.epsilon, self.weight_decay = beta_1, beta_2, epsilon, weight_decay
 
+    def get_config(self):
+        return {**super().get_config(), "beta_1": self.beta_1, "beta_2": self.beta_2, "epsilon": self.epsilon,
+                "weight_decay": self.weight_decay}
+
     def slot_names(self) -> List[str]:
         return ["m", "v"]
 
@@ -104,6 +108,13 @@ class Adam(Optimizer):
         if self.weight_decay:
             upd = upd + self.weight_decay * (params if mask is None else params * mask)
         params.add_(upd, alpha=-lr_t)
+
+
+def from_config(config: Dict[str, float]) -> Optimizer:
+    """Rebuild an optimizer from get_config() (a schedule given as a callable is saved as its current value)."""
+    cfg = dict(config)
+    cls = {"sgd": SGD, "adam": Adam}[str(cfg.pop("name")).lower()]
+    return cls(**cfg)
 
 
 def get(x) -> Optimizer:
