@@ -180,14 +180,54 @@ class EarlyStopping(Callback):
                 self.model.stop_training = True
 
 
+class ReduceLROnPlateau(Callback):
+    """tf.keras.callbacks.ReduceLROnPlateau: multiply the learning rate by `factor` when `monitor` has not improved for
+    `patience` epochs. Every worker sees the same (all-reduced) logs, so every worker makes the same decision."""
+
+    def __init__(self, monitor: str = "val_loss", factor: float = 0.1, patience: int = 10, min_delta: float = 1e-4,
+                 cooldown: int = 0, min_lr: float = 0.0, mode: str = "min", verbose: int = 0) -> None:
+        super().__init__()
+        if not 0.0 < factor < 1.0:
+            raise ValueError("ReduceLROnPlateau needs 0 < factor < 1")
+        self.monitor, self.factor, self.patience, self.min_delta = monitor, factor, patience, min_delta
+        self.cooldown, self.min_lr, self.mode, self.verbose = cooldown, min_lr, mode, verbose
+        self.best: Optional[float] = None
+        self.wait = 0
+        self.cooldown_left = 0
+
+    def on_epoch_end(self, epoch, logs=None):
+        logs = logs if logs is not None else {}
+        opt = self.model.optimizer
+        logs["lr"] = opt.learning_rate
+        v = logs.get(self.monitor)
+        if v is None:
+            return
+        if self.cooldown_left > 0:
+            self.cooldown_left -= 1
+            self.wait = 0
+        better = self.best is None or (v < self.best - self.min_delta if self.mode == "min" else v > self.best + self.min_delta)
+        if better:
+            self.best, self.wait = v, 0
+            return
+        if self.cooldown_left > 0:
+            return
+        self.wait += 1
+        if self.wait >= self.patience and opt.learning_rate > self.min_lr:
+            new_lr = max(opt.learning_rate * self.factor, self.min_lr)
+            opt.learning_rate = new_lr
+            self.cooldown_left, self.wait = self.cooldown, 0
+            if self.verbose:
+                print(f"Epoch {epoch + 1}: ReduceLROnPlateau reducing learning rate to {new_lr:g}.")
+
+
 class ModelCheckpoint(Callback):
-    """Saves weights at epoch end. Every worker takes part (the save is a collective point), only the
-    chief writes to `filepath`; other workers write nothing (README.md:51)."""
+    """Saves weights (or, with save_weights_only=False, the whole model) at epoch end. Every worker takes part (the save
+    is a collective point), only the chief writes to `filepath`; other workers write nothing (README.md:51)."""
 
     def __init__(self, filepath: str, save_weights_only: bool = True, save_freq: Union[str, int] = "epoch",
                  monitor: str = "loss", save_best_only: bool = False, mode: str = "min", verbose: int = 0) -> None:
         super().__init__()
-        self.filepath, self.save_freq = filepath, save_freq
+        self.filepath, self.save_freq, self.save_weights_only = filepath, save_freq, save_weights_only
         self.monitor, self.save_best_only, self.mode, self.verbose = monitor, save_best_only, mode, verbose
         self.best: Optional[float] = None
         self.saved: List[str] = []
@@ -209,7 +249,10 @@ class ModelCheckpoint(Callback):
                 return
             self.best = v
         path = self._path(epoch, logs)
-        self.model.save_weights(path)
+        if self.save_weights_only:
+            self.model.save_weights(path)
+        else:
+            self.model.save(path)  # architecture + compile arguments + variables (keras/models.py)
         if self.model.strategy.is_chief:
             self.saved.append(path)
             if self.verbose:

@@ -267,7 +267,8 @@ class Model:
     def fit(self, x: Any = None, y: Any = None, batch_size: Optional[int] = None, epochs: int = 1,
             verbose: Union[int, str] = 1, callbacks: Optional[Sequence[_cb.Callback]] = None,
             validation_data: Any = None, shuffle: bool = True, initial_epoch: int = 0,
-            steps_per_epoch: Optional[int] = None, validation_steps: Optional[int] = None, **_: Any) -> History:
+            steps_per_epoch: Optional[int] = None, validation_steps: Optional[int] = None,
+            validation_split: float = 0.0, **unused: Any) -> History:
         """tf.keras.Model.fit (tf_dist_example.py:59: fit(x=dataset, epochs=10, steps_per_epoch=20)).
 
         With `steps_per_epoch` the dataset iterator is carried across epochs (the reference has no
@@ -276,6 +277,22 @@ class Model:
         if self.optimizer is None or self.loss is None:
             raise RuntimeError("compile(optimizer=..., loss=...) must be called before fit()")
         t_fit = time.time()
+        for k, v in unused.items():
+            # arguments that change the result must not be dropped silently; the ones that only tune Keras' own input
+            # machinery (workers, use_multiprocessing, max_queue_size, validation_freq, ...) have no meaning here
+            if k in ("class_weight", "sample_weight") and v is not None:
+                raise NotImplementedError(f"fit({k}=...) is not supported")
+        if validation_split:
+            # Keras: the LAST fraction of the arrays, taken before any shuffling, is held out for validation
+            if isinstance(x, (Dataset, DistributedDataset)) or y is None:
+                raise ValueError("validation_split needs array inputs x and y (a dataset cannot be split this way)")
+            if not 0.0 < validation_split < 1.0:
+                raise ValueError("validation_split must be in (0, 1)")
+            xs, ys = np.asarray(x), np.asarray(y)
+            cut = int(len(xs) * (1.0 - validation_split))
+            if validation_data is None:
+                validation_data = (xs[cut:], ys[cut:])
+            x, y = xs[:cut], ys[:cut]
         ds = _as_dataset(x, y, batch_size, shuffle=shuffle and not isinstance(x, Dataset))
         dist = ds if isinstance(x, DistributedDataset) else self.strategy.experimental_distribute_dataset(ds)
         if not self.built:
@@ -287,7 +304,8 @@ class Model:
         callbacks = list(callbacks or [])
         if os.environ.get("TFDL_FAULT") and not any(isinstance(c, _cb.FaultInjection) for c in callbacks):
             callbacks.append(_cb.FaultInjection())  # fault injection by environment alone
-        cbs = _cb.CallbackList([history] + callbacks, model=self, verbose=verbose, epochs=epochs,
+        # History after the user's callbacks, as in Keras: what they add to the logs (ReduceLROnPlateau's "lr") is recorded
+        cbs = _cb.CallbackList(callbacks + [history], model=self, verbose=verbose, epochs=epochs,
                                steps=steps_per_epoch)
         self.stop_training = False
         logs: Dict[str, float] = {}
@@ -400,8 +418,13 @@ class Model:
             else:
                 logs = self._read_logs()
                 if validation_data is not None:
-                    val = self.evaluate(validation_data, steps=validation_steps, verbose=0, return_dict=True,
-                                        _prefix="val_")
+                    if isinstance(validation_data, (tuple, list)) and len(validation_data) == 2 and \
+                            not isinstance(validation_data[0], (Dataset, DistributedDataset)):
+                        vx, vy = validation_data  # the (x_val, y_val) arrays form
+                    else:
+                        vx, vy = validation_data, None
+                    val = self.evaluate(vx, vy, batch_size=batch_size, steps=validation_steps, verbose=0,
+                                        return_dict=True, _prefix="val_")
                     logs.update(val)
                 logs["_epoch_time"] = time.time() - t0
                 logs["_steps"] = step
@@ -429,6 +452,22 @@ class Model:
         self._steps_done += 1
         logs = self._read_logs()
         return logs if return_dict else [logs[n] for n in self.metrics_names]
+
+    def test_on_batch(self, x: Any, y: Any = None, return_dict: bool = False) -> Any:
+        """Loss and metrics of one GLOBAL batch given as arrays, without a training step."""
+        engine = self._prepare_for_arrays(x)
+        self.reset_metrics()
+        engine.test_step(self._split_arrays(x, y))
+        logs = self._read_logs()
+        return logs if return_dict else [logs[n] for n in self.metrics_names]
+
+    def predict_on_batch(self, x: Any) -> np.ndarray:
+        return self.predict(x, batch_size=max(1, len(np.asarray(x))))
+
+    @property
+    def metrics(self) -> List[_metrics.Metric]:
+        """The loss tracker followed by the compiled metrics (tf.keras.Model.metrics)."""
+        return [self.loss_tracker] + list(self.compiled_metrics)
 
     def _prepare_for_arrays(self, x: Any) -> Any:
         if not self.built:

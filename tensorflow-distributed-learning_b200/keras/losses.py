@@ -71,11 +71,38 @@ class MeanSquaredError(Loss):
         return d.reshape(d.shape[0], -1).mean(-1)
 
 
+class MeanAbsoluteError(Loss):
+    name = "mean_absolute_error"
+
+    def per_example(self, y_true: torch.Tensor, y_pred: torch.Tensor) -> torch.Tensor:
+        d = (y_pred.float() - y_true.float().reshape(y_pred.shape)).abs()
+        return d.reshape(d.shape[0], -1).mean(-1)
+
+
+class BinaryCrossentropy(Loss):
+    name = "binary_crossentropy"
+
+    def __init__(self, from_logits: bool = False) -> None:
+        self.from_logits = from_logits
+
+    def per_example(self, y_true: torch.Tensor, y_pred: torch.Tensor) -> torch.Tensor:
+        yp = y_pred.float()
+        yt = y_true.float().reshape(yp.shape)
+        if self.from_logits:
+            per = F.binary_cross_entropy_with_logits(yp, yt, reduction="none")
+        else:
+            per = F.binary_cross_entropy(yp.clamp(1e-7, 1 - 1e-7), yt, reduction="none")
+        return per.reshape(per.shape[0], -1).mean(-1)
+
+
 _BY_NAME = {
     "sparse_categorical_crossentropy": lambda: SparseCategoricalCrossentropy(),
     "categorical_crossentropy": lambda: CategoricalCrossentropy(),
     "mse": lambda: MeanSquaredError(),
     "mean_squared_error": lambda: MeanSquaredError(),
+    "mae": lambda: MeanAbsoluteError(),
+    "mean_absolute_error": lambda: MeanAbsoluteError(),
+    "binary_crossentropy": lambda: BinaryCrossentropy(),
 }
 
 

@@ -70,15 +70,32 @@ class CategoricalAccuracy(Metric):
         return (y_pred.argmax(-1) == y_true.argmax(-1)).float()
 
 
+class BinaryAccuracy(Metric):
+    name = "binary_accuracy"
+
+    def __init__(self, name: str | None = None, threshold: float = 0.5) -> None:
+        super().__init__(name)
+        self.threshold = threshold
+
+    def batch_values(self, y_true: torch.Tensor, y_pred: torch.Tensor) -> torch.Tensor:
+        hit = ((y_pred.float() > self.threshold) == (y_true.float().reshape(y_pred.shape) > 0.5)).float()
+        return hit.reshape(hit.shape[0], -1).mean(-1)
+
+
 def get(x, loss=None) -> Metric:
     if isinstance(x, Metric):
         return x
     if x in ("accuracy", "acc"):
-        from .losses import CategoricalCrossentropy
+        from .losses import BinaryCrossentropy, CategoricalCrossentropy
 
-        m: Metric = CategoricalAccuracy() if isinstance(loss, CategoricalCrossentropy) else SparseCategoricalAccuracy()
+        # Keras picks the accuracy that matches the loss
+        m: Metric = (CategoricalAccuracy() if isinstance(loss, CategoricalCrossentropy)
+                     else BinaryAccuracy(threshold=0.0 if getattr(loss, "from_logits", False) else 0.5)
+                     if isinstance(loss, BinaryCrossentropy) else SparseCategoricalAccuracy())
         m.name = "accuracy"
         return m
+    if x == "binary_accuracy":
+        return BinaryAccuracy()
     if x == "sparse_categorical_accuracy":
         return SparseCategoricalAccuracy()
     if x == "categorical_accuracy":

@@ -110,10 +110,43 @@ class Adam(Optimizer):
         params.add_(upd, alpha=-lr_t)
 
 
+class RMSprop(Optimizer):
+    """tf.keras.optimizers.RMSprop: v = rho*v + (1-rho)*g^2; w -= lr * g / (sqrt(v) + eps), optionally through a momentum
+    buffer. Runs as tensor ops on the flat arenas behind the plain-sum all-reduce (no fused kernel)."""
+
+    name = "RMSprop"
+
+    def __init__(self, learning_rate: Union[float, Schedule] = 0.001, rho: float = 0.9, momentum: float = 0.0,
+                 epsilon: float = 1e-7) -> None:
+        super().__init__(learning_rate)
+        self.rho, self.momentum, self.epsilon = float(rho), float(momentum), float(epsilon)
+
+    def slot_names(self) -> List[str]:
+        return ["rms", "momentum"] if self.momentum else ["rms"]
+
+    def apply_flat(self, params, grads, replica, mask):
+        g = grads if mask is None else grads * mask
+        v = self._slots["rms"][replica]
+        v.mul_(self.rho).addcmul_(g, g, value=1 - self.rho)
+        upd = g / (v.sqrt() + self.epsilon)
+        if self.momentum:
+            mom = self._slots["momentum"][replica]
+            mom.mul_(self.momentum).add_(upd, alpha=self.learning_rate)
+            params.sub_(mom)
+        else:
+            params.add_(upd, alpha=-self.learning_rate)
+
+    def get_config(self):
+        return {**super().get_config(), "rho": self.rho, "momentum": self.momentum, "epsilon": self.epsilon}
+
+
+_BY_NAME = {"sgd": SGD, "adam": Adam, "rmsprop": RMSprop}
+
+
 def from_config(config: Dict[str, float]) -> Optimizer:
     """Rebuild an optimizer from get_config() (a schedule given as a callable is saved as its current value)."""
     cfg = dict(config)
-    cls = {"sgd": SGD, "adam": Adam}[str(cfg.pop("name")).lower()]
+    cls = _BY_NAME[str(cfg.pop("name")).lower()]
     return cls(**cfg)
 
 
@@ -121,5 +154,7 @@ def get(x) -> Optimizer:
     if isinstance(x, Optimizer):
         return x
     if isinstance(x, str):
-        return {"sgd": SGD, "adam": Adam}[x.lower()]()
+        if x.lower() not in _BY_NAME:
+            raise ValueError(f"unknown optimizer {x!r}; known: {sorted(_BY_NAME)}")
+        return _BY_NAME[x.lower()]()
     raise ValueError(f"unknown optimizer {x!r}")

@@ -222,3 +222,29 @@ def test_relu_after_pool_on_cpu_is_exactly_relu_before_pool():
     assert torch.equal(o1, o2)
     for a, b in zip(g1, g2):
         torch.testing.assert_close(a, b, rtol=1e-6, atol=1e-7)  # same terms; the library may add them in another order
+
+
+def test_validation_data_arrays_and_validation_split():
+    """fit(validation_data=(x_val, y_val)) - the arrays form the reference's README shows (README.md:121-129 builds
+    train and val arrays) - and fit(validation_split=...): val_ metrics every epoch, the held-out tail never trained on."""
+    import tfdl
+
+    rng = np.random.default_rng(0)
+    x, y = rng.random((96, 28, 28, 1), dtype=np.float32), rng.integers(0, 10, size=96)
+    m = tfdl.models.build_and_compile_cnn_model(learning_rate=0.01)
+    h = m.fit(x[:64], y[:64], batch_size=32, epochs=2, verbose=0, validation_data=(x[64:], y[64:]))
+    assert set(h.history) == {"loss", "sparse_categorical_accuracy", "val_loss", "val_sparse_categorical_accuracy"}
+    assert len(h.history["val_loss"]) == 2
+    want = m.evaluate(x[64:], y[64:], batch_size=32, return_dict=True)["loss"]
+    assert abs(h.history["val_loss"][-1] - want) < 1e-5  # validation ran on exactly those arrays, after the last epoch
+    ds_val = tfdl.data.Dataset.from_tensor_slices((x[64:], y[64:])).batch(16)
+    h2 = m.fit(x[:64], y[:64], batch_size=32, epochs=1, verbose=0, validation_data=ds_val)
+    assert "val_loss" in h2.history
+
+    m2 = tfdl.models.build_and_compile_cnn_model(learning_rate=0.01)
+    h3 = m2.fit(x, y, batch_size=24, epochs=1, verbose=0, validation_split=0.25, shuffle=False)
+    assert m2._steps_done == 3  # 72 training rows / 24, the last 24 rows held out
+    want = m2.evaluate(x[72:], y[72:], batch_size=24, return_dict=True)["loss"]
+    assert abs(h3.history["val_loss"][-1] - want) < 1e-5
+    with pytest.raises(ValueError, match="validation_split"):
+        m2.fit(ds_val, epochs=1, verbose=0, validation_split=0.5)
