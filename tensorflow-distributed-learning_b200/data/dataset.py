@@ -346,6 +346,26 @@ class Dataset:
     def concatenate(self, other: "Dataset") -> "Dataset":
         return _GeneratorDataset(lambda: itertools.chain(iter(self), iter(other)))
 
+    def filter(self, predicate: Callable[..., Any]) -> "Dataset":
+        """Elements for which `predicate(*element)` is true (a generic, element-at-a-time stage)."""
+        def keep(e: Any) -> bool:
+            return bool(np.asarray(predicate(*e) if isinstance(e, tuple) else predicate(e)))
+
+        return _GeneratorDataset(lambda: (e for e in self if keep(e)))
+
+    @staticmethod
+    def zip(*datasets: Any) -> "Dataset":
+        """tf.data.Dataset.zip((a, b)) / zip(a, b): tuples of corresponding elements, as long as the shortest input."""
+        if len(datasets) == 1 and isinstance(datasets[0], (tuple, list)):
+            datasets = tuple(datasets[0])
+        return _GeneratorDataset(lambda: zip(*[iter(d) for d in datasets]))
+
+    def reduce(self, initial_state: Any, reduce_func: Callable[[Any, Any], Any]) -> Any:
+        state = initial_state
+        for e in self:
+            state = reduce_func(state, e)
+        return state
+
     # ---- introspection --------------------------------------------------------------------
     def options(self) -> Options:
         node, chain = self, []
@@ -526,6 +546,8 @@ class _CacheDataset(_IndexableDataset):
         c = self._parent.cardinality()
         return c if c >= 0 else len(self._materialise())
 
+
+AUTOTUNE = -1  # tf.data.AUTOTUNE: accepted wherever TensorFlow takes it (map / prefetch); this pipeline sizes itself
 
 _global_seed = [None]
 

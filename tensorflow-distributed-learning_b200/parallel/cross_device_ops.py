@@ -82,6 +82,47 @@ class LocalAllReduce(CrossDeviceOps):
             g.copy_(acc, non_blocking=True)
 
 
+class NcclAllReduce:
+    """tf.distribute.NcclAllReduce - MirroredStrategy's default `cross_device_ops` (README.md:17 of the reference). A
+    request, not an implementation: the strategy answers it with this framework's NVLink peer-memory kernels
+    (ops/allreduce.py) when its devices are CUDA GPUs with peer access, else with the local sum. `num_packs` is accepted
+    for compatibility; the gradients already live in one flat arena."""
+
+    def __init__(self, num_packs: int = 1) -> None:
+        self.num_packs = num_packs
+
+
+class ReductionToOneDevice(LocalAllReduce):
+    """tf.distribute.ReductionToOneDevice: sum on replica 0's device, copy the result back to the others."""
+
+    name = "reduction_to_one_device"
+
+    def __init__(self, reduce_to_device=None, accumulation_fn=None) -> None:  # arguments accepted for compatibility
+        super().__init__()
+
+
+class HierarchicalCopyAllReduce(LocalAllReduce):
+    """tf.distribute.HierarchicalCopyAllReduce. On NVSwitch machines there is no hierarchy to exploit: the same local
+    sum-and-copy as ReductionToOneDevice."""
+
+    name = "hierarchical_copy"
+
+    def __init__(self, num_packs: int = 1) -> None:
+        super().__init__()
+
+
+class CommunicationOptions:
+    """tf.distribute.experimental.CommunicationOptions: `implementation` chooses RING / NCCL / AUTO for
+    MultiWorkerMirroredStrategy(communication_options=...); bytes_per_pack and timeout_seconds are accepted
+    (buckets are sized by this framework; the collective timeout is the strategy's `timeout_s`)."""
+
+    def __init__(self, bytes_per_pack: int = 0, timeout_seconds: Optional[float] = None,
+                 implementation: "CollectiveCommunication" = CollectiveCommunication.AUTO) -> None:
+        if isinstance(implementation, str):
+            implementation = CollectiveCommunication[implementation.upper()]
+        self.bytes_per_pack, self.timeout_seconds, self.implementation = bytes_per_pack, timeout_seconds, implementation
+
+
 class TcpRingAllReduce(CrossDeviceOps):
     """RING: local sum, then the C++ TCP ring across workers, then fan the result back out."""
 

@@ -318,6 +318,10 @@ class MirroredStrategy(Strategy):
 
     def __init__(self, devices: Optional[Sequence[Union[str, torch.device]]] = None,
                  cross_device_ops: Optional[CrossDeviceOps] = None) -> None:
+        from .cross_device_ops import NcclAllReduce
+
+        if isinstance(cross_device_ops, NcclAllReduce):
+            cross_device_ops = None  # TensorFlow's default, and the default here: the NVLink kernels where possible
         env = _torchrun_env() if devices is None else None
         if env is not None:
             rank, world, local_rank = env
@@ -359,7 +363,11 @@ class MultiWorkerMirroredStrategy(Strategy):
     def __init__(self, communication: CollectiveCommunication = CollectiveCommunication.AUTO,
                  cluster_resolver: Optional[TFConfigClusterResolver] = None, *,
                  tf_config: Union[None, str, dict] = None, devices: Optional[Sequence[Union[str, torch.device]]] = None,
-                 timeout_s: float = 120.0, heartbeat_timeout_s: float = 10.0) -> None:
+                 timeout_s: float = 120.0, heartbeat_timeout_s: float = 10.0, communication_options: Any = None) -> None:
+        if communication_options is not None:  # tf.distribute.MultiWorkerMirroredStrategy(communication_options=...)
+            communication = communication_options.implementation
+            if communication_options.timeout_seconds:
+                timeout_s = float(communication_options.timeout_seconds)
         if isinstance(communication, str):
             communication = CollectiveCommunication[communication.upper()]
         self.communication = communication

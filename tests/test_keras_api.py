@@ -99,3 +99,33 @@ def test_utils():
     b = keras.layers.glorot_uniform((3, 3))
     tfdl.config.set_random_seed(None)
     np.testing.assert_array_equal(a, b)
+
+
+def test_data_and_distribute_call_forms():
+    """tf.data / tf.distribute spellings around the ones the reference uses: AUTOTUNE, filter / zip / reduce,
+    MirroredStrategy(cross_device_ops=NcclAllReduce()) (the default the reference's README names, README.md:17),
+    MultiWorkerMirroredStrategy(communication_options=...)."""
+    D, T = tfdl.data, tfdl.distribute
+    x = np.arange(40, dtype=np.float32).reshape(20, 2)
+    y = np.arange(20) % 3
+    ds = D.Dataset.from_tensor_slices((x, y))
+    assert D.AUTOTUNE == D.experimental.AUTOTUNE == -1
+    out = list(ds.map(lambda a, b: (a * 2, b), num_parallel_calls=D.AUTOTUNE).batch(8).prefetch(D.AUTOTUNE))
+    assert [o[0].shape for o in out] == [(8, 2), (8, 2), (4, 2)] and out[0][0][1, 0] == 4.0
+    kept = list(ds.filter(lambda a, b: b == 1))
+    assert [int(b) for _, b in kept] == [1] * 7 and float(kept[0][0][0]) == 2.0
+    pairs = list(D.Dataset.zip((ds, D.Dataset.range(5))))
+    assert len(pairs) == 5 and int(pairs[4][1]) == 4 and float(pairs[4][0][0][0]) == 8.0
+    assert len(list(D.Dataset.zip(D.Dataset.range(3), D.Dataset.range(7)))) == 3
+    assert int(D.Dataset.range(5).reduce(np.int64(0), lambda s, e: s + e)) == 10
+
+    s = T.MirroredStrategy(devices=["cpu", "cpu"], cross_device_ops=T.NcclAllReduce())
+    assert s.num_replicas_in_sync == 2 and s.cross_device_ops.name == "local"  # CPU replicas: no NVLink to use
+    s2 = T.MirroredStrategy(devices=["cpu", "cpu"], cross_device_ops=T.HierarchicalCopyAllReduce())
+    assert s2.cross_device_ops.name == "hierarchical_copy"
+    g = [torch.ones(4), 2 * torch.ones(4)]
+    T.ReductionToOneDevice().allreduce_grads(g)
+    assert g[0].tolist() == g[1].tolist() == [3.0] * 4
+    opts = T.experimental.CommunicationOptions(implementation=T.experimental.CommunicationImplementation.RING)
+    single = T.MultiWorkerMirroredStrategy(communication_options=opts, devices=["cpu"], tf_config={})
+    assert single.communication is T.CollectiveCommunication.RING and single.num_replicas_in_sync == 1
