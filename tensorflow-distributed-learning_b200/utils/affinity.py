@@ -7,7 +7,8 @@ each of them, and the end-to-end rate of a synchronous job is that of its slowes
 process (all of its threads, and therefore the input pipeline's worker pool created later) to the CPUs NVML reports as
 local to the device.
 
-`TFDL_CPU_AFFINITY=0` turns it off, `=1` forces it on for a single process as well. Nothing here is required for
+By default this happens only for multi-process launches on hosts with more than one NUMA node.
+`TFDL_CPU_AFFINITY=0` turns it off, `=1` forces it on (single process, single-node hosts). Nothing here is required for
 correctness: every failure (no NVML, no topology information in a container, an empty intersection with the cgroup's
 CPU set) leaves the affinity untouched.
 """
@@ -44,6 +45,14 @@ def device_cpus(device: torch.device) -> Optional[Set[int]]:
         return None
 
 
+def numa_nodes() -> int:
+    """Number of memory nodes the kernel exposes (1 when that cannot be read)."""
+    try:
+        return max(1, sum(1 for d in os.listdir("/sys/devices/system/node") if d.startswith("node") and d[4:].isdigit()))
+    except OSError:
+        return 1
+
+
 def bind_to_device(device: torch.device, local_world: int = 1) -> Optional[Set[int]]:
     """Pin every thread of this process to the CPUs local to `device`. Returns the CPU set that was applied, or None
     when nothing was changed. Only narrows: the result is the intersection with what the process may already use, and a
@@ -52,8 +61,8 @@ def bind_to_device(device: torch.device, local_world: int = 1) -> Optional[Set[i
     mode = os.environ.get("TFDL_CPU_AFFINITY", "auto")
     if mode == "0" or device.type != "cuda" or not hasattr(os, "sched_setaffinity"):
         return None
-    if mode != "1" and local_world <= 1:
-        return None  # a single process: the scheduler's choice costs nothing measurable
+    if mode != "1" and (local_world <= 1 or numa_nodes() <= 1):
+        return None  # a single process, or a host with one memory node (most VMs): nothing to gain from pinning
     local = device_cpus(device)
     if not local:
         return None

@@ -42,13 +42,18 @@ def test_bind_narrows_every_thread(monkeypatch, restore_affinity):
     assert seen["aff"] == want  # a thread that existed before the call moved too
 
 
-@pytest.mark.parametrize("case", ["off", "single_process_auto", "no_nvml", "too_small", "already_local", "cpu_device"])
+@pytest.mark.parametrize("case", ["off", "single_process_auto", "one_numa_node_auto", "no_nvml", "too_small",
+                                  "already_local", "cpu_device"])
 def test_bind_leaves_affinity_alone(monkeypatch, restore_affinity, case):
     allowed = set(restore_affinity)
     local = set(sorted(allowed)[:1])
     world = 8
     dev = torch.device("cuda", 0)
     monkeypatch.setenv("TFDL_CPU_AFFINITY", "auto")
+    monkeypatch.setattr(affinity, "numa_nodes", lambda: 2)
+    if case == "one_numa_node_auto":
+        monkeypatch.setattr(affinity, "numa_nodes", lambda: 1)
+        world, local = 2, set(sorted(allowed)[: max(1, len(allowed) // 2)])
     if case == "off":
         monkeypatch.setenv("TFDL_CPU_AFFINITY", "0")
     elif case == "single_process_auto":
@@ -66,3 +71,19 @@ def test_bind_leaves_affinity_alone(monkeypatch, restore_affinity, case):
 
 def test_device_cpus_without_a_gpu_is_none():
     assert affinity.device_cpus(torch.device("cuda", 0)) is None or torch.cuda.is_available()
+
+
+def test_auto_binds_multi_process_launch_on_a_two_node_host(monkeypatch, restore_affinity):
+    allowed = sorted(restore_affinity)
+    if len(allowed) < 8:
+        pytest.skip("needs at least 8 usable CPUs")
+    local = set(allowed[: len(allowed) // 2])
+    monkeypatch.setattr(affinity, "device_cpus", lambda dev: local)
+    monkeypatch.setattr(affinity, "numa_nodes", lambda: 2)
+    monkeypatch.setenv("TFDL_CPU_AFFINITY", "auto")
+    assert affinity.bind_to_device(torch.device("cuda", 0), local_world=2) == local
+    assert os.sched_getaffinity(0) == local
+
+
+def test_numa_nodes_reads_the_host():
+    assert affinity.numa_nodes() >= 1
