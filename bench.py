@@ -417,6 +417,8 @@ def main() -> None:
     if args.model != "cnn" and args.steps == 2000:
         args.steps, args.warmup = 20, 5
     if args.impl == "reference":
+        if int(os.environ.get("RANK", "0")) != 0:
+            return  # launched like the other arm (torchrun for N > 1): one line, from rank 0
         print(json.dumps({"impl": "reference",
                           "unavailable": "the reference is a TensorFlow 2.x script: /root/reference has no setup.py/"
                                          "pyproject (pip install fails) and no tensorflow/keras/tfds wheel exists in "
