@@ -182,3 +182,79 @@ def test_index_stream_matches_the_materialised_batches():
     np.testing.assert_array_equal(steps[0], np.arange(16))
     for st, per in zip(steps, dist):
         np.testing.assert_array_equal(np.concatenate([np.asarray(b[1]) for b in per]), y[st])
+
+
+def test_index_stream_equals_iteration_for_random_pipelines():
+    """Property test (hypothesis): for pipelines assembled at random from the indexable stages - shuffle (seeded), repeat,
+    take, skip, shard, map, cache - the row numbers of `index_stream` gather exactly the batches that iterating the same
+    pipeline yields, including the ragged last batch and drop_remainder, and also after auto-sharding for a worker."""
+    from hypothesis import HealthCheck, given, settings
+    from hypothesis import strategies as st
+
+    import tfdl
+    from tfdl.data import dataset as D
+
+    stage = st.one_of(
+        st.tuples(st.just("shuffle"), st.integers(1, 64), st.integers(0, 1000)),
+        st.tuples(st.just("repeat"), st.integers(1, 3)),
+        st.tuples(st.just("take"), st.integers(0, 90)),
+        st.tuples(st.just("skip"), st.integers(0, 40)),
+        st.tuples(st.just("shard"), st.integers(1, 4), st.integers(0, 3)),
+        st.tuples(st.just("map")),
+        st.tuples(st.just("cache")),
+    )
+
+    def build(n, stages, bs, drop):
+        x = (np.arange(n * 3, dtype=np.float32).reshape(n, 3) + 0.5)
+        y = np.arange(n, dtype=np.int64)
+        ds = tfdl.data.Dataset.from_tensor_slices((x, y))
+        for s in stages:
+            if s[0] == "shuffle":
+                ds = ds.shuffle(s[1], seed=s[2], reshuffle_each_iteration=False)
+            elif s[0] == "repeat":
+                ds = ds.repeat(s[1])
+            elif s[0] == "take":
+                ds = ds.take(s[1])
+            elif s[0] == "skip":
+                ds = ds.skip(s[1])
+            elif s[0] == "shard":
+                ds = ds.shard(s[1], s[2] % s[1])
+            elif s[0] == "map":
+                ds = ds.map(lambda a, b: (a * 2 + 1, b))
+            elif s[0] == "cache":
+                ds = ds.cache()
+        return ds.batch(bs, drop_remainder=drop)
+
+    @settings(max_examples=60, deadline=None, suppress_health_check=[HealthCheck.too_slow])
+    @given(n=st.integers(1, 80), stages=st.lists(stage, max_size=5), bs=st.integers(1, 17), drop=st.booleans(),
+           workers=st.integers(1, 3))
+    def check(n, stages, bs, drop, workers):
+        ds = build(n, stages, bs, drop)
+        real = list(build(n, stages, bs, drop))
+        st_ = D.index_stream(ds)
+        if st_ is None:
+            return  # not an indexable pipeline: fit() iterates it instead
+        base, it = st_
+        got = list(it)
+        arrays = base.arrays if hasattr(base, "arrays") else None
+        assert len(got) == len(real)
+        for idx, (bx, by) in zip(got, real):
+            e = base.gather(idx)
+            np.testing.assert_array_equal(e[0], bx)
+            np.testing.assert_array_equal(e[1], by)
+            if arrays is not None:
+                np.testing.assert_array_equal(arrays[1][idx], by)
+        if workers > 1:  # the DATA policy on top: worker w's stream is what worker w's sharded dataset yields
+            for w in range(workers):
+                sharded = D.auto_shard(build(n, stages, bs, drop), workers, w, tfdl.data.AutoShardPolicy.DATA)
+                want = list(D.auto_shard(build(n, stages, bs, drop), workers, w, tfdl.data.AutoShardPolicy.DATA))
+                sw = D.index_stream(sharded)
+                if sw is None:
+                    continue
+                bw, iw = sw
+                gotw = list(iw)
+                assert len(gotw) == len(want)
+                for idx, (bx, by) in zip(gotw, want):
+                    np.testing.assert_array_equal(bw.gather(idx)[1], by)
+
+    check()
