@@ -67,9 +67,26 @@ def unbatched_training_set(synthetic: int):
     return splits["train"].map(to_unit_range).cache().shuffle(SHUFFLE_BUFFER)
 
 
+def run_evaluator(a: argparse.Namespace) -> None:
+    """The `evaluator` task of the cluster (README.md:57 of the reference): outside the training group, it evaluates every
+    checkpoint the chief writes to --checkpoint-dir on the test split."""
+    if not a.checkpoint_dir:
+        raise SystemExit("an evaluator task needs --checkpoint-dir (where the chief saves)")
+    kw = {"synthetic_size": (a.synthetic, max(64, a.synthetic // 8))} if a.synthetic else {}
+    splits, _ = tfdl.datasets.load(name="mnist", with_info=True, as_supervised=True, **kw)
+    test = splits["test"].map(lambda im, lb: (tfdl.utils.cast(im, tfdl.utils.float32) / 255, lb)).batch(PER_WORKER_BATCH)
+    model = tfdl.models.build_and_compile_cnn_model(learning_rate=a.learning_rate)
+    ev = tfdl.keras.utils.SidecarEvaluator(model, test, a.checkpoint_dir, until_step=a.epochs * a.steps_per_epoch,
+                                           log_dir=os.path.join(a.checkpoint_dir, "logs"), poll_interval_s=0.2, timeout_s=300)
+    for out in ev.start():
+        print(json.dumps({"evaluator": True, **{k: v for k, v in out.items()}}))
+
+
 def main() -> None:
     a = parse_args()
     tfdl.datasets.disable_progress_bar()
+    if not a.mirrored and tfdl.cluster.TFConfigClusterResolver.from_env(a.tf_config).task_type == "evaluator":
+        return run_evaluator(a)
     strategy = make_strategy(a)  # TF_CONFIG is read here, before anything else touches the devices
     global_batch = PER_WORKER_BATCH * strategy.num_replicas_in_sync
 

@@ -35,5 +35,10 @@ class utils:  # tf.keras.utils look-alike
         config.set_random_seed(seed)
 
 
+from .sidecar import SidecarEvaluator  # noqa: E402
+
+utils.SidecarEvaluator = SidecarEvaluator
+
+
 __all__ = ["callbacks", "layers", "losses", "metrics", "optimizers", "History", "Model", "Sequential", "TorchEngine",
            "mixed_precision", "backend", "clear_session", "models", "Input", "utils"]

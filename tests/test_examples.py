@@ -48,3 +48,35 @@ def test_tutorial_walkthrough_code_runs(tmp_path):
     assert r.returncode == 0, r.stdout[-4000:]
     assert "HISTORY" in r.stdout
     assert any(f.startswith("ckpt-2") and f.endswith(".index") for f in os.listdir(tmp_path))
+
+
+def test_example_cluster_with_an_evaluator_task(tmp_path):
+    """chief + worker train over the TCP ring while an `evaluator` task of the same TF_CONFIG cluster (README.md:38-44,57
+    of the reference) evaluates each checkpoint the chief writes."""
+    import socket
+
+    def port():
+        with socket.socket() as s:
+            s.bind(("127.0.0.1", 0))
+            return s.getsockname()[1]
+
+    cluster = {"chief": [f"127.0.0.1:{port()}"], "worker": [f"127.0.0.1:{port()}"], "evaluator": [f"127.0.0.1:{port()}"]}
+    base = [sys.executable, os.path.join(ROOT, "examples", "mnist_multiworker.py"), "--device", "cpu", "--synthetic", "512",
+            "--epochs", "2", "--steps-per-epoch", "2", "--communication", "RING", "--checkpoint-dir", str(tmp_path / "run")]
+    env0 = {k: v for k, v in os.environ.items() if k not in ("TF_CONFIG", "RANK", "WORLD_SIZE", "LOCAL_RANK")}
+    env0["CUDA_VISIBLE_DEVICES"] = ""
+    procs = []
+    for ttype, idx in (("evaluator", 0), ("chief", 0), ("worker", 0)):
+        env = dict(env0, TF_CONFIG=json.dumps({"cluster": cluster, "task": {"type": ttype, "index": idx}}))
+        procs.append((ttype, subprocess.Popen(base, stdout=subprocess.PIPE, stderr=subprocess.STDOUT, text=True, env=env)))
+    outs = {}
+    for ttype, p in procs:
+        out, _ = p.communicate(timeout=600)
+        assert p.returncode == 0, (ttype, out[-3000:])
+        outs[ttype] = out
+    evals = [json.loads(l) for l in outs["evaluator"].splitlines() if l.startswith("{") and "evaluator" in l]
+    # it stops at the run's last checkpoint (step counter 4 = 2 epochs x 2 steps); an epoch that is overwritten between two
+    # polls is skipped, as with TensorFlow's SidecarEvaluator
+    assert 1 <= len(evals) <= 2 and evals[-1]["checkpoint"].endswith("ckpt-2") and evals[-1]["step"] == 4
+    assert all("loss" in e and "sparse_categorical_accuracy" in e for e in evals)
+    assert any(l.startswith("{") and '"replicas": 2' in l for l in outs["chief"].splitlines())  # two training replicas

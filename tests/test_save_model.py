@@ -135,3 +135,44 @@ def test_only_the_chief_writes_the_saved_model(tmp_path):
     assert res[0][0] == "ok" and res[1][0] == "ok", res
     assert res[0][1] == (["model.json", "variables"], True)
     assert res[1][1] == ([], None)  # README.md:51: the chief does the saving
+
+
+def test_sidecar_evaluator_follows_the_chiefs_checkpoints(tmp_path):
+    """The `evaluator` role of TF_CONFIG (README.md:38-44,57 of the reference): outside the training group, it evaluates
+    each checkpoint the chief writes."""
+    import threading
+
+    from tfdl.cluster import TFConfigClusterResolver
+
+    cfg = {"cluster": {"worker": ["127.0.0.1:1", "127.0.0.1:2"], "evaluator": ["127.0.0.1:3"]},
+           "task": {"type": "evaluator", "index": 0}}
+    res = TFConfigClusterResolver.from_env(cfg)
+    assert res.task_type == "evaluator" and not res.is_training_task
+    with pytest.raises(ValueError, match="not a training replica"):
+        tfdl.distribute.MultiWorkerMirroredStrategy(tf_config=cfg, devices=["cpu"])
+
+    x, y = _data(96)
+    ckpt = str(tmp_path / "ckpt")
+    trainer = tfdl.models.build_and_compile_cnn_model(learning_rate=0.05)
+    side = tfdl.models.build_and_compile_cnn_model(learning_rate=0.05)  # the evaluator's own copy, default strategy
+    seen = []
+    ev = keras.utils.SidecarEvaluator(side, tfdl.data.Dataset.from_tensor_slices((x, y)).batch(32), ckpt, max_evaluations=2,
+                                      callbacks=[keras.callbacks.LambdaCallback(on_epoch_end=lambda e, logs: seen.append(dict(logs)))],
+                                      log_dir=str(tmp_path / "logs"), poll_interval_s=0.05, timeout_s=60)
+    assert ev.evaluate_once() is None  # nothing written yet
+    t = threading.Thread(target=ev.start)
+    t.start()
+    for epoch in range(2):  # the chief: one checkpoint per epoch
+        trainer.fit(x, y, batch_size=32, epochs=1, shuffle=False, verbose=0,
+                    callbacks=[keras.callbacks.ModelCheckpoint(os.path.join(ckpt, "ck-%d" % epoch))])
+        want = trainer.evaluate(x, y, batch_size=32, return_dict=True)
+        deadline = __import__("time").time() + 60
+        while len(ev.history) <= epoch and __import__("time").time() < deadline:
+            __import__("time").sleep(0.05)
+        assert len(ev.history) == epoch + 1, ev.history
+        got = ev.history[epoch]
+        assert got["checkpoint"].endswith("ck-%d" % epoch) and got["step"] == 3 * (epoch + 1)
+        assert abs(got["loss"] - want["loss"]) < 1e-6
+    t.join(timeout=60)
+    assert not t.is_alive() and len(seen) == 2 and "loss" in seen[0]
+    assert os.listdir(tmp_path / "logs" / "validation")
