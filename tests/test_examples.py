@@ -80,3 +80,20 @@ def test_example_cluster_with_an_evaluator_task(tmp_path):
     assert 1 <= len(evals) <= 2 and evals[-1]["checkpoint"].endswith("ckpt-2") and evals[-1]["step"] == 4
     assert all("loss" in e and "sparse_categorical_accuracy" in e for e in evals)
     assert any(l.startswith("{") and '"replicas": 2' in l for l in outs["chief"].splitlines())  # two training replicas
+
+
+def test_cpu_side_tools_run():
+    """tools/fit_overhead.py (host cost of fit() on the index path, no GPU needed) and tools/cpu_topology.py."""
+    env = {k: v for k, v in os.environ.items() if k not in ("TF_CONFIG", "RANK", "WORLD_SIZE", "LOCAL_RANK")}
+    env["CUDA_VISIBLE_DEVICES"] = ""
+    r = subprocess.run([sys.executable, os.path.join(ROOT, "tools", "fit_overhead.py"), "--reps", "5"], stdout=subprocess.PIPE,
+                       stderr=subprocess.STDOUT, text=True, timeout=600, env=env)
+    assert r.returncode == 0, r.stdout[-3000:]
+    out = json.loads(r.stdout.strip().splitlines()[-1])
+    assert out["steps"] == 20 and 0 < out["fit_until_first_train_call_us"] <= out["fit_python_only_us"] < 1e5
+    assert 0 < out["gather_job_first_2_records_us"] <= out["gather_job_all_records_us"]
+    r = subprocess.run([sys.executable, os.path.join(ROOT, "tools", "cpu_topology.py")], stdout=subprocess.PIPE,
+                       stderr=subprocess.STDOUT, text=True, timeout=300, env=env)
+    assert r.returncode == 0, r.stdout[-3000:]
+    topo = json.loads([l for l in r.stdout.splitlines() if l.startswith("CPU_TOPOLOGY ")][-1][len("CPU_TOPOLOGY "):])
+    assert topo["cpu_count"] >= 1 and topo["allowed"]
