@@ -27,3 +27,25 @@ def test_runtime_is_clean_under_thread_sanitizer(tmp_path):
     r = subprocess.run([exe, "4", str(base), "5"], capture_output=True, text=True, timeout=300, env=env)
     assert r.returncode == 0 and "ThreadSanitizer" not in r.stderr, (r.stdout[-500:], r.stderr[-3000:])
     assert "-> ok" in r.stdout
+
+
+def test_runtime_is_clean_under_address_and_ub_sanitizers(tmp_path):
+    """The same in-process multi-rank driver (collectives, worker pool, blocking and background gathers) under
+    AddressSanitizer + UndefinedBehaviorSanitizer."""
+    if shutil.which("g++") is None:
+        pytest.skip("no g++")
+    exe = str(tmp_path / "asan_driver")
+    srcs = [os.path.join(ROOT, "csrc", "runtime", f) for f in sorted(os.listdir(os.path.join(ROOT, "csrc", "runtime")))
+            if f.endswith(".cc")] + [os.path.join(ROOT, "csrc", "runtime_tests", "tsan_driver.cc")]
+    b = subprocess.run(["g++", "-std=c++17", "-g", "-O1", "-fsanitize=address,undefined", "-fno-omit-frame-pointer", "-pthread",
+                        *srcs, "-o", exe], capture_output=True, text=True)
+    if b.returncode != 0 and ("asan" in (b.stderr or "").lower() or "ubsan" in (b.stderr or "").lower()):
+        pytest.skip("libasan / libubsan not available")
+    assert b.returncode == 0, b.stderr[-2000:]
+    base = free_ports(1)[0]
+    env = dict(os.environ, ASAN_OPTIONS="detect_leaks=0", UBSAN_OPTIONS="halt_on_error=1:print_stacktrace=1")
+    env.pop("LD_PRELOAD", None)
+    r = subprocess.run([exe, "4", str(base), "4"], capture_output=True, text=True, timeout=300, env=env)
+    assert r.returncode == 0 and "ERROR: AddressSanitizer" not in r.stderr and "runtime error" not in r.stderr, (
+        r.stdout[-500:], r.stderr[-3000:])
+    assert "-> ok" in r.stdout
