@@ -2,10 +2,11 @@
 // group (listener, ring / control / heartbeat sockets, heartbeat thread), hammering barrier / allgather /
 // broadcast / ring all-reduce back to back, then blocking and background gathers on the shared worker pool. Built with -fsanitize=thread by tools/sanitize.sh (ThreadSanitizer
 // sees every pair of threads because they share the process), and without it as a plain stress test.
-//   usage: tsan_driver <world> <base_port> <iters>
+//   usage: tsan_driver <world> <base_port> <iters> [scratch_dir]
 #include <cmath>
 #include <cstdio>
 #include <cstdlib>
+#include <cstring>
 #include <string>
 #include <thread>
 #include <vector>
@@ -40,7 +41,51 @@ static int run_gathers(int rank, int iters) {
   return 0;
 }
 
-static int run_rank(int rank, int world, const std::vector<std::string>& addrs, int iters) {
+// Checkpoint bundle + event file round trip (memory-error coverage under ASan / UBSan; one call, rank-private paths).
+static int run_files(int rank, const std::string& dir) {
+  const std::string prefix = dir + "/ck-rank" + std::to_string(rank);
+  std::vector<float> a(3 * 5 * 7), b(1);
+  for (size_t i = 0; i < a.size(); ++i) a[i] = (float)i * 0.25f - 3.f;
+  b[0] = 42.f;
+  std::vector<int64_t> it(1, 1234567);
+  void* w = tfdl_rt_bundle_writer_create(prefix.c_str());
+  if (!w) return 30;
+  const int64_t da[3] = {3, 5, 7}, db[1] = {1};
+  if (tfdl_rt_bundle_writer_add(w, "layer/kernel", 1 /* DT_FLOAT */, 3, da, a.data(), a.size() * 4)) return 31;
+  if (tfdl_rt_bundle_writer_add(w, "layer/bias", 1, 1, db, b.data(), 4)) return 32;
+  if (tfdl_rt_bundle_writer_add(w, "optimizer/iter", 9 /* DT_INT64 */, 0, nullptr, it.data(), 8)) return 33;
+  if (tfdl_rt_bundle_writer_add_string(w, "_GRAPH", "abc\0def", 7)) return 34;
+  if (tfdl_rt_bundle_writer_finish(w)) return 35;
+  void* r = tfdl_rt_bundle_reader_open(prefix.c_str());
+  if (!r) return 36;
+  const int n = tfdl_rt_bundle_reader_num_entries(r);
+  int seen = 0;
+  for (int i = 0; i < n; ++i) {
+    char key[256];
+    int dt = 0, nd = 0;
+    int64_t dims[8];
+    uint64_t nbytes = 0, got = 0;
+    if (tfdl_rt_bundle_reader_entry(r, i, key, sizeof key, &dt, &nd, dims, &nbytes)) return 37;
+    std::vector<char> buf(nbytes + 1);
+    if (tfdl_rt_bundle_reader_read(r, i, buf.data(), nbytes, &got)) return 38;
+    if (dt == 7 /* DT_STRING: the payload without its length prefix and checksum */ ? got != 7 : got != nbytes) return 44;
+    if (std::string(key) == "layer/kernel") {
+      if (nd != 3 || dims[2] != 7 || nbytes != a.size() * 4 || std::memcmp(buf.data(), a.data(), nbytes)) return 39;
+      ++seen;
+    }
+  }
+  tfdl_rt_bundle_reader_close(r);
+  if (seen != 1 || n < 4) return 40;
+  void* ev = tfdl_rt_events_open((dir + "/events-rank" + std::to_string(rank)).c_str(), ".v2");
+  if (!ev) return 41;
+  for (int s = 0; s < 5; ++s)
+    if (tfdl_rt_events_scalar(ev, "epoch_loss", 2.3 - 0.1 * s, s)) return 42;
+  if (tfdl_rt_events_flush(ev)) return 43;
+  tfdl_rt_events_close(ev);
+  return 0;
+}
+
+static int run_rank(int rank, int world, const std::vector<std::string>& addrs, int iters, const std::string& dir) {
   std::vector<const char*> c;
   for (auto& a : addrs) c.push_back(a.c_str());
   void* g = tfdl_rt_group_create(rank, world, c.data(), 20000, 50, 2000);
@@ -71,6 +116,7 @@ static int run_rank(int rank, int world, const std::vector<std::string>& addrs, 
     if (!bad && tfdl_rt_barrier(g)) bad = 10;
   }
   if (!bad) bad = run_gathers(rank, iters * 4);
+  if (!bad && !dir.empty()) bad = run_files(rank, dir);
   if (bad) std::fprintf(stderr, "rank %d: check %d failed: %s\n", rank, bad, tfdl_rt_last_error());
   if (tfdl_rt_group_failed_rank(g) != -1) bad = bad ? bad : 11;
   tfdl_rt_group_destroy(g);
@@ -81,11 +127,12 @@ int main(int argc, char** argv) {
   const int world = argc > 1 ? std::atoi(argv[1]) : 4;
   const int base = argc > 2 ? std::atoi(argv[2]) : 24500;
   const int iters = argc > 3 ? std::atoi(argv[3]) : 20;
+  const std::string dir = argc > 4 ? argv[4] : "";  // where the checkpoint / event-file round trip may write (optional)
   std::vector<std::string> addrs;
   for (int r = 0; r < world; ++r) addrs.push_back("127.0.0.1:" + std::to_string(base + r));
   std::vector<int> rc(world, 0);
   std::vector<std::thread> th;
-  for (int r = 0; r < world; ++r) th.emplace_back([&, r] { rc[r] = run_rank(r, world, addrs, iters); });
+  for (int r = 0; r < world; ++r) th.emplace_back([&, r] { rc[r] = run_rank(r, world, addrs, iters, dir); });
   for (auto& t : th) t.join();
   int bad = 0;
   for (int r = 0; r < world; ++r) bad |= rc[r];
