@@ -5,7 +5,7 @@ import time
 import numpy as np
 import pytest
 
-from _mp import run_workers
+from _mp import free_ports, run_workers
 
 native = pytest.importorskip("tfdl.runtime.native")
 if not native.available():  # pragma: no cover
@@ -234,3 +234,58 @@ def test_gather_jobs_queue_behind_each_other_and_reject_bad_rows():
         rt.GatherJob(x, y, bad, k, B, rings[0].ctypes.data, rec)
     with pytest.raises(RuntimeError, match="out of range"):
         rt.gather_records(x, y, bad, k, B, rings[0].ctypes.data, rec)
+
+
+def test_rendezvous_ignores_stray_connections():
+    """Something else connects to a worker's port while the cluster is forming (a port scanner, a health probe): bytes that
+    are not this protocol's hello, or a connection that closes half way through it, are dropped and the rendezvous goes on."""
+    import socket
+    import threading
+
+    from tfdl.runtime import native
+
+    addrs = [f"127.0.0.1:{p}" for p in free_ports(2)]
+    groups, errors = {}, []
+
+    def join(rank):
+        try:
+            groups[rank] = native.Group(rank, addrs, timeout_s=30, hb_timeout_s=5)
+        except Exception as e:  # noqa: BLE001
+            errors.append((rank, repr(e)))
+
+    t0 = threading.Thread(target=join, args=(0,))
+    t0.start()
+    host, port = addrs[0].split(":")
+    deadline = time.time() + 10
+    while True:  # wait until rank 0 listens
+        try:
+            s = socket.create_connection((host, int(port)), timeout=1)
+            break
+        except OSError:
+            assert time.time() < deadline
+            time.sleep(0.05)
+    s.sendall(os.urandom(64))  # not a hello
+    s.close()
+    s2 = socket.create_connection((host, int(port)), timeout=1)
+    s2.sendall(b"\x01\x02\x03")  # closes in the middle of one
+    s2.close()
+    t1 = threading.Thread(target=join, args=(1,))
+    t1.start()
+    t0.join(40)
+    t1.join(40)
+    assert not errors and set(groups) == {0, 1}, errors
+    try:
+        out = {}
+
+        def reduce(rank):
+            a = np.full(1000, rank + 1.0, dtype=np.float32)
+            groups[rank].allreduce_(a)
+            out[rank] = a
+
+        ts = [threading.Thread(target=reduce, args=(r,)) for r in (0, 1)]
+        [t.start() for t in ts]
+        [t.join(30) for t in ts]
+        assert np.all(out[0] == 3.0) and np.all(out[1] == 3.0)
+    finally:
+        for g in groups.values():
+            g.close()
