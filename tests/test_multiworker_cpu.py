@@ -132,3 +132,40 @@ def test_auto_across_hosts_takes_the_ring_and_nccl_is_refused():
     assert res[0][1] == "ring" and res[1][1] == "ring", res
     res = run_workers(_topology, 2, args=("NCCL",), timeout=60)
     assert all("different hosts" in v[1] for v in res.values()), res
+
+
+def _train_with_validation(rank, addrs):
+    import tfdl
+    from tfdl import keras
+    from tfdl.models import build_and_compile_cnn_model
+
+    os.environ["TF_CONFIG"] = json.dumps({"cluster": {"chief": addrs[:1], "worker": addrs[1:]},
+                                          "task": {"type": "chief" if rank == 0 else "worker", "index": max(0, rank - 1)}})
+    strategy = tfdl.distribute.experimental.MultiWorkerMirroredStrategy(timeout_s=30, heartbeat_timeout_s=5)
+    rng = np.random.default_rng(0)
+    x, y = rng.random((192, 28, 28, 1), dtype=np.float32), rng.integers(0, 10, size=192)
+    xv, yv = rng.random((60, 28, 28, 1), dtype=np.float32), rng.integers(0, 10, size=60)
+    with strategy.scope():
+        model = build_and_compile_cnn_model(learning_rate=0.05)
+    cb = keras.callbacks.EarlyStopping(monitor="val_loss", patience=0, min_delta=100.0)  # stops after the second epoch
+    h = model.fit(x, y, batch_size=48, epochs=5, shuffle=False, verbose=0, validation_data=(xv, yv), callbacks=[cb])
+    alone = model.evaluate(xv, yv, batch_size=48, return_dict=True)
+    out = {"history": h.history, "alone": alone, "weights": model.get_weights(), "chief": strategy.is_chief}
+    strategy.close()
+    return out
+
+
+def test_three_tasks_with_a_chief_validation_and_early_stopping():
+    """chief + 2 workers (README.md:38-51 of the reference), arrays in, validation arrays, a callback that stops training
+    from the validation loss: every task sees the same logs, takes the same decision and ends with the same weights."""
+    res = run_workers(_train_with_validation, 3, timeout=240)
+    assert all(v[0] == "ok" for v in res.values()), res
+    outs = [res[r][1] for r in range(3)]
+    assert [o["chief"] for o in outs] == [True, False, False]
+    for o in outs[1:]:
+        assert o["history"] == outs[0]["history"]
+        for a, b in zip(o["weights"], outs[0]["weights"]):
+            np.testing.assert_array_equal(a, b)
+    h = outs[0]["history"]
+    assert len(h["loss"]) == 2 and len(h["val_loss"]) == 2  # stopped early, everywhere at the same epoch
+    assert abs(h["val_loss"][-1] - outs[0]["alone"]["loss"]) < 1e-5
