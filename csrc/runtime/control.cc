@@ -25,6 +25,7 @@
 
 #include <atomic>
 #include <chrono>
+#include <condition_variable>
 #include <mutex>
 #include <thread>
 
@@ -88,10 +89,36 @@ struct Group {
   std::vector<char> scratch;
   uint64_t bytes_sent = 0, bytes_recv = 0;
 
+  // Send half of a large ring step on a second thread: at these sizes a step is two memory copies into / out of the
+  // socket buffers plus the accumulation, and one thread doing all three is what bounds the bandwidth. The helper is
+  // created on the first large collective and parked on a condition variable between steps.
+  struct Sender {
+    std::thread th;
+    std::mutex mu;
+    std::condition_variable cv;
+    const char* ptr = nullptr;
+    size_t len = 0;
+    int peer = 0;
+    bool has_job = false, done = true, quit = false;
+    int rc = 0;
+    uint64_t sent = 0;
+    char err[512] = "";
+    std::atomic<bool> abort{false};
+  } sender;
+
   ~Group() { shutdown_all(); }
 
   void shutdown_all() {
     stop = true;
+    if (sender.th.joinable()) {
+      {
+        std::lock_guard<std::mutex> lk(sender.mu);
+        sender.quit = true;
+        sender.abort = true;
+      }
+      sender.cv.notify_all();
+      sender.th.join();
+    }
     if (hb_thread.joinable()) hb_thread.join();
     auto cl = [](int& fd) {
       if (fd >= 0) {
@@ -462,9 +489,108 @@ extern "C" int tfdl_rt_broadcast0(void* h, void* buf, uint64_t nbytes) {
   return 0;
 }
 
+// ---- helper thread for the send half of large ring steps ---------------------------------------------------
+static void sender_loop(Group* g) {
+  Group::Sender& s = g->sender;
+  for (;;) {
+    const char* p;
+    size_t left;
+    int peer;
+    {
+      std::unique_lock<std::mutex> lk(s.mu);
+      s.cv.wait(lk, [&] { return s.has_job || s.quit; });
+      if (s.quit) return;
+      p = s.ptr;
+      left = s.len;
+      peer = s.peer;
+    }
+    int rc = 0;
+    uint64_t sent = 0;
+    char err[512] = "";
+    int64_t deadline = now_ms() + g->timeout_ms;
+    while (left && rc == 0) {
+      if (s.abort.load()) { rc = -5; break; }  // the receiving side gave up: its error is the one that is reported
+      if (int f = g->failed_rank.load(); f >= 0) {
+        snprintf(err, sizeof err, "ring all-reduce aborted: rank %d (%s) is unreachable or has exited", f,
+                 f < (int)g->addrs.size() ? g->addrs[f].c_str() : "?");
+        rc = -2;
+        break;
+      }
+      pollfd pf{g->ring_send, POLLOUT, 0};
+      int pr = poll(&pf, 1, 100);
+      if (pr < 0 && errno == EINTR) continue;
+      if (pr == 0) {
+        if (now_ms() > deadline) {
+          snprintf(err, sizeof err, "ring all-reduce timed out after %d ms (sending to rank %d)", g->timeout_ms, peer);
+          rc = -3;
+        }
+        continue;
+      }
+      ssize_t w = ::send(g->ring_send, p, left, MSG_NOSIGNAL);
+      if (w > 0) {
+        p += w;
+        left -= (size_t)w;
+        sent += (uint64_t)w;
+        deadline = now_ms() + g->timeout_ms;
+      } else if (w < 0 && errno != EAGAIN && errno != EWOULDBLOCK && errno != EINTR) {
+        if (g->failed_rank.load() < 0) g->failed_rank = peer;
+        snprintf(err, sizeof err, "ring all-reduce: connection to rank %d (%s) lost: %s", peer, g->addrs[peer].c_str(),
+                 strerror(errno));
+        rc = -2;
+      }
+    }
+    {
+      std::lock_guard<std::mutex> lk(s.mu);
+      s.rc = rc;
+      s.sent = sent;
+      memcpy(s.err, err, sizeof err);
+      s.has_job = false;
+      s.done = true;
+    }
+    s.cv.notify_all();
+  }
+}
+static void sender_start(Group* g, const char* p, size_t len, int peer) {
+  Group::Sender& s = g->sender;
+  if (!s.th.joinable()) s.th = std::thread(sender_loop, g);
+  {
+    std::lock_guard<std::mutex> lk(s.mu);
+    s.ptr = p;
+    s.len = len;
+    s.peer = peer;
+    s.abort = false;
+    s.done = false;
+    s.has_job = true;
+  }
+  s.cv.notify_all();
+}
+// Waits for the helper's step; gives up = true makes it stop early. Returns its rc (error text already set).
+static int sender_join(Group* g, bool give_up) {
+  Group::Sender& s = g->sender;
+  if (give_up) s.abort = true;
+  std::unique_lock<std::mutex> lk(s.mu);
+  s.cv.wait(lk, [&] { return s.done; });
+  g->bytes_sent += s.sent;
+  s.sent = 0;
+  if (s.rc != 0 && s.rc != -5 && !give_up) set_error("%s", s.err);
+  return s.rc;
+}
+// Below this size a step is latency, not copy bandwidth (TFDL_RING_THREAD_BYTES overrides; 0 = never use the helper).
+static size_t threaded_step_bytes() {
+  static const size_t v = [] {
+    if (const char* e = getenv("TFDL_RING_THREAD_BYTES")) {
+      const long long b = atoll(e);
+      return b <= 0 ? (size_t)-1 : (size_t)b;
+    }
+    return (size_t)(1 << 20);
+  }();
+  return v;
+}
+
 // Ring all-reduce (sum): W-1 reduce-scatter steps then W-1 all-gather steps; each step sends one
 // segment to the next rank while receiving one from the previous rank, both non-blocking under a
-// single poll() loop, and the incoming bytes are accumulated as they arrive.
+// single poll() loop, and the incoming bytes are accumulated as they arrive. From 1 MB per step the
+// send half moves to a helper thread (sender_loop above).
 template <class T>
 static int ring_allreduce(Group* g, T* buf, int64_t n) {
   const int W = g->world, R = g->rank;
@@ -504,6 +630,11 @@ static int ring_allreduce(Group* g, T* buf, int64_t n) {
       size_t rtotal = (off[recv_seg + 1] - off[recv_seg]) * sizeof(T), rgot = 0, rdone_elems = 0;
       char* rp = phase == 0 ? g->scratch.data() : reinterpret_cast<char*>(dst);
       int64_t deadline = now_ms() + g->timeout_ms;
+      const bool threaded = sleft >= threaded_step_bytes();
+      if (threaded) {  // the helper sends this step's segment; this thread receives and accumulates
+        sender_start(g, sp, sleft, next);
+        sleft = 0;
+      }
       while ((sleft || rgot < rtotal) && rc == 0) {
         if (g->check_failed("ring all-reduce")) { rc = -2; break; }
         pollfd pf[2] = {{g->ring_send, (short)(sleft ? POLLOUT : 0), 0}, {g->ring_recv, (short)(rgot < rtotal ? POLLIN : 0), 0}};
@@ -541,6 +672,10 @@ static int ring_allreduce(Group* g, T* buf, int64_t n) {
             rc = -2;
           }
         }
+      }
+      if (threaded) {
+        const int src = sender_join(g, rc != 0);
+        if (rc == 0 && src != 0) rc = src;
       }
     }
   }

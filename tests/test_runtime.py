@@ -67,7 +67,8 @@ def _w_collectives(rank, addrs, n):
     return got, [o["rank"] for o in objs], a, d, b
 
 
-@pytest.mark.parametrize("world,n", [(2, 225034), (3, 1001), (4, 7)])
+# the last two sizes give ring steps of 1 MB and more: the send half of each step runs on the helper thread (control.cc)
+@pytest.mark.parametrize("world,n", [(2, 225034), (3, 1001), (4, 7), (2, 1_500_001), (3, 1_000_003)])
 def test_group_collectives(world, n):
     res = run_workers(_w_collectives, world, args=(n,))
     assert all(v[0] == "ok" for v in res.values()), res
@@ -289,3 +290,34 @@ def test_rendezvous_ignores_stray_connections():
     finally:
         for g in groups.values():
             g.close()
+
+
+def _w_big_ring_with_a_death(rank, addrs):
+    """Large all-reduces (helper-thread path); rank 1 exits after the second one."""
+    from tfdl.runtime import native as nat
+
+    g = nat.Group(rank, addrs, timeout_s=20, hb_interval_s=0.1, hb_timeout_s=1.5)
+    buf = np.ones(2_000_000, dtype=np.float32)
+    t0 = time.time()
+    try:
+        for it in range(50):
+            if rank == 1 and it == 2:
+                os._exit(0)
+            buf[:] = 1.0
+            g.allreduce_(buf)
+            assert buf[0] == 2.0 and buf[-1] == 2.0
+    except nat.CollectiveError as e:
+        return str(e), time.time() - t0, g.failed_rank
+    finally:
+        if rank == 0:
+            g.close()
+    return "no error", time.time() - t0, -1
+
+
+def test_killed_worker_during_large_allreduce_is_reported_not_hung():
+    res = run_workers(_w_big_ring_with_a_death, 2, timeout=90, expect_fail=(1,))
+    status, out = res[0]
+    assert status == "ok", res
+    msg, dt, failed = out
+    assert "rank 1" in msg and msg != "no error", msg
+    assert dt < 30 and failed == 1

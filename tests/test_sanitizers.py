@@ -23,7 +23,8 @@ def test_runtime_is_clean_under_thread_sanitizer(tmp_path):
         pytest.skip("libtsan not available")
     assert b.returncode == 0, b.stderr[-2000:]
     base = free_ports(1)[0]
-    env = dict(os.environ, TSAN_OPTIONS="halt_on_error=1 exitcode=66")
+    # 64 KB: the driver's 400 KB all-reduces take the helper-thread path of the ring (send half on a second thread)
+    env = dict(os.environ, TSAN_OPTIONS="halt_on_error=1 exitcode=66", TFDL_RING_THREAD_BYTES="65536")
     r = subprocess.run([exe, "4", str(base), "5", str(tmp_path)], capture_output=True, text=True, timeout=300, env=env)
     assert r.returncode == 0 and "ThreadSanitizer" not in r.stderr, (r.stdout[-500:], r.stderr[-3000:])
     assert "-> ok" in r.stdout
@@ -43,7 +44,8 @@ def test_runtime_is_clean_under_address_and_ub_sanitizers(tmp_path):
         pytest.skip("libasan / libubsan not available")
     assert b.returncode == 0, b.stderr[-2000:]
     base = free_ports(1)[0]
-    env = dict(os.environ, ASAN_OPTIONS="detect_leaks=0", UBSAN_OPTIONS="halt_on_error=1:print_stacktrace=1")
+    env = dict(os.environ, ASAN_OPTIONS="detect_leaks=0", UBSAN_OPTIONS="halt_on_error=1:print_stacktrace=1",
+               TFDL_RING_THREAD_BYTES="65536")
     env.pop("LD_PRELOAD", None)
     r = subprocess.run([exe, "4", str(base), "4", str(tmp_path)], capture_output=True, text=True, timeout=300, env=env)
     assert r.returncode == 0 and "ERROR: AddressSanitizer" not in r.stderr and "runtime error" not in r.stderr, (

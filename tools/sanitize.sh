@@ -12,13 +12,13 @@ mode=${1:-host}
 if [ "$mode" = host ]; then
   mkdir -p build/san
   g++ -std=c++17 -g -O1 -fsanitize=thread -pthread csrc/runtime/*.cc csrc/runtime_tests/tsan_driver.cc -o build/san/tsan_driver || exit 2
-  TSAN_OPTIONS="halt_on_error=1 exitcode=66" timeout 600 ./build/san/tsan_driver "${2:-4}" "${3:-24600}" "${4:-10}"
+  TFDL_RING_THREAD_BYTES=65536 TSAN_OPTIONS="halt_on_error=1 exitcode=66" timeout 600 ./build/san/tsan_driver "${2:-4}" "${3:-24600}" "${4:-10}"
   exit $?
 fi
 if [ "$mode" = host-asan ]; then
   mkdir -p build/san
   g++ -std=c++17 -g -O1 -fsanitize=address,undefined -fno-omit-frame-pointer -pthread csrc/runtime/*.cc csrc/runtime_tests/tsan_driver.cc -o build/san/asan_driver || exit 2
-  ASAN_OPTIONS=detect_leaks=0 UBSAN_OPTIONS=halt_on_error=1:print_stacktrace=1 timeout 600 ./build/san/asan_driver "${2:-4}" "${3:-24700}" "${4:-6}"
+  TFDL_RING_THREAD_BYTES=65536 ASAN_OPTIONS=detect_leaks=0 UBSAN_OPTIONS=halt_on_error=1:print_stacktrace=1 timeout 600 ./build/san/asan_driver "${2:-4}" "${3:-24700}" "${4:-6}"
   exit $?
 fi
 tool=${2:-memcheck}
